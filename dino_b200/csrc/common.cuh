@@ -1,0 +1,91 @@
+// Shared declarations for the dino_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+namespace dino {
+
+// One dense contraction  C[M,N] = A[M,K] * B[K,N]  with the fused epilogue every stage of the
+// H1 step needs.  Operand element (m,k) of A lives at A[row(m)*a_sm + k*a_sk]; element (k,n) of
+// B at B[krow(k)*b_sk + n*b_sn].  Rows of C are grouped into samples of `sdim` consecutive rows
+// (the seed rows of one sample's Jacobian); per-sample vectors are indexed by b = m / sdim.
+//
+//   acc      = sum_k A(m,k) B(k,n)
+//   rowsum[b,n] += acc * yref[m,n]                 (optional; the d sigma term)
+//   v        = acc + bias[n]                       (optional)
+//   v        = act ? softplus(v) : v ; s_out[m,n] = act ? sigmoid(pre-activation) : -
+//   v        = (v + add_pre[m,n]) * scale[b,n] + add_post[m,n]      (each optional)
+//   C[m,n]   = v            or   atomicAdd(C[m,n], v)  when atomic_c (split-K weight gradients)
+struct GemmOp {
+  const float* A; long long a_sm, a_sk; int a_mod;   // a_mod>0: row(m) = m % a_mod (shared seed)
+  const float* B; long long b_sk, b_sn; int b_kmod;  // b_kmod>0: krow(k) = k % b_kmod
+  int M, N, K;
+  int k_per_split;                                   // K range handled by one blockIdx.z
+  float* C; long long ldc; int atomic_c;
+  int sdim;
+  const float* bias;
+  int act; float* s_out; long long ld_s;
+  const float* yref; long long ld_y; float* rowsum; long long ld_rs;
+  const float* add_pre; long long ld_ap;
+  const float* scale; long long ld_sc;
+  const float* add_post; long long ld_apo;
+};
+
+inline GemmOp gemm_op_zero() {
+  GemmOp o;
+  o.A = nullptr; o.a_sm = 0; o.a_sk = 0; o.a_mod = 0;
+  o.B = nullptr; o.b_sk = 0; o.b_sn = 0; o.b_kmod = 0;
+  o.M = o.N = o.K = 0; o.k_per_split = 0;
+  o.C = nullptr; o.ldc = 0; o.atomic_c = 0; o.sdim = 1;
+  o.bias = nullptr; o.act = 0; o.s_out = nullptr; o.ld_s = 0;
+  o.yref = nullptr; o.ld_y = 0; o.rowsum = nullptr; o.ld_rs = 0;
+  o.add_pre = nullptr; o.ld_ap = 0; o.scale = nullptr; o.ld_sc = 0;
+  o.add_post = nullptr; o.ld_apo = 0;
+  return o;
+}
+
+// fp32 SIMT engine (exact-parity mode).  Returns a cudaError_t from the launch.
+cudaError_t launch_gemm_simt(const GemmOp& op, int num_sms, cudaStream_t st);
+
+// ---- elementwise / reduction kernels (elementwise.cu) ---------------------------------------
+cudaError_t launch_gather_rows(const float* src, const int* idx, int rows, int cols, long long ld_src,
+                               float* dst, long long ld_dst, cudaStream_t st);
+cudaError_t launch_fill_identity(float* dst, int n, long long ld, cudaStream_t st);
+cudaError_t launch_scale_seed(const float* seed, long long seed_sample_stride, long long ld_seed,
+                              const float* s, long long ld_s, int B, int sdim, int n,
+                              float* out, long long ld_out, cudaStream_t st);
+cudaError_t launch_transpose_batched(const float* src, int B, int rows, int cols, float* dst,
+                                     long long ld_dst, const int* idx, cudaStream_t st);
+cudaError_t launch_loss_q(const float* qhat, long long ld_qh, const float* q, const float* qn2,
+                          const int* idx, int B, int n, float coef, float* dq, long long ld_dq,
+                          float* stats, cudaStream_t st);
+cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, const float* jn2,
+                          const int* idx, int B, int sdim, int n, float coef, int write_grad,
+                          float* stats, cudaStream_t st);
+cudaError_t launch_mlp_da(const float* dz, long long ld_dz, const float* s, long long ld_s,
+                          const float* rowsum, long long ld_rs, int B, int n, float* da,
+                          long long ld_da, float* dbias, cudaStream_t st);
+cudaError_t launch_sketch_close(const float* r0, long long ld_r0, const float* V, const int* idx,
+                                int B, int k, int dM, float* S, cudaStream_t st);
+cudaError_t launch_sketch_open(const float* dS, const float* V, const int* idx, int B, int k, int dM,
+                               float* dr0, long long ld_r0, cudaStream_t st);
+cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long n, float lr_t,
+                        float b1, float b2, float eps, cudaStream_t st);
+cudaError_t launch_sgd(float* p, const float* g, long long n, float lr, cudaStream_t st);
+cudaError_t launch_sqnorms(const float* x, long long n, long long len, float* out, cudaStream_t st);
+cudaError_t launch_copy2d(const float* src, long long ld_src, float* dst, long long ld_dst, int rows,
+                          int cols, cudaStream_t st);
+
+// statistics slots accumulated by the loss kernels (floats)
+enum { ST_L2_SUM = 0, ST_H1_SUM = 1, ST_EQ_SUM = 2, ST_NQ_SUM = 3, ST_JROW_SUM = 4, ST_COUNT = 5,
+       ST_JROWS = 6, ST_SLOTS = 8 };
+
+__device__ __forceinline__ float softplus_f(float x) {
+  return fmaxf(x, 0.f) + log1pf(expf(-fabsf(x)));
+}
+__device__ __forceinline__ float sigmoid_f(float x) {
+  return 1.f / (1.f + expf(-x));
+}
+
+}  // namespace dino

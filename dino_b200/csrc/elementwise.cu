@@ -1,0 +1,378 @@
+// Bandwidth-bound kernels of the H1 step: gathers, the two loss kernels (which also emit the
+// loss gradients in place), the activation-derivative merge of the MLP backward, the sketch
+// open/close contractions and the fused Keras-form Adam / SGD updates.
+#include "common.cuh"
+
+namespace dino {
+
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void gather_rows_kernel(const float* __restrict__ src, const int* __restrict__ idx, int rows,
+                                   int cols, long long ld_src, float* __restrict__ dst, long long ld_dst) {
+  const long long total = (long long)rows * cols;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(e / cols), c = (int)(e % cols);
+    const long long sr = idx ? idx[r] : r;
+    dst[r * ld_dst + c] = __ldg(src + sr * ld_src + c);
+  }
+}
+cudaError_t launch_gather_rows(const float* src, const int* idx, int rows, int cols, long long ld_src,
+                               float* dst, long long ld_dst, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return cudaSuccess;
+  const long long total = (long long)rows * cols;
+  gather_rows_kernel<<<min(cdiv(total, 256), 148 * 8), 256, 0, st>>>(src, idx, rows, cols, ld_src, dst, ld_dst);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_copy2d(const float* src, long long ld_src, float* dst, long long ld_dst, int rows,
+                          int cols, cudaStream_t st) {
+  return launch_gather_rows(src, nullptr, rows, cols, ld_src, dst, ld_dst, st);
+}
+
+__global__ void fill_identity_kernel(float* dst, int n, long long ld) {
+  const long long total = (long long)n * ld;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const long long r = e / ld, c = e % ld;
+    dst[e] = (r == c) ? 1.f : 0.f;
+  }
+}
+cudaError_t launch_fill_identity(float* dst, int n, long long ld, cudaStream_t st) {
+  fill_identity_kernel<<<min(cdiv((long long)n * ld, 256), 148 * 8), 256, 0, st>>>(dst, n, ld);
+  return cudaGetLastError();
+}
+
+// out[(b*sdim+i), n] = seed[b*sample_stride + i*ld_seed + n] * s[b, n]
+__global__ void scale_seed_kernel(const float* __restrict__ seed, long long sample_stride, long long ld_seed,
+                                  const float* __restrict__ s, long long ld_s, int B, int sdim, int n,
+                                  float* __restrict__ out, long long ld_out) {
+  const long long total = (long long)B * sdim * n;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(e % n);
+    const long long row = e / n;
+    const int i = (int)(row % sdim);
+    const long long b = row / sdim;
+    float v = __ldg(seed + b * sample_stride + i * ld_seed + c);
+    if (s) v *= s[b * ld_s + c];
+    out[row * ld_out + c] = v;
+  }
+}
+cudaError_t launch_scale_seed(const float* seed, long long seed_sample_stride, long long ld_seed,
+                              const float* s, long long ld_s, int B, int sdim, int n, float* out,
+                              long long ld_out, cudaStream_t st) {
+  const long long total = (long long)B * sdim * n;
+  if (total <= 0) return cudaSuccess;
+  scale_seed_kernel<<<min(cdiv(total, 256), 148 * 8), 256, 0, st>>>(seed, seed_sample_stride, ld_seed, s, ld_s,
+                                                                  B, sdim, n, out, ld_out);
+  return cudaGetLastError();
+}
+
+// dst[(b*cols + j), r] = src[idx[b]][r][j]      (U [*, d_Q, k] -> U^T rows, one sample per z-block)
+__global__ void transpose_batched_kernel(const float* __restrict__ src, int rows, int cols,
+                                         float* __restrict__ dst, long long ld_dst, const int* __restrict__ idx) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const long long sb = idx ? idx[b] : b;
+  const float* s = src + sb * (long long)rows * cols;
+  const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (r < rows && c < cols) ? __ldg(s + (long long)r * cols + c) : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (c < cols && r < rows) dst[((long long)b * cols + c) * ld_dst + r] = tile[threadIdx.x][i];
+  }
+}
+cudaError_t launch_transpose_batched(const float* src, int B, int rows, int cols, float* dst,
+                                     long long ld_dst, const int* idx, cudaStream_t st) {
+  if (B <= 0) return cudaSuccess;
+  dim3 grid(cdiv(cols, 32), cdiv(rows, 32), B), block(32, 8);
+  transpose_batched_kernel<<<grid, block, 0, st>>>(src, rows, cols, dst, ld_dst, idx);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// normalized_mse on q (trainingUtilities.py:25-29): one warp per sample.
+__global__ void loss_q_kernel(const float* __restrict__ qhat, long long ld_qh, const float* __restrict__ q,
+                              const float* __restrict__ qn2, const int* __restrict__ idx, int B, int n,
+                              float coef, float* __restrict__ dq, long long ld_dq, float* __restrict__ stats) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= B) return;
+  const long long sb = idx ? idx[warp] : warp;
+  const float* qt = q + sb * n;
+  const float* qh = qhat + (long long)warp * ld_qh;
+  float e = 0.f;
+  for (int c = lane; c < n; c += 32) {
+    const float d = qh[c] - __ldg(qt + c);
+    e = fmaf(d, d, e);
+  }
+  e = warp_sum(e);
+  const float nq = __ldg(qn2 + sb);
+  if (dq != nullptr) {
+    const float g = coef / nq;
+    for (int c = lane; c < n; c += 32) dq[(long long)warp * ld_dq + c] = g * (qh[c] - __ldg(qt + c));
+  }
+  if (lane == 0) {
+    atomicAdd(stats + ST_L2_SUM, e / nq);
+    atomicAdd(stats + ST_EQ_SUM, e);
+    atomicAdd(stats + ST_NQ_SUM, nq);
+    atomicAdd(stats + ST_COUNT, 1.f);
+  }
+}
+cudaError_t launch_loss_q(const float* qhat, long long ld_qh, const float* q, const float* qn2, const int* idx,
+                          int B, int n, float coef, float* dq, long long ld_dq, float* stats, cudaStream_t st) {
+  if (B <= 0) return cudaSuccess;
+  loss_q_kernel<<<cdiv((long long)B * 32, 128), 128, 0, st>>>(qhat, ld_qh, q, qn2, idx, B, n, coef, dq, ld_dq, stats);
+  return cudaGetLastError();
+}
+
+// normalized_mse_matrix on the Jacobian (trainingUtilities.py:31-37): one warp per Jacobian row.
+// Reads the prediction row and the target row once; overwrites the prediction with
+// d loss / d J_hat = coef * (J_hat - J) / ||J_b||_F^2 when write_grad.
+__global__ void __launch_bounds__(256) loss_j_kernel(float* __restrict__ jhat, long long ld_jh,
+                                                     const float* __restrict__ jt, const float* __restrict__ jn2,
+                                                     const int* __restrict__ idx, int B, int sdim, int n,
+                                                     float coef, int write_grad, float* __restrict__ stats) {
+  __shared__ float red[3][8];
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long rows = (long long)B * sdim;
+  float h1 = 0.f, rr = 0.f, cnt = 0.f;
+  for (long long row = (long long)blockIdx.x * 8 + wib; row < rows; row += (long long)gridDim.x * 8) {
+    const int b = (int)(row / sdim), i = (int)(row % sdim);
+    const long long sb = idx ? idx[b] : b;
+    const float* t = jt + (sb * sdim + i) * (long long)n;
+    float* p = jhat + row * ld_jh;
+    const float nj = __ldg(jn2 + sb);
+    const float g = coef / nj;
+    float e = 0.f, nr = 0.f;
+    for (int c = lane; c < n; c += 32) {
+      const float tv = __ldg(t + c);
+      const float d = p[c] - tv;
+      e = fmaf(d, d, e);
+      nr = fmaf(tv, tv, nr);
+      if (write_grad) p[c] = g * d;
+    }
+    e = warp_sum(e);
+    nr = warp_sum(nr);
+    h1 += e / nj;
+    rr += e / nr;
+    cnt += 1.f;
+  }
+  if (lane == 0) { red[0][wib] = h1; red[1][wib] = rr; red[2][wib] = cnt; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    float v = 0.f;
+    for (int w = 0; w < 8; ++w) v += red[threadIdx.x][w];
+    const int slot = threadIdx.x == 0 ? ST_H1_SUM : (threadIdx.x == 1 ? ST_JROW_SUM : ST_JROWS);
+    atomicAdd(stats + slot, v);
+  }
+}
+cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, const float* jn2, const int* idx, int B,
+                          int sdim, int n, float coef, int write_grad, float* stats, cudaStream_t st) {
+  const long long rows = (long long)B * sdim;
+  if (rows <= 0) return cudaSuccess;
+  loss_j_kernel<<<min(cdiv(rows, 8), 148 * 16), 256, 0, st>>>(jhat, ld_jh, jt, jn2, idx, B, sdim, n, coef, write_grad,
+                                                            stats);
+  return cudaGetLastError();
+}
+
+// da = dz * s + rowsum * (1 - s)   and   dbias[n] = sum_b da[b,n]
+// (s == nullptr: linear layer, da = dz; rowsum == nullptr: no Jacobian term)
+__global__ void mlp_da_kernel(const float* __restrict__ dz, long long ld_dz, const float* __restrict__ s,
+                              long long ld_s, const float* __restrict__ rowsum, long long ld_rs, int B, int n,
+                              float* __restrict__ da, long long ld_da, float* __restrict__ dbias) {
+  __shared__ float red[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  float acc = 0.f;
+  if (c < n) {
+    for (int b = threadIdx.y; b < B; b += 8) {
+      float v = dz[(long long)b * ld_dz + c];
+      if (s != nullptr) {
+        const float sv = s[(long long)b * ld_s + c];
+        v *= sv;
+        if (rowsum != nullptr) v = fmaf(rowsum[(long long)b * ld_rs + c], 1.f - sv, v);
+      }
+      if (da != nullptr) da[(long long)b * ld_da + c] = v;
+      acc += v;
+    }
+  }
+  red[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < n && dbias != nullptr) {
+    float v = 0.f;
+    for (int r = 0; r < 8; ++r) v += red[r][threadIdx.x];
+    dbias[c] = v;
+  }
+}
+cudaError_t launch_mlp_da(const float* dz, long long ld_dz, const float* s, long long ld_s, const float* rowsum,
+                          long long ld_rs, int B, int n, float* da, long long ld_da, float* dbias, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  mlp_da_kernel<<<cdiv(n, 32), dim3(32, 8), 0, st>>>(dz, ld_dz, s, ld_s, rowsum, ld_rs, B, n, da, ld_da, dbias);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sketch closure  S[b] = R0[b] V[b]   ([k,dM] x [dM,k]) and its adjoint dR0[b] = dS[b] V[b]^T.
+// One CTA per (sample, 8 rows of S); V tiles staged through shared memory.
+__global__ void __launch_bounds__(256) sketch_close_kernel(const float* __restrict__ r0, long long ld_r0,
+                                                           const float* __restrict__ V, const int* __restrict__ idx,
+                                                           int k, int dM, float* __restrict__ S) {
+  extern __shared__ float sm[];
+  float* rt = sm;              // [8][64]
+  const int b = blockIdx.y, i0 = blockIdx.x * 8;
+  const long long sb = idx ? idx[b] : b;
+  const float* Vb = V + sb * (long long)dM * k;
+  const int tid = threadIdx.x;
+  // thread -> (row i = tid / 32, column group j = tid % 32 + 32*t)
+  const int li = tid >> 5, lane = tid & 31;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int d0 = 0; d0 < dM; d0 += 64) {
+    for (int e = tid; e < 8 * 64; e += 256) {
+      const int i = e / 64, d = e % 64;
+      rt[e] = (i0 + i < k && d0 + d < dM) ? r0[((long long)b * k + i0 + i) * ld_r0 + d0 + d] : 0.f;
+    }
+    __syncthreads();
+    const int dmax = min(64, dM - d0);
+    for (int d = 0; d < dmax; ++d) {
+      const float rv = rt[li * 64 + d];
+      const float* vrow = Vb + (long long)(d0 + d) * k;
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const int j = lane + 32 * t;
+        if (j < k) acc[t] = fmaf(rv, __ldg(vrow + j), acc[t]);
+      }
+    }
+    __syncthreads();
+  }
+  if (i0 + li < k) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int j = lane + 32 * t;
+      if (j < k) S[((long long)b * k + i0 + li) * k + j] = acc[t];
+    }
+  }
+}
+cudaError_t launch_sketch_close(const float* r0, long long ld_r0, const float* V, const int* idx, int B, int k,
+                                int dM, float* S, cudaStream_t st) {
+  if (B <= 0) return cudaSuccess;
+  if (k > 128) return cudaErrorInvalidValue;
+  sketch_close_kernel<<<dim3(cdiv(k, 8), B), 256, 8 * 64 * sizeof(float), st>>>(r0, ld_r0, V, idx, k, dM, S);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) sketch_open_kernel(const float* __restrict__ dS, const float* __restrict__ V,
+                                                          const int* __restrict__ idx, int k, int dM,
+                                                          float* __restrict__ dr0, long long ld_r0) {
+  extern __shared__ float sm[];   // dS[b] : k*k
+  const int b = blockIdx.y;
+  const long long sb = idx ? idx[b] : b;
+  const float* Vb = V + sb * (long long)dM * k;
+  for (int e = threadIdx.x; e < k * k; e += 256) sm[e] = dS[(long long)b * k * k + e];
+  __syncthreads();
+  const int d = blockIdx.x * 256 + threadIdx.x;
+  if (d >= dM) return;
+  const float* vrow = Vb + (long long)d * k;
+  for (int i = 0; i < k; ++i) {
+    float acc = 0.f;
+    for (int j = 0; j < k; ++j) acc = fmaf(sm[i * k + j], __ldg(vrow + j), acc);
+    dr0[((long long)b * k + i) * ld_r0 + d] = acc;
+  }
+}
+cudaError_t launch_sketch_open(const float* dS, const float* V, const int* idx, int B, int k, int dM, float* dr0,
+                               long long ld_r0, cudaStream_t st) {
+  if (B <= 0) return cudaSuccess;
+  if (k > 128) return cudaErrorInvalidValue;
+  const size_t smem = (size_t)k * k * sizeof(float);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(sketch_open_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  sketch_open_kernel<<<dim3(cdiv(dM, 256), B), 256, smem, st>>>(dS, V, idx, k, dM, dr0, ld_r0);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Keras-form Adam (TF ResourceApplyAdam): theta -= lr_t * m / (sqrt(v) + eps), lr_t carries the
+// bias correction and eps sits OUTSIDE it.
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                            float* __restrict__ v, long long n, float lr_t, float b1, float b2, float eps) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long n4 = n >> 2;
+  float4* p4 = reinterpret_cast<float4*>(p);
+  const float4* g4 = reinterpret_cast<const float4*>(g);
+  float4* m4 = reinterpret_cast<float4*>(m);
+  float4* v4 = reinterpret_cast<float4*>(v);
+  const float ob1 = 1.f - b1, ob2 = 1.f - b2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 P = p4[i], G = g4[i], M = m4[i], V = v4[i];
+#define DINO_ADAM1(c)                                   \
+    M.c = b1 * M.c + ob1 * G.c;                         \
+    V.c = b2 * V.c + ob2 * G.c * G.c;                   \
+    P.c -= lr_t * M.c / (sqrtf(V.c) + eps);
+    DINO_ADAM1(x) DINO_ADAM1(y) DINO_ADAM1(z) DINO_ADAM1(w)
+#undef DINO_ADAM1
+    p4[i] = P; m4[i] = M; v4[i] = V;
+  }
+  for (long long i = (n4 << 2) + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float G = g[i];
+    const float M = b1 * m[i] + ob1 * G;
+    const float V = b2 * v[i] + ob2 * G * G;
+    m[i] = M; v[i] = V;
+    p[i] -= lr_t * M / (sqrtf(V) + eps);
+  }
+}
+cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long n, float lr_t, float b1, float b2,
+                        float eps, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  adam_kernel<<<min(cdiv(n, 1024), 148 * 8), 256, 0, st>>>(p, g, m, v, n, lr_t, b1, b2, eps);
+  return cudaGetLastError();
+}
+
+__global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, long long n, float lr) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    p[i] -= lr * g[i];
+}
+cudaError_t launch_sgd(float* p, const float* g, long long n, float lr, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  sgd_kernel<<<min(cdiv(n, 256), 148 * 8), 256, 0, st>>>(p, g, n, lr);
+  return cudaGetLastError();
+}
+
+// out[i] = sum_j x[i,j]^2 : one CTA per row (rows are Jacobians of 2.5k .. 1.7M floats, or q rows)
+__global__ void __launch_bounds__(256) sqnorms_kernel(const float* __restrict__ x, long long len,
+                                                      float* __restrict__ out) {
+  __shared__ float red[8];
+  const float* r = x + (long long)blockIdx.x * len;
+  float acc = 0.f;
+  for (long long j = threadIdx.x; j < len; j += 256) {
+    const float v = __ldg(r + j);
+    acc = fmaf(v, v, acc);
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float v = 0.f;
+    for (int w = 0; w < 8; ++w) v += red[w];
+    out[blockIdx.x] = v;
+  }
+}
+cudaError_t launch_sqnorms(const float* x, long long n, long long len, float* out, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  if (n > 2147483647LL) return cudaErrorInvalidValue;
+  sqnorms_kernel<<<(unsigned)n, 256, 0, st>>>(x, len, out);
+  return cudaGetLastError();
+}
+
+}  // namespace dino

@@ -1,0 +1,246 @@
+// fp32 SIMT GEMM with the fused H1-step epilogue (exact-parity engine).
+//
+// Every dense contraction of the step (MLP forward/backward, the per-sample Jacobian chain, its
+// data-gradient and its split-K weight gradient) is one GemmOp (common.cuh).  This engine
+// computes it with FFMA only, so the result is fp32-exact up to summation order; the tcgen05
+// engine (gemm_tc.cu) replaces it for the large chain contractions in the tf32 precision mode.
+//
+// Tiling: BMxBNx16 per CTA, 256 threads, TMxTN register micro-tile, double-buffered shared
+// memory with register prefetch (one __syncthreads per K step).  Operands may be contiguous in
+// either of their two indices (the four NN/NT/TN/TT layouts), chosen from the strides.
+#include "common.cuh"
+
+namespace dino {
+
+constexpr int BK = 16;
+constexpr int NT = 256;
+
+template <int BM, int BN, int TM, int TN, bool A_KC, bool B_NC>
+__global__ void __launch_bounds__(NT) gemm_simt_kernel(const GemmOp op) {
+  static_assert((BM / TM) * (BN / TN) == NT, "thread layout");
+  constexpr int LDA_S = BM + 4, LDB_S = BN + 4;
+  constexpr int A_PER_T = BM * BK / NT, B_PER_T = BK * BN / NT;
+  __shared__ __align__(16) float smem[2 * BK * LDA_S + 2 * BK * LDB_S];
+  float* As = smem;
+  float* Bs = smem + 2 * BK * LDA_S;
+
+  const int tid = threadIdx.x;
+  const int tx = tid % (BN / TN), ty = tid / (BN / TN);
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int kbeg = blockIdx.z * op.k_per_split;
+  const int kend = min(op.K, kbeg + op.k_per_split);
+  const int nk = (kend - kbeg + BK - 1) / BK;
+
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+  float ra[A_PER_T], rb[B_PER_T];
+
+  auto load_regs = [&](int k0) {
+#pragma unroll
+    for (int j = 0; j < A_PER_T; ++j) {
+      const int e = tid + j * NT;
+      const int m = A_KC ? e / BK : e % BM;
+      const int k = A_KC ? e % BK : e / BM;
+      const int gm = m0 + m, gk = k0 + k;
+      float v = 0.f;
+      if (gm < op.M && gk < kend) {
+        const int r = op.a_mod > 0 ? gm % op.a_mod : gm;
+        v = __ldg(op.A + (long long)r * op.a_sm + (long long)gk * op.a_sk);
+      }
+      ra[j] = v;
+    }
+#pragma unroll
+    for (int j = 0; j < B_PER_T; ++j) {
+      const int e = tid + j * NT;
+      const int n = B_NC ? e % BN : e / BK;
+      const int k = B_NC ? e / BN : e % BK;
+      const int gn = n0 + n, gk = k0 + k;
+      float v = 0.f;
+      if (gn < op.N && gk < kend) {
+        const int kr = op.b_kmod > 0 ? gk % op.b_kmod : gk;
+        v = __ldg(op.B + (long long)kr * op.b_sk + (long long)gn * op.b_sn);
+      }
+      rb[j] = v;
+    }
+  };
+  auto store_smem = [&](int buf) {
+    float* as = As + buf * BK * LDA_S;
+    float* bs = Bs + buf * BK * LDB_S;
+#pragma unroll
+    for (int j = 0; j < A_PER_T; ++j) {
+      const int e = tid + j * NT;
+      const int m = A_KC ? e / BK : e % BM;
+      const int k = A_KC ? e % BK : e / BM;
+      as[k * LDA_S + m] = ra[j];
+    }
+#pragma unroll
+    for (int j = 0; j < B_PER_T; ++j) {
+      const int e = tid + j * NT;
+      const int n = B_NC ? e % BN : e / BK;
+      const int k = B_NC ? e / BN : e % BK;
+      bs[k * LDB_S + n] = rb[j];
+    }
+  };
+
+  if (nk > 0) {
+    load_regs(kbeg);
+    store_smem(0);
+  }
+  __syncthreads();
+  for (int kt = 0; kt < nk; ++kt) {
+    const int buf = kt & 1;
+    if (kt + 1 < nk) load_regs(kbeg + (kt + 1) * BK);
+    const float* as = As + buf * BK * LDA_S + ty * TM;
+    const float* bs = Bs + buf * BK * LDB_S + tx * TN;
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      float a[TM], b[TN];
+      if constexpr (TM % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < TM; i += 4) {
+          const float4 t = *reinterpret_cast<const float4*>(as + kk * LDA_S + i);
+          a[i] = t.x; a[i + 1] = t.y; a[i + 2] = t.z; a[i + 3] = t.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < TM; i += 2) {
+          const float2 t = *reinterpret_cast<const float2*>(as + kk * LDA_S + i);
+          a[i] = t.x; a[i + 1] = t.y;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < TN; j += 4) {
+        const float4 t = *reinterpret_cast<const float4*>(bs + kk * LDB_S + j);
+        b[j] = t.x; b[j + 1] = t.y; b[j + 2] = t.z; b[j + 3] = t.w;
+      }
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    if (kt + 1 < nk) store_smem(buf ^ 1);
+    __syncthreads();
+  }
+
+  // ---- rowsum[b,n] += sum over the sample's rows of acc * yref  (pre-epilogue accumulators) ----
+  if (op.rowsum != nullptr) {
+    const int sdim = op.sdim;
+    const int b_first = m0 / sdim;
+    const int m_last = min(op.M, m0 + BM) - 1;
+    const int ns = m_last / sdim - b_first + 1;
+    constexpr int SMEM_FLOATS = 2 * BK * LDA_S + 2 * BK * LDB_S;
+    const bool use_smem = ns * BN <= SMEM_FLOATS;      // main loop is over: tiles are free
+    if (use_smem) {
+      for (int e = tid; e < ns * BN; e += NT) smem[e] = 0.f;
+      __syncthreads();
+    }
+    float part[TN];
+    int cur_b = -1;
+    auto flush = [&]() {
+      if (cur_b < 0) return;
+#pragma unroll
+      for (int j = 0; j < TN; ++j) {
+        const int gn = n0 + tx * TN + j;
+        if (gn < op.N) {
+          if (use_smem) atomicAdd(&smem[(cur_b - b_first) * BN + tx * TN + j], part[j]);
+          else atomicAdd(op.rowsum + (long long)cur_b * op.ld_rs + gn, part[j]);
+        }
+      }
+    };
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+      const int gm = m0 + ty * TM + i;
+      if (gm >= op.M) break;
+      const int b = gm / sdim;
+      if (b != cur_b) {
+        flush();
+        cur_b = b;
+#pragma unroll
+        for (int j = 0; j < TN; ++j) part[j] = 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < TN; ++j) {
+        const int gn = n0 + tx * TN + j;
+        if (gn < op.N) part[j] = fmaf(acc[i][j], op.yref[(long long)gm * op.ld_y + gn], part[j]);
+      }
+    }
+    flush();
+    if (use_smem) {
+      __syncthreads();
+      for (int e = tid; e < ns * BN; e += NT) {
+        const int lb = e / BN, n = e % BN;
+        if (n0 + n < op.N) atomicAdd(op.rowsum + (long long)(b_first + lb) * op.ld_rs + n0 + n, smem[e]);
+      }
+    }
+  }
+
+  // ---- epilogue -------------------------------------------------------------------------------
+  if (op.C == nullptr) return;
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int gm = m0 + ty * TM + i;
+    if (gm >= op.M) break;
+    const int b = gm / op.sdim;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int gn = n0 + tx * TN + j;
+      if (gn >= op.N) continue;
+      float v = acc[i][j];
+      if (op.bias != nullptr) v += op.bias[gn];
+      if (op.act) {
+        if (op.s_out != nullptr) op.s_out[(long long)gm * op.ld_s + gn] = sigmoid_f(v);
+        v = softplus_f(v);
+      }
+      if (op.add_pre != nullptr) v += op.add_pre[(long long)gm * op.ld_ap + gn];
+      if (op.scale != nullptr) v *= op.scale[(long long)b * op.ld_sc + gn];
+      if (op.add_post != nullptr) v += op.add_post[(long long)gm * op.ld_apo + gn];
+      float* c = op.C + (long long)gm * op.ldc + gn;
+      if (op.atomic_c) atomicAdd(c, v);
+      else *c = v;
+    }
+  }
+}
+
+template <int BM, int BN, int TM, int TN>
+static cudaError_t launch_cfg(const GemmOp& op, int splits, cudaStream_t st) {
+  dim3 grid((op.N + BN - 1) / BN, (op.M + BM - 1) / BM, splits);
+  const bool akc = (op.a_sk == 1), bnc = (op.b_sn == 1);
+  if (akc && bnc) gemm_simt_kernel<BM, BN, TM, TN, true, true><<<grid, NT, 0, st>>>(op);
+  else if (akc && !bnc) gemm_simt_kernel<BM, BN, TM, TN, true, false><<<grid, NT, 0, st>>>(op);
+  else if (!akc && bnc) gemm_simt_kernel<BM, BN, TM, TN, false, true><<<grid, NT, 0, st>>>(op);
+  else gemm_simt_kernel<BM, BN, TM, TN, false, false><<<grid, NT, 0, st>>>(op);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gemm_simt(const GemmOp& op_in, int num_sms, cudaStream_t st) {
+  GemmOp op = op_in;
+  if (op.M <= 0 || op.N <= 0) return cudaSuccess;
+  if (op.sdim <= 0) op.sdim = 1;
+  const int BM = op.M <= 32 ? 32 : (op.M <= 64 ? 64 : 128);
+  int splits = 1;
+  if (op.atomic_c && op.k_per_split == 0) {
+    const int tiles = ((op.M + BM - 1) / BM) * ((op.N + 63) / 64);
+    const int kchunks = (op.K + BK - 1) / BK;
+    splits = (2 * num_sms + tiles - 1) / tiles;
+    if (splits > (kchunks + 1) / 2) splits = (kchunks + 1) / 2;
+    if (splits < 1) splits = 1;
+  }
+  if (op.k_per_split == 0) {
+    int kps = (op.K + splits - 1) / splits;
+    kps = ((kps + BK - 1) / BK) * BK;
+    if (kps < BK) kps = BK;
+    op.k_per_split = kps;
+  }
+  splits = (op.K + op.k_per_split - 1) / op.k_per_split;
+  if (splits < 1) splits = 1;
+  if (splits > 1 && !op.atomic_c) return cudaErrorInvalidValue;
+  if (BM == 32) return launch_cfg<32, 64, 2, 4>(op, splits, st);
+  if (BM == 64) return launch_cfg<64, 64, 4, 4>(op, splits, st);
+  return launch_cfg<128, 64, 8, 4>(op, splits, st);
+}
+
+}  // namespace dino

@@ -1,0 +1,489 @@
+// Execution plan and C ABI of the H1 training step (see include/dino_b200.h).
+//
+// The step runs the per-sample Jacobian in REVERSE mode, seeded on the output side with s rows
+// (identity, Phi^T or U_b^T), because s = min(d_in_seed, d_out_seed) for every configuration the
+// reference trains.  With z_0 = m, a_l = z_l W_l + b_l, sg_l = act'(a_l):
+//
+//   MLP forward      l = 0..L-1   z_{l+1} = act(a_l) [+ z_skip]
+//   chain forward    l = L-1..0   Q_l = R_{l+1} * sg_l ;  R_l = Q_l W_l^T [+ Q_skip]      R_L = seed
+//   losses                        dq, G = d loss / d R_0  (in place over R_0)
+//   chain backward   l = 0..L-1   dQ_l = dR_l W_l ; dW_l += dR_l^T Q_l ; rs_l = sum_rows dQ_l*Q_l ;
+//                                 dR_{l+1} = dQ_l * sg_l [+ dR_skip]
+//   MLP backward     l = L-1..0   da_l = dz_{l+1}*sg_l + rs_l*(1-sg_l) ; dW_l += z_l^T da_l ;
+//                                 db_l = sum_b da_l ; dz_l = da_l W_l^T [+ dz_skip]
+//
+// (softplus'' = sg(1-sg), which is why only the post-scaling Q_l has to be kept.)  The formulas
+// are checked against autograd double-backward in tests/test_pipeline_model.py.
+#include <math.h>
+#include <string.h>
+
+#include <atomic>
+#include <string>
+#include <vector>
+
+#include "../../include/dino_b200.h"
+#include "common.cuh"
+
+using namespace dino;
+
+static thread_local std::string g_err;
+static std::atomic<long long> g_launches{0};
+
+static int fail(const std::string& msg) {
+  g_err = msg;
+  return 1;
+}
+
+#define DINO_CUDA(expr)                                                                      \
+  do {                                                                                       \
+    cudaError_t _e = (expr);                                                                 \
+    if (_e != cudaSuccess)                                                                   \
+      return fail(std::string(#expr) + ": " + cudaGetErrorString(_e));                       \
+  } while (0)
+#define DINO_LAUNCH(expr)                                                                    \
+  do {                                                                                       \
+    g_launches.fetch_add(1, std::memory_order_relaxed);                                      \
+    DINO_CUDA(expr);                                                                         \
+  } while (0)
+
+static inline long long r4(long long n) { return (n + 3) & ~3LL; }
+
+struct LayerPlan {
+  int n_in, n_out, act, has_bias, trainable, skip_from;
+  long long koff, boff;      // offsets in the parameter arena (floats)
+  long long z_off, sg_off, q_off, rs_off;   // workspace offsets (floats); -1 when absent
+  long long ld_out;          // r4(n_out)
+  int lands_skip;            // index l2 of the skip layer whose source is THIS layer's input, or -1
+};
+
+struct DinoPlan {
+  int device, num_sms;
+  int d_in, d_out, L, jac_mode, s, max_batch, precision;
+  std::vector<LayerPlan> layers;
+  long long n_params;
+  bool seed_shared;          // FULL / OUT_REDUCED
+  bool top_materialised;     // Q_{L-1} stored in the workspace (else it is the shared seed itself)
+  // workspace offsets (floats)
+  long long off_ident, off_z0, off_r0, off_sk, off_dr[3], off_dz[3], off_da, off_rs_begin, rs_floats;
+  long long ld_in, ld_dr, ld_dz, ld_ident;
+  long long ws_floats;
+  float* ws;
+};
+
+static cudaStream_t S(dino_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+extern "C" const char* dino_last_error(void) { return g_err.c_str(); }
+extern "C" const char* dino_version(void) { return "dino_b200 0.1 (sm_100a)"; }
+extern "C" int64_t dino_launch_count(void) { return g_launches.load(); }
+
+extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** out) {
+  if (!spec || !out) return fail("dino_plan_create: null argument");
+  if (spec->n_layers < 1 || spec->d_in < 1 || spec->max_batch < 1) return fail("dino_plan_create: bad sizes");
+  if (spec->jac_mode < DINO_JAC_NONE || spec->jac_mode > DINO_JAC_SKETCHED) return fail("dino_plan_create: bad jac_mode");
+  if (spec->precision != DINO_PREC_FP32 && spec->precision != DINO_PREC_TF32)
+    return fail("dino_plan_create: bad precision");
+  int ndev = 0;
+  DINO_CUDA(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) return fail("dino_plan_create: no such CUDA device");
+  cudaDeviceProp prop;
+  DINO_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail("dino_plan_create: this library is built for sm_100a (B200) only");
+
+  DinoPlan* p = new DinoPlan();
+  p->device = device;
+  p->num_sms = prop.multiProcessorCount;
+  p->d_in = spec->d_in;
+  p->L = spec->n_layers;
+  p->jac_mode = spec->jac_mode;
+  p->max_batch = spec->max_batch;
+  p->precision = spec->precision;
+  p->ws = nullptr;
+  long long poff = 0;
+  int n_in = spec->d_in;
+  for (int l = 0; l < p->L; ++l) {
+    const DinoLayerSpec& ls = spec->layers[l];
+    LayerPlan lp;
+    lp.n_in = n_in; lp.n_out = ls.n_out; lp.act = ls.act; lp.has_bias = ls.has_bias;
+    lp.trainable = ls.trainable; lp.skip_from = ls.skip_from; lp.lands_skip = -1;
+    if (ls.n_out < 1) { delete p; return fail("dino_plan_create: layer width < 1"); }
+    if (ls.act != DINO_ACT_LINEAR && ls.act != DINO_ACT_SOFTPLUS) { delete p; return fail("dino_plan_create: bad activation"); }
+    if (ls.skip_from >= 0) {
+      // the low-rank residual block of neuralNetworks.py:93-117: in(softplus) -> out(linear) + block input
+      if (ls.skip_from != l - 1 || l < 1 || ls.act != DINO_ACT_LINEAR || p->layers[l - 1].n_in != ls.n_out) {
+        delete p;
+        return fail("dino_plan_create: skip_from must name the previous layer of a two-layer residual block "
+                    "with a linear, width-preserving output");
+      }
+    }
+    lp.koff = poff; poff += r4((long long)lp.n_in * lp.n_out);
+    if (lp.has_bias) { lp.boff = poff; poff += r4(lp.n_out); } else lp.boff = -1;
+    lp.ld_out = r4(lp.n_out);
+    p->layers.push_back(lp);
+    n_in = ls.n_out;
+  }
+  for (int l = 0; l < p->L; ++l)
+    if (p->layers[l].skip_from >= 0) p->layers[p->layers[l].skip_from].lands_skip = l;
+  p->n_params = poff;
+  p->d_out = n_in;
+  if (p->jac_mode == DINO_JAC_NONE) p->s = 0;
+  else if (p->jac_mode == DINO_JAC_FULL) p->s = p->d_out;
+  else p->s = spec->seed_dim;
+  if (p->jac_mode != DINO_JAC_NONE && p->s < 1) { delete p; return fail("dino_plan_create: seed_dim < 1"); }
+  if (p->jac_mode == DINO_JAC_FULL && spec->seed_dim != 0 && spec->seed_dim != p->d_out) {
+    delete p;
+    return fail("dino_plan_create: FULL jacobian needs seed_dim == d_out");
+  }
+  if (p->jac_mode == DINO_JAC_SKETCHED && p->s > 128) { delete p; return fail("dino_plan_create: sketch rank > 128"); }
+  p->seed_shared = (p->jac_mode == DINO_JAC_FULL || p->jac_mode == DINO_JAC_OUT_REDUCED);
+  const LayerPlan& last = p->layers[p->L - 1];
+  p->top_materialised = p->jac_mode != DINO_JAC_NONE &&
+                        (!p->seed_shared || last.act == DINO_ACT_SOFTPLUS || last.skip_from >= 0);
+
+  // ---- workspace layout ------------------------------------------------------------------------
+  const long long Bm = p->max_batch, Ms = Bm * (long long)p->s;
+  long long off = 0;
+  auto take = [&](long long n) { long long o = off; off += r4(n); return o; };
+  p->ld_in = r4(p->d_in);
+  p->ld_ident = r4(p->d_out);
+  p->off_ident = (p->jac_mode == DINO_JAC_FULL) ? take((long long)p->d_out * p->ld_ident) : -1;
+  p->off_z0 = take(Bm * p->ld_in);
+  long long max_w = p->ld_in;
+  for (auto& lp : p->layers) {
+    lp.z_off = take(Bm * lp.ld_out);
+    lp.sg_off = lp.act == DINO_ACT_SOFTPLUS ? take(Bm * lp.ld_out) : -1;
+    if (lp.ld_out > max_w) max_w = lp.ld_out;
+  }
+  p->off_rs_begin = off;
+  for (auto& lp : p->layers)
+    lp.rs_off = (p->jac_mode != DINO_JAC_NONE && lp.act == DINO_ACT_SOFTPLUS) ? take(Bm * lp.ld_out) : -1;
+  p->rs_floats = off - p->off_rs_begin;
+  p->ld_dz = max_w;
+  for (int i = 0; i < 3; ++i) p->off_dz[i] = take(Bm * max_w);
+  p->off_da = take(Bm * max_w);
+  p->off_r0 = p->off_sk = -1;
+  p->ld_dr = 0;
+  for (int i = 0; i < 3; ++i) p->off_dr[i] = -1;
+  for (auto& lp : p->layers) lp.q_off = -1;
+  if (p->jac_mode != DINO_JAC_NONE) {
+    for (int l = 0; l < p->L; ++l) {
+      LayerPlan& lp = p->layers[l];
+      if (l < p->L - 1 || p->top_materialised) lp.q_off = take(Ms * lp.ld_out);
+      if (l < p->L - 1 && lp.ld_out > p->ld_dr) p->ld_dr = lp.ld_out;
+    }
+    p->off_r0 = take(Ms * p->ld_in);
+    if (p->ld_dr > 0)
+      for (int i = 0; i < 3; ++i) p->off_dr[i] = take(Ms * p->ld_dr);
+    if (p->jac_mode == DINO_JAC_SKETCHED) p->off_sk = take(Bm * (long long)p->s * p->s);
+  }
+  p->ws_floats = off;
+  *out = p;
+  return 0;
+}
+
+extern "C" void dino_plan_destroy(DinoPlan* plan) { delete plan; }
+
+extern "C" int64_t dino_plan_param_count(const DinoPlan* plan) { return plan ? plan->n_params : -1; }
+
+extern "C" int dino_plan_layer_offsets(const DinoPlan* plan, int64_t* kernel_off, int64_t* bias_off) {
+  if (!plan || !kernel_off || !bias_off) return fail("dino_plan_layer_offsets: null argument");
+  for (int l = 0; l < plan->L; ++l) {
+    kernel_off[l] = plan->layers[l].koff;
+    bias_off[l] = plan->layers[l].boff;
+  }
+  return 0;
+}
+
+extern "C" size_t dino_plan_workspace_bytes(const DinoPlan* plan) {
+  return plan ? (size_t)plan->ws_floats * sizeof(float) : 0;
+}
+
+extern "C" int dino_plan_bind_workspace(DinoPlan* plan, void* d_ws, size_t bytes, dino_stream_t stream) {
+  if (!plan || !d_ws) return fail("dino_plan_bind_workspace: null argument");
+  if (bytes < (size_t)plan->ws_floats * sizeof(float)) return fail("dino_plan_bind_workspace: workspace too small");
+  if ((reinterpret_cast<uintptr_t>(d_ws) & 255) != 0) return fail("dino_plan_bind_workspace: workspace must be 256-byte aligned");
+  plan->ws = static_cast<float*>(d_ws);
+  if (plan->off_ident >= 0)
+    DINO_LAUNCH(launch_fill_identity(plan->ws + plan->off_ident, plan->d_out, plan->ld_ident, S(stream)));
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+static int check_call(const DinoPlan* p, const float* params, const DinoBatch* b, int B, bool need_targets) {
+  if (!p || !params || !b) return fail("null argument");
+  if (!p->ws) return fail("workspace not bound (dino_plan_bind_workspace)");
+  if (B < 1 || B > p->max_batch) return fail("batch size outside [1, max_batch]");
+  if (!b->m) return fail("batch.m is null");
+  if (p->jac_mode == DINO_JAC_SKETCHED && (!b->U || !b->V)) return fail("sketched Jacobian needs batch.U and batch.V");
+  if (p->jac_mode == DINO_JAC_OUT_REDUCED && !b->seed) return fail("output-reduced Jacobian needs batch.seed (Phi^T)");
+  if (need_targets) {
+    if (!b->q || !b->q_sqnorm) return fail("batch.q / batch.q_sqnorm is null");
+    if (p->jac_mode != DINO_JAC_NONE && (!b->J || !b->J_sqnorm)) return fail("batch.J / batch.J_sqnorm is null");
+  }
+  return 0;
+}
+
+static int gemm(const DinoPlan* p, const GemmOp& op, cudaStream_t st) {
+  DINO_LAUNCH(launch_gemm_simt(op, p->num_sms, st));
+  return 0;
+}
+
+static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b, int B, cudaStream_t st) {
+  float* ws = p->ws;
+  DINO_LAUNCH(launch_gather_rows(b->m, b->idx, B, p->d_in, p->d_in, ws + p->off_z0, p->ld_in, st));
+  const float* zin = ws + p->off_z0;
+  long long ld_zin = p->ld_in;
+  for (int l = 0; l < p->L; ++l) {
+    const LayerPlan& lp = p->layers[l];
+    GemmOp op = gemm_op_zero();
+    op.A = zin; op.a_sm = ld_zin; op.a_sk = 1;
+    op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1;
+    op.M = B; op.N = lp.n_out; op.K = lp.n_in;
+    op.C = ws + lp.z_off; op.ldc = lp.ld_out;
+    op.bias = lp.has_bias ? params + lp.boff : nullptr;
+    op.act = lp.act == DINO_ACT_SOFTPLUS;
+    op.s_out = lp.sg_off >= 0 ? ws + lp.sg_off : nullptr; op.ld_s = lp.ld_out;
+    if (lp.skip_from >= 0) {
+      const int j = lp.skip_from;   // add the INPUT of layer j
+      op.add_post = j == 0 ? ws + p->off_z0 : ws + p->layers[j - 1].z_off;
+      op.ld_apo = j == 0 ? p->ld_in : p->layers[j - 1].ld_out;
+    }
+    if (gemm(p, op, st)) return 1;
+    zin = ws + lp.z_off; ld_zin = lp.ld_out;
+  }
+  return 0;
+}
+
+// Top operand of the chain: Q_{L-1}.  Returns pointer / ld / row-modulus.
+struct TopQ { const float* ptr; long long ld; int mod; };
+
+static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* b, int B, cudaStream_t st, TopQ* top_out) {
+  float* ws = p->ws;
+  const int s = p->s, L = p->L;
+  const int M = B * s;
+  const LayerPlan& last = p->layers[L - 1];
+  TopQ top;
+  const float* seed; long long ld_seed, seed_stride;
+  if (p->jac_mode == DINO_JAC_FULL) { seed = ws + p->off_ident; ld_seed = p->ld_ident; seed_stride = 0; }
+  else if (p->jac_mode == DINO_JAC_OUT_REDUCED) { seed = b->seed; ld_seed = p->d_out; seed_stride = 0; }
+  else { seed = nullptr; ld_seed = 0; seed_stride = 0; }
+  if (p->jac_mode == DINO_JAC_SKETCHED) {
+    // Q_{L-1}[b] = U_b^T (* sg_{L-1})
+    DINO_LAUNCH(launch_transpose_batched(b->U, B, p->d_out, s, ws + last.q_off, last.ld_out, b->idx, st));
+    if (last.act == DINO_ACT_SOFTPLUS)
+      DINO_LAUNCH(launch_scale_seed(ws + last.q_off, (long long)s * last.ld_out, last.ld_out, ws + last.sg_off,
+                                    last.ld_out, B, s, p->d_out, ws + last.q_off, last.ld_out, st));
+    top = {ws + last.q_off, last.ld_out, 0};
+  } else if (p->top_materialised) {
+    DINO_LAUNCH(launch_scale_seed(seed, seed_stride, ld_seed, last.sg_off >= 0 ? ws + last.sg_off : nullptr,
+                                  last.ld_out, B, s, p->d_out, ws + last.q_off, last.ld_out, st));
+    top = {ws + last.q_off, last.ld_out, 0};
+  } else {
+    top = {seed, ld_seed, s};
+  }
+  *top_out = top;
+  for (int l = L - 1; l >= 0; --l) {
+    const LayerPlan& lp = p->layers[l];
+    GemmOp op = gemm_op_zero();
+    if (l == L - 1) { op.A = top.ptr; op.a_sm = top.ld; op.a_mod = top.mod; }
+    else { op.A = ws + lp.q_off; op.a_sm = lp.ld_out; }
+    op.a_sk = 1;
+    op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out;     // W_l^T
+    op.M = M; op.N = lp.n_in; op.K = lp.n_out; op.sdim = s;
+    if (lp.lands_skip >= 0) {
+      const LayerPlan& sk = p->layers[lp.lands_skip];
+      op.add_pre = ws + sk.q_off; op.ld_ap = sk.ld_out;             // Q of the (linear) skip layer = R above it
+    }
+    if (l > 0) {
+      const LayerPlan& below = p->layers[l - 1];
+      if (below.act == DINO_ACT_SOFTPLUS) { op.scale = ws + below.sg_off; op.ld_sc = below.ld_out; }
+      op.C = ws + below.q_off; op.ldc = below.ld_out;
+    } else {
+      op.C = ws + p->off_r0; op.ldc = p->ld_in;
+    }
+    if (gemm(p, op, st)) return 1;
+  }
+  return 0;
+}
+
+static int run_losses(DinoPlan* p, const DinoBatch* b, int B, float w_l2, float w_h1, float inv_gb, bool grads,
+                      float* stats, cudaStream_t st) {
+  float* ws = p->ws;
+  const LayerPlan& last = p->layers[p->L - 1];
+  float* dq = grads ? ws + p->off_dz[p->L % 3] : nullptr;
+  DINO_LAUNCH(launch_loss_q(ws + last.z_off, last.ld_out, b->q, b->q_sqnorm, b->idx, B, p->d_out,
+                            2.f * w_l2 * inv_gb, dq, p->ld_dz, stats, st));
+  if (p->jac_mode == DINO_JAC_NONE) return 0;
+  const float cj = 2.f * w_h1 * inv_gb;
+  if (p->jac_mode == DINO_JAC_SKETCHED) {
+    const int k = p->s;
+    DINO_LAUNCH(launch_sketch_close(ws + p->off_r0, p->ld_in, b->V, b->idx, B, k, p->d_in, ws + p->off_sk, st));
+    DINO_LAUNCH(launch_loss_j(ws + p->off_sk, k, b->J, b->J_sqnorm, b->idx, B, k, k, cj, grads ? 1 : 0, stats, st));
+    if (grads)
+      DINO_LAUNCH(launch_sketch_open(ws + p->off_sk, b->V, b->idx, B, k, p->d_in, ws + p->off_r0, p->ld_in, st));
+  } else {
+    DINO_LAUNCH(launch_loss_j(ws + p->off_r0, p->ld_in, b->J, b->J_sqnorm, b->idx, B, p->s, p->d_in, cj,
+                              grads ? 1 : 0, stats, st));
+  }
+  return 0;
+}
+
+static int run_chain_backward(DinoPlan* p, const float* params, int B, float* grad, const TopQ& top, cudaStream_t st) {
+  float* ws = p->ws;
+  const int s = p->s, L = p->L, M = B * s;
+  // dR_l lives in: l == 0 -> R0 buffer; l >= 1 -> off_dr[(l-1) % 3]
+  auto dr_ptr = [&](int l) { return l == 0 ? ws + p->off_r0 : ws + p->off_dr[(l - 1) % 3]; };
+  auto dr_ld = [&](int l) { return l == 0 ? p->ld_in : p->ld_dr; };
+  for (int l = 0; l < L; ++l) {
+    const LayerPlan& lp = p->layers[l];
+    const float* q; long long ldq; int qmod;
+    if (l == L - 1) { q = top.ptr; ldq = top.ld; qmod = top.mod; }
+    else { q = ws + lp.q_off; ldq = lp.ld_out; qmod = 0; }
+    if (lp.trainable) {     // dW_l += dR_l^T Q_l   (reduction over all B*s chain rows, split-K)
+      GemmOp op = gemm_op_zero();
+      op.A = dr_ptr(l); op.a_sm = 1; op.a_sk = dr_ld(l);
+      op.B = q; op.b_sk = ldq; op.b_sn = 1; op.b_kmod = qmod;
+      op.M = lp.n_in; op.N = lp.n_out; op.K = M;
+      op.C = grad + lp.koff; op.ldc = lp.n_out; op.atomic_c = 1;
+      if (gemm(p, op, st)) return 1;
+    }
+    const bool need_rs = lp.act == DINO_ACT_SOFTPLUS;
+    const bool need_out = l < L - 1;
+    if (!need_rs && !need_out) continue;
+    GemmOp op = gemm_op_zero();
+    op.A = dr_ptr(l); op.a_sm = dr_ld(l); op.a_sk = 1;
+    op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1;      // W_l
+    op.M = M; op.N = lp.n_out; op.K = lp.n_in; op.sdim = s;
+    if (need_rs) {
+      op.yref = q; op.ld_y = ldq;       // softplus top layers are always materialised (qmod == 0)
+      op.rowsum = ws + lp.rs_off; op.ld_rs = lp.ld_out;
+      op.scale = ws + lp.sg_off; op.ld_sc = lp.ld_out;
+    }
+    if (need_out) {
+      op.C = dr_ptr(l + 1); op.ldc = dr_ld(l + 1);
+      if (lp.skip_from >= 0) { op.add_post = dr_ptr(lp.skip_from); op.ld_apo = dr_ld(lp.skip_from); }
+    }
+    if (gemm(p, op, st)) return 1;
+  }
+  return 0;
+}
+
+static int run_mlp_backward(DinoPlan* p, const float* params, int B, float* grad, cudaStream_t st) {
+  float* ws = p->ws;
+  const int L = p->L;
+  auto dz_ptr = [&](int l) { return ws + p->off_dz[l % 3]; };
+  int lowest_trainable = L;
+  for (int l = 0; l < L; ++l)
+    if (p->layers[l].trainable) { lowest_trainable = l; break; }
+  for (int l = L - 1; l >= lowest_trainable; --l) {
+    const LayerPlan& lp = p->layers[l];
+    const float* g = dz_ptr(l + 1);
+    const float* da = g;
+    float* dbias = (lp.trainable && lp.has_bias) ? grad + lp.boff : nullptr;
+    if (lp.act == DINO_ACT_SOFTPLUS) {
+      DINO_LAUNCH(launch_mlp_da(g, p->ld_dz, ws + lp.sg_off, lp.ld_out, lp.rs_off >= 0 ? ws + lp.rs_off : nullptr,
+                                lp.ld_out, B, lp.n_out, ws + p->off_da, p->ld_dz, dbias, st));
+      da = ws + p->off_da;
+    } else if (dbias != nullptr) {
+      DINO_LAUNCH(launch_mlp_da(g, p->ld_dz, nullptr, 0, nullptr, 0, B, lp.n_out, nullptr, 0, dbias, st));
+    }
+    if (lp.trainable) {     // dW_l += z_l^T da_l
+      GemmOp op = gemm_op_zero();
+      op.A = l == 0 ? ws + p->off_z0 : ws + p->layers[l - 1].z_off;
+      op.a_sm = 1; op.a_sk = l == 0 ? p->ld_in : p->layers[l - 1].ld_out;
+      op.B = da; op.b_sk = p->ld_dz; op.b_sn = 1;
+      op.M = lp.n_in; op.N = lp.n_out; op.K = B;
+      op.C = grad + lp.koff; op.ldc = lp.n_out; op.atomic_c = 1;
+      if (gemm(p, op, st)) return 1;
+    }
+    if (l > lowest_trainable) {   // dz_l = da_l W_l^T [+ dz above the residual block that starts here]
+      GemmOp op = gemm_op_zero();
+      op.A = da; op.a_sm = p->ld_dz; op.a_sk = 1;
+      op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out;
+      op.M = B; op.N = lp.n_in; op.K = lp.n_out;
+      op.C = dz_ptr(l); op.ldc = p->ld_dz;
+      if (lp.lands_skip >= 0) { op.add_post = dz_ptr(lp.lands_skip + 1); op.ld_apo = p->ld_dz; }
+      if (gemm(p, op, st)) return 1;
+    }
+  }
+  return 0;
+}
+
+extern "C" int dino_forward(DinoPlan* p, const float* params, const DinoBatch* b, int32_t B, float* q_out,
+                            dino_stream_t stream) {
+  if (!p || !params || !b || !q_out) return fail("dino_forward: null argument");
+  if (!p->ws) return fail("dino_forward: workspace not bound");
+  if (B < 1 || B > p->max_batch) return fail("dino_forward: batch size outside [1, max_batch]");
+  if (!b->m) return fail("dino_forward: batch.m is null");
+  cudaStream_t st = S(stream);
+  if (run_mlp_forward(p, params, b, B, st)) return 1;
+  const LayerPlan& last = p->layers[p->L - 1];
+  DINO_LAUNCH(launch_copy2d(p->ws + last.z_off, last.ld_out, q_out, p->d_out, B, p->d_out, st));
+  return 0;
+}
+
+extern "C" int dino_jacobian(DinoPlan* p, const float* params, const DinoBatch* b, int32_t B, float* q_out,
+                             float* J_out, dino_stream_t stream) {
+  if (!J_out) return fail("dino_jacobian: null output");
+  if (check_call(p, params, b, B, false)) return 1;
+  if (p->jac_mode == DINO_JAC_NONE) return fail("dino_jacobian: plan has no Jacobian output");
+  cudaStream_t st = S(stream);
+  if (run_mlp_forward(p, params, b, B, st)) return 1;
+  TopQ top;
+  if (run_chain_forward(p, params, b, B, st, &top)) return 1;
+  const LayerPlan& last = p->layers[p->L - 1];
+  if (q_out) DINO_LAUNCH(launch_copy2d(p->ws + last.z_off, last.ld_out, q_out, p->d_out, B, p->d_out, st));
+  if (p->jac_mode == DINO_JAC_SKETCHED)
+    DINO_LAUNCH(launch_sketch_close(p->ws + p->off_r0, p->ld_in, b->V, b->idx, B, p->s, p->d_in, J_out, st));
+  else
+    DINO_LAUNCH(launch_copy2d(p->ws + p->off_r0, p->ld_in, J_out, p->d_in, B * p->s, p->d_in, st));
+  return 0;
+}
+
+extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch* b, int32_t B, float w_l2,
+                               float w_h1, float inv_gb, float* grad, float* stats, dino_stream_t stream) {
+  if (!grad || !stats) return fail("dino_h1_fwd_bwd: null output");
+  if (check_call(p, params, b, B, true)) return 1;
+  cudaStream_t st = S(stream);
+  DINO_CUDA(cudaMemsetAsync(grad, 0, (size_t)p->n_params * sizeof(float), st));
+  if (p->rs_floats > 0)
+    DINO_CUDA(cudaMemsetAsync(p->ws + p->off_rs_begin, 0, (size_t)p->rs_floats * sizeof(float), st));
+  if (run_mlp_forward(p, params, b, B, st)) return 1;
+  TopQ top = {nullptr, 0, 0};
+  if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
+  if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st)) return 1;
+  if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, st)) return 1;
+  if (run_mlp_backward(p, params, B, grad, st)) return 1;
+  return 0;
+}
+
+extern "C" int dino_h1_eval(DinoPlan* p, const float* params, const DinoBatch* b, int32_t B, float* stats,
+                            dino_stream_t stream) {
+  if (!stats) return fail("dino_h1_eval: null output");
+  if (check_call(p, params, b, B, true)) return 1;
+  cudaStream_t st = S(stream);
+  if (run_mlp_forward(p, params, b, B, st)) return 1;
+  TopQ top = {nullptr, 0, 0};
+  if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
+  return run_losses(p, b, B, 1.f, 1.f, 1.f, false, stats, st);
+}
+
+extern "C" int dino_adam(float* params, const float* grad, float* m, float* v, int64_t count, float lr, float b1,
+                         float b2, float eps, int64_t t, dino_stream_t stream) {
+  if (!params || !grad || !m || !v) return fail("dino_adam: null argument");
+  if (t < 1) return fail("dino_adam: step t must be >= 1");
+  const double lr_t = (double)lr * sqrt(1.0 - pow((double)b2, (double)t)) / (1.0 - pow((double)b1, (double)t));
+  DINO_LAUNCH(launch_adam(params, grad, m, v, count, (float)lr_t, b1, b2, eps, S(stream)));
+  return 0;
+}
+
+extern "C" int dino_sgd(float* params, const float* grad, int64_t count, float lr, dino_stream_t stream) {
+  if (!params || !grad) return fail("dino_sgd: null argument");
+  DINO_LAUNCH(launch_sgd(params, grad, count, lr, S(stream)));
+  return 0;
+}
+
+extern "C" int dino_sample_sqnorms(const float* x, int64_t n, int64_t len, float* out, dino_stream_t stream) {
+  if (!x || !out) return fail("dino_sample_sqnorms: null argument");
+  DINO_LAUNCH(launch_sqnorms(x, n, len, out, S(stream)));
+  return 0;
+}

@@ -1,0 +1,624 @@
+"""DinoModel: the Keras ``Model`` surface the reference drivers use, backed by the CUDA library.
+
+The reference builds tf.keras functional models (neuralNetworks.py:21-172) and drives them with
+``compile / fit / evaluate / predict`` plus ``layers``, ``get_layer``, ``get_weights`` and
+``set_weights`` (SURVEY.md 8b lists every call site).  This module offers the same duck-typed
+surface.  Host code here only marshals: arrays go to HBM through torch tensors, every
+arithmetic step is a call into libdino_b200.so (include/dino_b200.h).  No CPU compute path exists.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from . import parallel
+
+ACT_NAMES = {None: _lib.ACT_LINEAR, "linear": _lib.ACT_LINEAR, "softplus": _lib.ACT_SOFTPLUS}
+
+
+def _r4(n: int) -> int:
+    return (n + 3) & ~3
+
+
+# --------------------------------------------------------------------------------------------
+# optimisers (the objects trainingUtilities.py:89-94 constructs)
+# --------------------------------------------------------------------------------------------
+class Adam:
+    """Keras Adam: beta_1=0.9, beta_2=0.999, epsilon=1e-7 placed outside the bias correction."""
+
+    def __init__(self, learning_rate=1e-3, beta_1=0.9, beta_2=0.999, epsilon=1e-7):
+        self.learning_rate, self.beta_1, self.beta_2, self.epsilon = learning_rate, beta_1, beta_2, epsilon
+        self.iterations = 0
+        self._m = self._v = None
+
+    kind = "adam"
+
+
+class SGD:
+    def __init__(self, learning_rate=1e-2):
+        self.learning_rate = learning_rate
+        self.iterations = 0
+
+    kind = "sgd"
+
+
+def _as_optimizer(opt):
+    if isinstance(opt, (Adam, SGD)):
+        return opt
+    if isinstance(opt, str):
+        if opt.lower() == "adam":
+            return Adam()
+        if opt.lower() == "sgd":
+            return SGD()
+    raise TypeError(f"unsupported optimizer {opt!r}: use dino_b200.Adam / dino_b200.SGD / 'adam' / 'sgd'")
+
+
+# --------------------------------------------------------------------------------------------
+# Keras-like layer / tensor placeholders
+# --------------------------------------------------------------------------------------------
+@dataclass
+class TensorSpec:
+    shape: tuple          # (None, d) / (None, s, d) : static shapes read at inferenceOracle.py:63-66
+    name: str = ""
+
+
+class DinoLayer:
+    """One entry of ``model.layers``.  Dense layers own a slice of the parameter arena; the input
+    and Add pseudo-layers carry no weights (Keras lists them too, and the reference pickles
+    ``{layer.name: layer.get_weights()}`` over all of them, jacobianTrainingDriver.py:326-328)."""
+
+    def __init__(self, core, name, index=None):
+        self._core, self.name, self._index = core, name, index
+
+    @property
+    def trainable(self):
+        return True if self._index is None else bool(self._core.trainable[self._index])
+
+    @trainable.setter
+    def trainable(self, value):
+        if self._index is not None:
+            self._core.trainable[self._index] = bool(value)
+            self._core.invalidate_plans()
+
+    def get_weights(self) -> List[np.ndarray]:
+        if self._index is None:
+            return []
+        return self._core.layer_weights(self._index)
+
+    def set_weights(self, weights: Sequence[np.ndarray]):
+        if self._index is None:
+            assert len(weights) == 0
+            return
+        self._core.set_layer_weights(self._index, weights)
+
+    def count_params(self):
+        return sum(int(w.size) for w in self.get_weights())
+
+
+class NetCore:
+    """Shared state of a network: layer table, parameter arena (host master copy + device mirror)."""
+
+    def __init__(self, d_in: int, name_prefix: str = ""):
+        self.d_in = int(d_in)
+        self.name_prefix = name_prefix
+        self.names: List[str] = []
+        self.n_in: List[int] = []
+        self.n_out: List[int] = []
+        self.act: List[int] = []
+        self.use_bias: List[bool] = []
+        self.trainable: List[bool] = []
+        self.skip_from: List[int] = []
+        self.keras_layers: List[DinoLayer] = [DinoLayer(self, name_prefix + "input_data")]
+        self.koff: List[int] = []
+        self.boff: List[int] = []
+        self.n_params = 0
+        self.host = np.zeros(0, dtype=np.float32)
+        self._dev = None                 # torch tensor mirror
+        self._dev_newer = False          # device copy has updates the host copy lacks
+        self._plans: Dict[tuple, "_Plan"] = {}
+
+    # ---- construction -------------------------------------------------------------------------
+    def add_dense(self, n_out, name, activation=None, use_bias=True, trainable=True, skip_from=-1,
+                  kernel=None, bias=None):
+        n_in = self.n_out[-1] if self.n_out else self.d_in
+        self.names.append(name)
+        self.n_in.append(int(n_in))
+        self.n_out.append(int(n_out))
+        self.act.append(ACT_NAMES[activation])
+        self.use_bias.append(bool(use_bias))
+        self.trainable.append(bool(trainable))
+        self.skip_from.append(int(skip_from))
+        self.koff.append(self.n_params)
+        self.n_params += _r4(n_in * n_out)
+        if use_bias:
+            self.boff.append(self.n_params)
+            self.n_params += _r4(n_out)
+        else:
+            self.boff.append(-1)
+        self.host = np.concatenate([self.host, np.zeros(self.n_params - self.host.size, dtype=np.float32)])
+        idx = len(self.names) - 1
+        self.keras_layers.append(DinoLayer(self, name, idx))
+        if kernel is not None:
+            self.set_layer_weights(idx, [kernel] if bias is None else [kernel, bias])
+        return idx
+
+    def add_pseudo(self, name):
+        self.keras_layers.append(DinoLayer(self, name))
+
+    @property
+    def d_out(self):
+        return self.n_out[-1]
+
+    @property
+    def n_layers(self):
+        return len(self.names)
+
+    # ---- weights ------------------------------------------------------------------------------
+    def _sync_host(self):
+        if self._dev_newer and self._dev is not None:
+            self.host = self._dev.detach().cpu().numpy().copy()
+            self._dev_newer = False
+
+    def layer_weights(self, l):
+        self._sync_host()
+        k, n = self.n_in[l], self.n_out[l]
+        out = [self.host[self.koff[l]:self.koff[l] + k * n].reshape(k, n).copy()]
+        if self.use_bias[l]:
+            out.append(self.host[self.boff[l]:self.boff[l] + n].copy())
+        return out
+
+    def set_layer_weights(self, l, weights):
+        self._sync_host()
+        k, n = self.n_in[l], self.n_out[l]
+        expect = 2 if self.use_bias[l] else 1
+        if len(weights) != expect:
+            raise ValueError(f"layer {self.names[l]} expects {expect} weight arrays, got {len(weights)}")
+        W = np.asarray(weights[0], dtype=np.float32)
+        if W.shape != (k, n):
+            raise ValueError(f"layer {self.names[l]}: kernel shape {W.shape} != {(k, n)}")
+        self.host[self.koff[l]:self.koff[l] + k * n] = W.reshape(-1)
+        if self.use_bias[l]:
+            b = np.asarray(weights[1], dtype=np.float32)
+            if b.shape != (n,):
+                raise ValueError(f"layer {self.names[l]}: bias shape {b.shape} != {(n,)}")
+            self.host[self.boff[l]:self.boff[l] + n] = b
+        if self._dev is not None:
+            import torch
+            self._dev.copy_(torch.from_numpy(self.host))
+
+    def device_params(self):
+        import torch
+        if self._dev is None:
+            self._dev = torch.from_numpy(self.host).to(_device())
+        return self._dev
+
+    def mark_device_updated(self):
+        self._dev_newer = True
+
+    def invalidate_plans(self):
+        for p in self._plans.values():
+            p.close()
+        self._plans.clear()
+
+
+def _device():
+    import torch
+    if not torch.cuda.is_available():
+        raise _lib.DinoLibraryError("dino_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _stream():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class _Plan:
+    """A DinoPlan handle plus its workspace tensor."""
+
+    def __init__(self, core: NetCore, jac_mode: int, seed_dim: int, max_batch: int, precision: int):
+        import torch
+        lib = _lib.load()
+        L = core.n_layers
+        arr = (_lib.DinoLayerSpec * L)()
+        for l in range(L):
+            arr[l] = _lib.DinoLayerSpec(core.n_out[l], core.act[l], int(core.use_bias[l]), int(core.trainable[l]),
+                                        core.skip_from[l])
+        spec = _lib.DinoNetSpec(core.d_in, L, arr, jac_mode, seed_dim, max_batch, precision)
+        handle = C.c_void_p()
+        dev = _device()
+        _lib.check(lib.dino_plan_create(C.byref(spec), dev.index, C.byref(handle)), "dino_plan_create")
+        self.handle = handle
+        self.lib = lib
+        if lib.dino_plan_param_count(handle) != core.n_params:
+            raise _lib.DinoLibraryError("parameter arena layout mismatch between host and library")
+        ko, bo = (C.c_int64 * L)(), (C.c_int64 * L)()
+        _lib.check(lib.dino_plan_layer_offsets(handle, ko, bo), "dino_plan_layer_offsets")
+        if list(ko) != core.koff or list(bo) != core.boff:
+            raise _lib.DinoLibraryError("parameter arena offsets mismatch between host and library")
+        nbytes = lib.dino_plan_workspace_bytes(handle)
+        self.workspace = torch.empty(max(nbytes, 256) // 4 + 64, dtype=torch.float32, device=dev)
+        _lib.check(lib.dino_plan_bind_workspace(handle, C.c_void_p(self.workspace.data_ptr()),
+                                                C.c_size_t(self.workspace.numel() * 4), _stream()),
+                   "dino_plan_bind_workspace")
+        self.max_batch = max_batch
+
+    def close(self):
+        if self.handle is not None:
+            self.lib.dino_plan_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DeviceDataset:
+    """(m, q, J[, U, V]) of one fit/evaluate call, resident in HBM as fp32 (numpy fp64 sources are
+    cast on upload, exactly as Keras casts to floatx on feed)."""
+
+    def __init__(self, jac_mode: int, x: Sequence[np.ndarray], y: Optional[Sequence[np.ndarray]], seed=None):
+        import torch
+        lib = _lib.load()
+        dev = _device()
+
+        def up(a):
+            a = np.asarray(a)
+            if a.dtype != np.float32:
+                a = a.astype(np.float32)
+            return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+        self.m = up(x[0])
+        self.n = int(self.m.shape[0])
+        self.U = self.V = self.q = self.J = self.qn2 = self.jn2 = None
+        self.seed = None if seed is None else up(seed)
+        if jac_mode == _lib.JAC_SKETCHED:
+            if len(x) != 3:
+                raise ValueError("sketched-Jacobian models take inputs [m, U, V]")
+            self.U, self.V = up(x[1]), up(x[2])
+        elif len(x) != 1:
+            raise ValueError("this model takes one input array [m]")
+        if y is not None:
+            self.q = up(y[0])
+            self.qn2 = torch.empty(self.n, dtype=torch.float32, device=dev)
+            _lib.check(lib.dino_sample_sqnorms(C.c_void_p(self.q.data_ptr()), self.n, self.q[0].numel(),
+                                               C.c_void_p(self.qn2.data_ptr()), _stream()), "dino_sample_sqnorms")
+            if jac_mode != _lib.JAC_NONE:
+                self.J = up(y[1])
+                self.jn2 = torch.empty(self.n, dtype=torch.float32, device=dev)
+                _lib.check(lib.dino_sample_sqnorms(C.c_void_p(self.J.data_ptr()), self.n, self.J[0].numel(),
+                                                   C.c_void_p(self.jn2.data_ptr()), _stream()), "dino_sample_sqnorms")
+
+    def batch(self, idx_ptr: Optional[int], row_offset: int = 0) -> _lib.DinoBatch:
+        """DinoBatch for rows addressed by a device int32 index array (idx_ptr) or, when idx_ptr is
+        None, the contiguous rows starting at row_offset."""
+        def p(t, per_row=None):
+            if t is None:
+                return None
+            if idx_ptr is None and row_offset:
+                return t.data_ptr() + row_offset * t[0].numel() * 4 if t.dim() > 1 else t.data_ptr() + row_offset * 4
+            return t.data_ptr()
+        return _lib.DinoBatch(p(self.m), p(self.q), p(self.J), p(self.qn2), p(self.jn2), idx_ptr,
+                              p(self.U), p(self.V), None if self.seed is None else self.seed.data_ptr())
+
+
+class History:
+    def __init__(self):
+        self.history: Dict[str, List[float]] = {}
+        self.epoch: List[int] = []
+
+    def _append(self, epoch, logs):
+        self.epoch.append(epoch)
+        for k, v in logs.items():
+            self.history.setdefault(k, []).append(v)
+
+
+def _combine_stats(stats: np.ndarray, weights, jac: bool):
+    """Keras aggregation (TF-knowledge): every reported value is the batch-size-weighted mean of
+    the per-batch values.  stats: [n_batches, STAT_SLOTS] per-batch sums from the loss kernels."""
+    s = stats.astype(np.float64)
+    cnt = s[:, _lib.STAT_COUNT]
+    keep = cnt > 0
+    s, cnt = s[keep], cnt[keep]
+    wts = cnt / cnt.sum()
+    l2 = s[:, _lib.STAT_L2_SUM] / cnt
+    out_q = [l2, 1.0 - np.sqrt(l2), 1.0 - np.sqrt(s[:, _lib.STAT_EQ_SUM] / s[:, _lib.STAT_NQ_SUM])]
+    if not jac:
+        loss = weights[0] * l2
+        vals = [loss, out_q[1]]
+        return [float((v * wts).sum()) for v in vals]
+    h1 = s[:, _lib.STAT_H1_SUM] / cnt
+    loss = weights[0] * l2 + weights[1] * h1
+    vals = [loss, l2, h1, out_q[1], out_q[2], 1.0 - np.sqrt(s[:, _lib.STAT_JROW_SUM] / s[:, _lib.STAT_JROWS]),
+            1.0 - np.sqrt(h1)]
+    return [float((v * wts).sum()) for v in vals]
+
+
+_LOSS_NAMES = {"normalized_mse", "normalized_mse_matrix"}
+
+
+class DinoModel:
+    """Duck-typed ``tf.keras.Model`` with one input (or [m, U, V]) and one or two outputs."""
+
+    def __init__(self, core: NetCore, jac_mode: str = "none", seed_dim: int = 0, output_basis=None,
+                 precision: Optional[str] = None):
+        self.core = core
+        self.jac_mode_name = jac_mode
+        self.jac_mode = _lib.JAC_MODES[jac_mode]
+        self.seed_dim = {"none": 0, "full": core.d_out}.get(jac_mode, seed_dim)
+        # Phi [d_Q, r_out] of equip_model_with_output_reduced_jacobian; the chain is seeded with Phi^T
+        self.output_basis = None if output_basis is None else np.asarray(output_basis, dtype=np.float32)
+        self.precision = precision or os.environ.get("DINO_B200_PRECISION", "fp32")
+        self.optimizer = None
+        self.loss_weights = [1.0, 1.0]
+        self._compiled = False
+        p = core.name_prefix
+        self.inputs = [TensorSpec((None, core.d_in), p + "input_data")]
+        self.outputs = [TensorSpec((None, core.d_out), core.names[-1])]
+        if jac_mode == "sketched":
+            self.inputs += [TensorSpec((None, core.d_out, seed_dim), p + "_input_U"),
+                            TensorSpec((None, core.d_in, seed_dim), p + "_input_V")]
+            self.outputs.append(TensorSpec((None, seed_dim, seed_dim), p + "reduced_jacobian"))
+        elif jac_mode != "none":
+            self.outputs.append(TensorSpec((None, self.seed_dim, core.d_in), p + "jacobian"))
+        self.stop_training = False
+
+    # ---- Keras structural surface ----------------------------------------------------------------
+    @property
+    def layers(self):
+        return self.core.keras_layers
+
+    def get_layer(self, name=None, index=None):
+        if index is not None:
+            return self.core.keras_layers[index]
+        for layer in self.core.keras_layers:
+            if layer.name == name:
+                return layer
+        raise ValueError(f"No such layer: {name}.")
+
+    @property
+    def input(self):
+        return self.inputs[0] if len(self.inputs) == 1 else self.inputs
+
+    @property
+    def output(self):
+        return self.outputs[0] if len(self.outputs) == 1 else self.outputs
+
+    @property
+    def input_shape(self):
+        return self.inputs[0].shape
+
+    @property
+    def output_shape(self):
+        return self.outputs[0].shape if len(self.outputs) == 1 else [o.shape for o in self.outputs]
+
+    def get_weights(self):
+        out = []
+        for layer in self.layers:
+            out += layer.get_weights()
+        return out
+
+    def set_weights(self, weights):
+        i = 0
+        for layer in self.layers:
+            n = len(layer.get_weights())
+            layer.set_weights(weights[i:i + n])
+            i += n
+
+    def count_params(self):
+        return sum(layer.count_params() for layer in self.layers)
+
+    def summary(self, print_fn=print):
+        lines = [f"Model: dino_b200 ({self.jac_mode_name} Jacobian output)" if self.jac_mode else "Model: dino_b200",
+                 "_" * 65, f"{'Layer':<40}{'Output Shape':<15}{'Param #':>10}", "=" * 65]
+        c = self.core
+        lines.append(f"{c.keras_layers[0].name:<40}{str((None, c.d_in)):<15}{0:>10}")
+        for layer in c.keras_layers[1:]:
+            shape = (None, c.n_out[layer._index]) if layer._index is not None else ""
+            lines.append(f"{layer.name:<40}{str(shape):<15}{layer.count_params():>10}")
+        total = self.count_params()
+        train = sum(l.count_params() for l in c.keras_layers if l._index is not None and l.trainable)
+        lines += ["=" * 65, f"Total params: {total}", f"Trainable params: {train}",
+                  f"Non-trainable params: {total - train}"]
+        for ln in lines:
+            print_fn(ln)
+
+    # ---- compile / metrics -------------------------------------------------------------------------
+    def compile(self, optimizer="adam", loss=None, loss_weights=None, metrics=None, **_ignored):
+        losses = loss if isinstance(loss, (list, tuple)) else [loss]
+        for f in losses:
+            name = f if isinstance(f, str) else getattr(f, "__name__", None)
+            if name not in _LOSS_NAMES:
+                raise NotImplementedError(f"loss {name!r}: only normalized_mse / normalized_mse_matrix "
+                                          "(trainingUtilities.py:25-37) exist as kernels")
+        if len(losses) != len(self.outputs):
+            raise ValueError(f"{len(losses)} losses for {len(self.outputs)} model outputs")
+        self.optimizer = _as_optimizer(optimizer)
+        if loss_weights is None:
+            loss_weights = [1.0] * len(self.outputs)
+        self.loss_weights = [float(w) for w in loss_weights] + [0.0] * (2 - len(loss_weights))
+        self._compiled = True
+
+    @property
+    def metrics_names(self):
+        o = [t.name for t in self.outputs]
+        if len(o) == 1:
+            return ["loss", "l2_accuracy"]
+        return ["loss", o[0] + "_loss", o[1] + "_loss", o[0] + "_l2_accuracy", o[0] + "_f_accuracy_matrix",
+                o[1] + "_l2_accuracy", o[1] + "_f_accuracy_matrix"]
+
+    # ---- device plumbing ---------------------------------------------------------------------------
+    def _plan(self, max_batch: int) -> _Plan:
+        key = (self.jac_mode, self.seed_dim, _lib.PRECISIONS[self.precision])
+        plan = self.core._plans.get(key)
+        if plan is None or plan.max_batch < max_batch:
+            if plan is not None:
+                plan.close()
+            plan = _Plan(self.core, self.jac_mode, self.seed_dim, max_batch, _lib.PRECISIONS[self.precision])
+            self.core._plans[key] = plan
+        return plan
+
+    def _dataset(self, x, y):
+        x = list(x) if isinstance(x, (list, tuple)) else [x]
+        if y is not None:
+            y = list(y) if isinstance(y, (list, tuple)) else [y]
+            if len(y) != len(self.outputs):
+                raise ValueError(f"{len(y)} target arrays for {len(self.outputs)} model outputs")
+        seed = None if self.output_basis is None else np.ascontiguousarray(self.output_basis.T)
+        return DeviceDataset(self.jac_mode, x, y, seed)
+
+    # ---- evaluate / predict ------------------------------------------------------------------------
+    def evaluate(self, x, y, verbose=0, batch_size=32, **_ignored):
+        import torch
+        ds = x if isinstance(x, DeviceDataset) else self._dataset(x, y)
+        stats = self._eval_stats(ds, batch_size)
+        vals = _combine_stats(stats, self.loss_weights, self.jac_mode != _lib.JAC_NONE)
+        if verbose:
+            print(" - ".join(f"{k}: {v:.4e}" for k, v in zip(self.metrics_names, vals)))
+        return vals
+
+    def _eval_stats(self, ds: DeviceDataset, batch_size: int) -> np.ndarray:
+        import torch
+        lib = _lib.load()
+        plan = self._plan(min(batch_size, ds.n))
+        params = self.core.device_params()
+        nb = (ds.n + batch_size - 1) // batch_size
+        stats = torch.zeros(nb, _lib.STAT_SLOTS, dtype=torch.float32, device=params.device)
+        st = _stream()
+        for i in range(nb):
+            lo = i * batch_size
+            B = min(batch_size, ds.n - lo)
+            batch = ds.batch(None, lo)
+            _lib.check(lib.dino_h1_eval(plan.handle, C.c_void_p(params.data_ptr()), C.byref(batch), B,
+                                        C.c_void_p(stats[i].data_ptr()), st), "dino_h1_eval")
+        return stats.cpu().numpy()
+
+    def predict(self, x, batch_size=32, **_ignored):
+        import torch
+        lib = _lib.load()
+        ds = self._dataset(x, None)
+        plan = self._plan(min(batch_size, ds.n))
+        params = self.core.device_params()
+        q = torch.empty(ds.n, self.core.d_out, dtype=torch.float32, device=params.device)
+        J = None
+        if self.jac_mode != _lib.JAC_NONE:
+            J = torch.empty((ds.n,) + tuple(self.outputs[1].shape[1:]), dtype=torch.float32, device=params.device)
+        st = _stream()
+        for lo in range(0, ds.n, batch_size):
+            B = min(batch_size, ds.n - lo)
+            batch = ds.batch(None, lo)
+            if J is None:
+                _lib.check(lib.dino_forward(plan.handle, C.c_void_p(params.data_ptr()), C.byref(batch), B,
+                                            C.c_void_p(q[lo].data_ptr()), st), "dino_forward")
+            else:
+                _lib.check(lib.dino_jacobian(plan.handle, C.c_void_p(params.data_ptr()), C.byref(batch), B,
+                                             C.c_void_p(q[lo].data_ptr()), C.c_void_p(J[lo].data_ptr()), st),
+                           "dino_jacobian")
+        if J is None:
+            return q.cpu().numpy()
+        return [q.cpu().numpy(), J.cpu().numpy()]
+
+    # ---- fit -----------------------------------------------------------------------------------------
+    def fit(self, x, y, validation_data=None, epochs=1, batch_size=32, verbose=0, callbacks=None,
+            shuffle=True, initial_epoch=0, perms=None, **_ignored):
+        """Keras ``fit`` semantics (trainingUtilities.py:135-138): per epoch a permutation drawn
+        from numpy's global RNG (``perms[e]`` overrides it), minibatches of ``batch_size`` in that
+        order, a short last batch averaged over its own size, validation after every epoch.
+        With torch.distributed initialised every global minibatch is split contiguously over the
+        ranks and the flat gradient is sum-all-reduced before the (replicated) optimiser step."""
+        import torch
+        if not self._compiled:
+            raise RuntimeError("You must compile your model before training/testing.")
+        lib = _lib.load()
+        ds = x if isinstance(x, DeviceDataset) else self._dataset(x, y)
+        val = None
+        if validation_data is not None:
+            val = self._dataset(validation_data[0], validation_data[1])
+        dp = parallel.context()
+        n, P = ds.n, self.core.n_params
+        params = self.core.device_params()
+        dev = params.device
+        local_max = -(-min(batch_size, n) // dp.world)
+        plan = self._plan(max(local_max, 1))
+        opt = self.optimizer
+        if opt.kind == "adam" and (opt._m is None or opt._m.numel() != P):
+            opt._m = torch.zeros(P, dtype=torch.float32, device=dev)
+            opt._v = torch.zeros(P, dtype=torch.float32, device=dev)
+        grad = torch.zeros(P, dtype=torch.float32, device=dev)
+        steps = (n + batch_size - 1) // batch_size
+        hist = History()
+        names = self.metrics_names
+        jac = self.jac_mode != _lib.JAC_NONE
+        w0, w1 = self.loss_weights[0], self.loss_weights[1]
+        callbacks = callbacks or []
+        for cb in callbacks:
+            if hasattr(cb, "set_model"):
+                cb.set_model(self)
+            if hasattr(cb, "on_train_begin"):
+                cb.on_train_begin({})
+        st = _stream()
+        for epoch in range(initial_epoch, epochs):
+            if perms is not None:
+                order = np.asarray(perms[epoch - initial_epoch])
+            elif shuffle:
+                order = np.random.permutation(n)
+            else:
+                order = np.arange(n)
+            if dp.world > 1:
+                order = dp.broadcast_order(order)
+            idx = torch.from_numpy(np.ascontiguousarray(order, dtype=np.int32)).to(dev)
+            stats = torch.zeros(steps, _lib.STAT_SLOTS, dtype=torch.float32, device=dev)
+            for cb in callbacks:
+                if hasattr(cb, "on_epoch_begin"):
+                    cb.on_epoch_begin(epoch, {})
+            for step in range(steps):
+                lo = step * batch_size
+                Bg = min(batch_size, n - lo)
+                off, Bl = parallel.shard_bounds(Bg, dp.rank, dp.world)
+                if Bl > 0:
+                    batch = ds.batch(idx.data_ptr() + 4 * (lo + off))
+                    _lib.check(lib.dino_h1_fwd_bwd(plan.handle, C.c_void_p(params.data_ptr()), C.byref(batch), Bl,
+                                                   w0, w1, 1.0 / Bg, C.c_void_p(grad.data_ptr()),
+                                                   C.c_void_p(stats[step].data_ptr()), st), "dino_h1_fwd_bwd")
+                else:
+                    grad.zero_()
+                if dp.world > 1:
+                    dp.all_reduce_sum(grad)
+                opt.iterations += 1
+                if opt.kind == "adam":
+                    _lib.check(lib.dino_adam(C.c_void_p(params.data_ptr()), C.c_void_p(grad.data_ptr()),
+                                             C.c_void_p(opt._m.data_ptr()), C.c_void_p(opt._v.data_ptr()), P,
+                                             opt.learning_rate, opt.beta_1, opt.beta_2, opt.epsilon,
+                                             opt.iterations, st), "dino_adam")
+                else:
+                    _lib.check(lib.dino_sgd(C.c_void_p(params.data_ptr()), C.c_void_p(grad.data_ptr()), P,
+                                            opt.learning_rate, st), "dino_sgd")
+            self.core.mark_device_updated()
+            if dp.world > 1:
+                dp.all_reduce_sum(stats)
+            vals = _combine_stats(stats.cpu().numpy(), self.loss_weights, jac)
+            logs = dict(zip(names, vals))
+            if val is not None:
+                vv = _combine_stats(self._eval_stats(val, batch_size), self.loss_weights, jac)
+                logs.update({"val_" + k: v for k, v in zip(names, vv)})
+            hist._append(epoch, logs)
+            if verbose and dp.rank == 0:
+                print(f"Epoch {epoch + 1}/{epochs} - " + " - ".join(f"{k}: {v:.4e}" for k, v in logs.items()))
+            for cb in callbacks:
+                if hasattr(cb, "on_epoch_end"):
+                    cb.on_epoch_end(epoch, logs)
+            if self.stop_training:
+                break
+        for cb in callbacks:
+            if hasattr(cb, "on_train_end"):
+                cb.on_train_end({})
+        self.history = hist
+        return hist

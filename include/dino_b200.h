@@ -1,0 +1,144 @@
+/* dino_b200 - C ABI of the B200-native DINO derivative-informed (H1) training step.
+ *
+ * The reference (tomoleary/dino) has no FFI layer: its hot path is TensorFlow 2.7 executing the
+ * Keras graph that dino/construction builds.  Each entry point below replaces one piece of that
+ * graph execution and cites the reference call site it stands in for.  The Python host layer
+ * (dino_b200/model.py, a duck-typed Keras Model) binds these with ctypes; see INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain C: pointers, sizes, no torch / C++ types.  Every pointer named d_* / listed as
+ *     "device" is a CUDA device pointer owned by the caller.  The library never allocates or
+ *     frees device memory: the caller supplies one workspace (dino_plan_workspace_bytes).
+ *   - all tensors fp32, row-major, dense.  Kernels are launched on `stream` (a cudaStream_t
+ *     passed as void*), asynchronously; no entry point synchronises the host.
+ *   - return 0 on success, non-zero on error; dino_last_error() gives a thread-local message.
+ *   - a plan is not thread-safe; use one plan per (device, network, host thread).
+ *   - built for sm_100a only; there is no CPU or other-architecture fallback.
+ */
+#ifndef DINO_B200_H
+#define DINO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct DinoPlan DinoPlan;
+typedef void* dino_stream_t; /* cudaStream_t */
+
+enum { DINO_ACT_LINEAR = 0, DINO_ACT_SOFTPLUS = 1 };
+/* which second model output the network is equipped with (jacobianConstruction.py:102,128,155) */
+enum { DINO_JAC_NONE = 0, DINO_JAC_FULL = 1, DINO_JAC_OUT_REDUCED = 2, DINO_JAC_SKETCHED = 3 };
+/* arithmetic of the Jacobian-chain contractions */
+enum { DINO_PREC_FP32 = 0, DINO_PREC_TF32 = 1 };
+
+/* One Keras Dense layer: y = act(x W + b) [+ input of layer skip_from]; W is [n_in, n_out]
+ * (Keras kernel layout).  Mirrors tf.keras.layers.Dense as used at neuralNetworks.py:34-61,
+ * 83-87 and the low-rank residual block of neuralNetworks.py:93-117,158-160 (skip_from). */
+typedef struct {
+  int32_t n_out;
+  int32_t act;       /* DINO_ACT_* */
+  int32_t has_bias;  /* 0/1 */
+  int32_t trainable; /* 0/1 : frozen layers get no gradient (neuralNetworks.py:66-71) */
+  int32_t skip_from; /* -1, or index j<=this of the layer whose INPUT is added to this output */
+} DinoLayerSpec;
+
+typedef struct {
+  int32_t d_in;      /* network input width (d_M, or r_in when trained in reduced coordinates) */
+  int32_t n_layers;
+  const DinoLayerSpec* layers;
+  int32_t jac_mode;  /* DINO_JAC_* */
+  int32_t seed_dim;  /* rows of the Jacobian output: d_out (FULL), r_out (OUT_REDUCED), k (SKETCHED) */
+  int32_t max_batch; /* largest minibatch the workspace is sized for */
+  int32_t precision; /* DINO_PREC_* */
+} DinoNetSpec;
+
+/* One minibatch, addressed inside device-resident datasets.  Sample b of the batch is dataset
+ * row idx[b] (idx == NULL: rows 0..B-1).  Mirrors the feed of Keras fit/evaluate
+ * (trainingUtilities.py:105-122): inputs [m] or [m,U,V]; targets [q, J] or [q, diag(sigma)]. */
+typedef struct {
+  const float* m;    /* [n, d_in] */
+  const float* q;    /* [n, d_out] */
+  const float* J;    /* [n, seed_dim, d_in]  (SKETCHED: [n, k, k]); NULL when jac_mode NONE */
+  const float* q_sqnorm; /* [n] sum_j q^2      (dino_sample_sqnorms) */
+  const float* J_sqnorm; /* [n] ||J||_F^2      (dino_sample_sqnorms) */
+  const int32_t* idx;    /* [B] or NULL */
+  const float* U;    /* SKETCHED: [n, d_out, k] (jacobianConstruction.py:115) else NULL */
+  const float* V;    /* SKETCHED: [n, d_in, k]  (jacobianConstruction.py:116) else NULL */
+  const float* seed; /* OUT_REDUCED: Phi^T [seed_dim, d_out] (jacobianConstruction.py:181) else NULL */
+} DinoBatch;
+
+/* statistics a step accumulates (+=) into the caller's float[DINO_STAT_SLOTS] device array;
+ * Keras' loss and the four metrics of trainingUtilities.py:25-51 derive from them:
+ *   l2 loss = L2_SUM/COUNT, h1 loss = H1_SUM/COUNT,
+ *   l2_accuracy(q) = 1-sqrt(L2_SUM/COUNT), f_accuracy_matrix(q) = 1-sqrt(EQ_SUM/NQ_SUM),
+ *   l2_accuracy(J) = 1-sqrt(JROW_SUM/JROWS), f_accuracy_matrix(J) = 1-sqrt(H1_SUM/COUNT) */
+enum { DINO_STAT_L2_SUM = 0, DINO_STAT_H1_SUM = 1, DINO_STAT_EQ_SUM = 2, DINO_STAT_NQ_SUM = 3,
+       DINO_STAT_JROW_SUM = 4, DINO_STAT_COUNT = 5, DINO_STAT_JROWS = 6, DINO_STAT_SLOTS = 8 };
+
+/* Build the execution plan of a network.  Replaces the Keras functional-graph construction of
+ * projected_dense / generic_dense / projected_resnet (neuralNetworks.py:21,77,122) plus
+ * equip_model_with_{full,output_reduced,sketched}_jacobian (jacobianConstruction.py:102-185). */
+int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** out);
+void dino_plan_destroy(DinoPlan* plan);
+
+/* Flat parameter arena: layers in graph order, kernel [n_in,n_out] row-major then bias [n_out],
+ * each block padded to a multiple of 4 floats.  This is the order of layer.get_weights()
+ * (jacobianTrainingDriver.py:327-328).  bias_off[l] = -1 for use_bias=False layers. */
+int64_t dino_plan_param_count(const DinoPlan* plan);
+int dino_plan_layer_offsets(const DinoPlan* plan, int64_t* kernel_off, int64_t* bias_off);
+
+/* Workspace (activations, chain intermediates, split-K partials): size query, then bind. */
+size_t dino_plan_workspace_bytes(const DinoPlan* plan);
+int dino_plan_bind_workspace(DinoPlan* plan, void* d_workspace, size_t bytes, dino_stream_t stream);
+
+/* q_hat = net(m): Model.predict (inferenceOracle.py:114) / first model output. d_q_out [B,d_out]. */
+int dino_forward(DinoPlan* plan, const float* d_params, const DinoBatch* batch, int32_t B,
+                 float* d_q_out, dino_stream_t stream);
+
+/* Second model output: J_hat [B,seed_dim,d_in] (FULL: tape.batch_jacobian, jacobianConstruction.py
+ * :145-149; OUT_REDUCED: Phi^T J_hat, :181) or U^T J_hat V [B,k,k] (SKETCHED, :119-123).
+ * Also the array form of InferenceOracle.J (inferenceOracle.py:127-139). d_q_out may be NULL. */
+int dino_jacobian(DinoPlan* plan, const float* d_params, const DinoBatch* batch, int32_t B,
+                  float* d_q_out, float* d_J_out, dino_stream_t stream);
+
+/* One training step minus the optimiser: forward, Jacobian, w_l2*normalized_mse +
+ * w_h1*normalized_mse_matrix, and d loss / d theta by the double backward.  Replaces what
+ * session.run(train_op) computes inside network.fit (trainingUtilities.py:135-138).
+ * Losses are scaled by inv_global_batch (= 1/B on one GPU; 1/B_global when the batch is sharded
+ * over ranks so that a SUM all-reduce of d_grad gives the global-mean gradient).
+ * d_grad [param_count] is overwritten; d_stats [DINO_STAT_SLOTS] is accumulated into. */
+int dino_h1_fwd_bwd(DinoPlan* plan, const float* d_params, const DinoBatch* batch, int32_t B,
+                    float w_l2, float w_h1, float inv_global_batch, float* d_grad, float* d_stats,
+                    dino_stream_t stream);
+
+/* Forward + losses/metrics only: one batch of Model.evaluate (trainingUtilities.py:125,169). */
+int dino_h1_eval(DinoPlan* plan, const float* d_params, const DinoBatch* batch, int32_t B,
+                 float* d_stats, dino_stream_t stream);
+
+/* Keras Adam (trainingUtilities.py:90; TF ResourceApplyAdam): with t the 1-based step,
+ * lr_t = lr*sqrt(1-b2^t)/(1-b1^t) is computed on the host in double precision;
+ * m = b1 m+(1-b1) g; v = b2 v+(1-b2) g^2; p -= lr_t m/(sqrt(v)+eps).  Frozen parameters have
+ * g == 0 and m == v == 0 and therefore do not move. */
+int dino_adam(float* d_params, const float* d_grad, float* d_m, float* d_v, int64_t count,
+              float lr, float beta1, float beta2, float eps, int64_t t, dino_stream_t stream);
+/* Keras SGD (trainingUtilities.py:92): p -= lr g. */
+int dino_sgd(float* d_params, const float* d_grad, int64_t count, float lr, dino_stream_t stream);
+
+/* out[i] = sum_j x[i, j]^2 over n rows of length len: the denominators of
+ * normalized_mse / normalized_mse_matrix (trainingUtilities.py:28,36), computed once per
+ * dataset because the targets do not change during fit. */
+int dino_sample_sqnorms(const float* d_x, int64_t n, int64_t len, float* d_out, dino_stream_t stream);
+
+/* number of kernels this library has launched in the calling process (bench.py gpu_launches) */
+int64_t dino_launch_count(void);
+
+const char* dino_last_error(void);
+const char* dino_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DINO_B200_H */
