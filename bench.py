@@ -1,0 +1,306 @@
+#!/usr/bin/env python
+"""bench.py - DINO H1 training-step throughput (BASELINE.json metric) on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config cfg2]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one optimiser step (forward + per-sample Jacobian + L2/H1 loss + double backward +
+[gradient all-reduce] + Adam) on one global minibatch of synthetic teacher data.  Workload at any
+N: BASELINE.json configs[1] (confusion-shaped rb_dense, r_in=100, d_Q=50, reduced-input training,
+frozen output layer), per-GPU minibatch 256 (weak scaling: global batch 256*N).
+
+Prints ONE JSON line (rank 0).  `value` = samples/s with the dataset resident in HBM, CUDA-event
+timed, max over ranks.  `e2e` = the same step through DinoModel.train_on_batch with HOST (pinned)
+minibatches: H2D copy of (m, q, J) and the D2H read of the loss inside the timed region.
+`--impl reference` times the reference's CPU path (TensorFlow is not installable here, so the
+oracle restatement in fp32 on all host cores, labelled kind="port").
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "DINO train samples/s (fwd+Jacobian loss+bwd)"
+UNIT = "samples/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="cfg2")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU minibatch (default: the config's)")
+    ap.add_argument("--n", type=int, default=16384, help="synthetic samples resident per GPU")
+    ap.add_argument("--precision", default=os.environ.get("DINO_B200_PRECISION", "fp32"))
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm=d["hbm_gbs"], tensor=d["bf16_tflops_sustained"], src="measured (MEASURED_PEAKS.json, bf16 sustained)")
+    return dict(hbm=6650.0, tensor=1400.0, src="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed regions run."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.idx = [], None, gpu_index
+        self.t0 = self.t1 = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+
+    def summary(self):
+        rows = [r for t, r in self.rows if self.t0 is not None and self.t0 - 0.05 <= t <= (self.t1 or 1e30) + 0.25]
+        if not rows:
+            rows = [r for _, r in self.rows]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm = sorted(float(r[1]) for r in rows)
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            for nm, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][2]), "reasons": sorted(reasons),
+                "samples": len(rows), "power_w_max": max(float(r[3]) for r in rows)}
+
+
+def cpu_reference_rate(arch, data, weights, batch, seconds, max_steps=None, threads=None):
+    """The reference's CPU training step restated in torch fp32 (oracle/dino_oracle.py: d_out reverse
+    passes vectorised like TF's pfor, autograd double backward, Keras Adam).  Returns samples/s."""
+    import torch
+    import helpers as H
+    from oracle import dino_oracle as O
+    if threads:
+        torch.set_num_threads(threads)
+    net = H.oracle_net(arch, weights, dtype=torch.float32)
+    opt = O.KerasAdam(net.trainable_tensors(), 1e-3)
+    n = data["m"].shape[0]
+    full = H.oracle_batch(data, None, dtype=torch.float32)
+
+    def one(i):
+        idx = (np.arange(batch) + i * batch) % n
+        _, grads = O.h1_step_grads(net, O.slice_batch(full, idx), (1.0, 1.0), vectorised=True)
+        opt.step(grads)
+
+    one(0)                                     # warm-up (allocator, thread pool)
+    t0, steps = time.perf_counter(), 0
+    while True:
+        one(steps + 1)
+        steps += 1
+        el = time.perf_counter() - t0
+        if el >= seconds or (max_steps and steps >= max_steps):
+            break
+    return steps * batch / el, steps, el, torch.get_num_threads()
+
+
+def run_reference(args, arch, batch):
+    """--impl reference: the CPU path on this box's host cores, same config/metric/unit."""
+    import warnings
+    warnings.filterwarnings("ignore")
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from dino_b200 import synthetic as S
+    import helpers as H
+    n = max(4 * batch, 1024)
+    data, tw = S.make_dataset(arch, n, 1234 + 1)
+    w = H.student_weights(arch, 1234 + 2, tw)
+    import torch
+    from oracle import dino_oracle as O
+    net = H.oracle_net(arch, w, dtype=torch.float32)
+    opt = O.KerasAdam(net.trainable_tensors(), 1e-3)
+    full = H.oracle_batch(data, None, dtype=torch.float32)
+
+    def one(i):
+        idx = (np.arange(batch) + i * batch) % n
+        _, grads = O.h1_step_grads(net, O.slice_batch(full, idx), (1.0, 1.0), vectorised=True)
+        opt.step(grads)
+
+    # bound the run to a few minutes: cap the number of CPU steps actually executed
+    one(0)
+    t0 = time.perf_counter(); one(1); per = time.perf_counter() - t0
+    warm = min(args.warmup, max(1, int(20.0 / max(per, 1e-6))))
+    steps = min(args.steps, max(3, int(120.0 / max(per, 1e-6))))
+    for i in range(warm):
+        one(i)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        one(i)
+    el = time.perf_counter() - t0
+    val = steps * batch / el
+    cores = torch.get_num_threads()
+    sample = f"{steps} steps of {batch} samples, torch-CPU fp32 restatement of the TF path (TF 2.7 not installable)"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warm, "ms_per_step": 1e3 * el / steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "config": {"workload": workload_name(args.config, arch, batch), "per_gpu_batch": batch, "optimizer": "adam"},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(cfg, arch, batch):
+    return (f"{cfg}: {arch.kind} r_in={arch.d_in} d_Q={arch.d_out} hidden={list(arch.hidden) or list(arch.ranks)} "
+            f"full reduced-Jacobian H1 loss, per-GPU minibatch {batch}")
+
+
+def main():
+    args = parse()
+    from dino_b200 import synthetic as S
+    cfg = S.CONFIGS[args.config]
+    arch = cfg["arch"]
+    batch = args.batch or cfg["batch"]
+    if args.impl == "reference":
+        run_reference(args, arch, batch)
+        return
+
+    import torch
+    import helpers as H
+    from dino_b200 import parallel, _lib, Adam
+    from dino_b200.construction import normalized_mse, normalized_mse_matrix, l2_accuracy, f_accuracy_matrix
+    dp = parallel.init_from_env("nccl")
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    world = dp.world
+    peaks = load_peaks()
+
+    # ---- synthetic teacher data (same on every rank), student initial weights ------------------------
+    n = args.n
+    data, tw = S.make_dataset(arch, n, 1234 + 1)
+    w = H.student_weights(arch, 1234 + 2, tw)
+    model = S.build_model(arch, w, precision=args.precision)
+    model.compile(optimizer=Adam(1e-3), loss=[normalized_mse, normalized_mse_matrix], loss_weights=[1.0, 1.0],
+                  metrics=[l2_accuracy, f_accuracy_matrix])
+    ds = model.make_dataset([data["m"]], [data["q"], data["J"]])
+    Bg = batch * world
+    steps_per_epoch = n // Bg
+    order = np.random.default_rng(0).permutation(n).astype(np.int32)
+    idx = torch.from_numpy(order).cuda()
+    dev = torch.device("cuda", local)
+    dataset_bytes = sum(int(t.numel()) * 4 for t in (ds.m, ds.q, ds.J))
+
+    sampler = ClockSampler(local)
+    if dp.rank == 0:
+        sampler.start()
+
+    def run_steps(k, first):
+        for i in range(k):
+            s = (first + i) % steps_per_epoch
+            model.train_on_indices(ds, idx, s * Bg, Bg)
+
+    # ---- resident-data throughput ------------------------------------------------------------------
+    run_steps(args.warmup, 0)
+    torch.cuda.synchronize(); dp.barrier(); torch.cuda.synchronize()
+    sampler.t0 = time.time()
+    l0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    run_steps(args.steps, args.warmup)
+    e1.record()
+    torch.cuda.synchronize(); dp.barrier(); torch.cuda.synchronize()
+    launches = _lib.launch_count() - l0
+    ms = dp.max_over_ranks(e0.elapsed_time(e1))
+    ms_per_step = ms / args.steps
+    value = Bg * args.steps / (ms * 1e-3)
+
+    # ---- end to end: host minibatches through train_on_batch ------------------------------------------
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    nb_host = min(8, steps_per_epoch)
+    host_batches = []
+    for s in range(nb_host):
+        sel = order[s * Bg + dp.rank * batch: s * Bg + (dp.rank + 1) * batch]
+        host_batches.append((pin(data["m"][sel]), pin(data["q"][sel]), pin(data["J"][sel])))
+    e2e_steps = args.steps
+    for i in range(max(3, min(args.warmup, 10))):
+        hb = host_batches[i % nb_host]
+        model.train_on_batch([hb[0]], [hb[1], hb[2]])
+    torch.cuda.synchronize(); dp.barrier(); torch.cuda.synchronize()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for i in range(e2e_steps):
+        hb = host_batches[i % nb_host]
+        last = model.train_on_batch([hb[0]], [hb[1], hb[2]])
+    e3.record()
+    torch.cuda.synchronize(); dp.barrier(); torch.cuda.synchronize()
+    sampler.t1 = time.time()
+    ms_e2e = dp.max_over_ranks(e2.elapsed_time(e3))
+    e2e_value = Bg * e2e_steps / (ms_e2e * 1e-3)
+    h2d, d2h = model.last_h2d_bytes, model.last_d2h_bytes
+    sampler.stop()
+
+    if dp.rank != 0:
+        return
+    # ---- roofline of the step (all kernels of one step taken as the unit) ----------------
+    F = S.flops_per_sample(arch)
+    achieved_tf = F * batch / (ms_per_step * 1e-3) / 1e12          # per GPU
+    roof = {"bound": "tensor", "achieved": achieved_tf, "peak": peaks["tensor"], "unit": "TFLOP/s",
+            "frac": achieved_tf / peaks["tensor"], "traffic": None, "peak_source": peaks["src"],
+            "kernel": "whole H1 step (all launches of one step), algorithmic FLOPs of SURVEY 8d",
+            "flops_per_sample": F,
+            "hbm_achieved_gbs": S.bytes_per_sample(arch) * batch / (ms_per_step * 1e-3) / 1e9,
+            "hbm_peak_gbs": peaks["hbm"]}
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        import warnings
+        warnings.filterwarnings("ignore")
+        sub = {k: v[:max(4 * batch, 1024)] for k, v in data.items()}
+        rate, csteps, el, cores = cpu_reference_rate(arch, sub, w, batch, args.cpu_seconds)
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{csteps} steps of {batch} samples in {el:.1f} s: torch-CPU fp32 restatement of the "
+                         f"reference's TF step (reverse-mode batch Jacobian, autograd double backward, Keras Adam)"}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "fp32" if args.precision == "fp32" else args.precision,
+            "data": "synthetic",
+            "config": {"workload": workload_name(args.config, arch, batch), "per_gpu_batch": batch,
+                       "global_batch": Bg, "resident_samples": n, "optimizer": "adam", "precision": args.precision,
+                       "parallelism": f"dp{world}",
+                       "l2_policy": f"inputs larger than L2: {dataset_bytes / 1e6:.0f} MB dataset cycled, "
+                                    f"a different minibatch every step"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / e2e_steps, "loss_last": last[0]},
+            "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "clocks": sampler.summary()}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

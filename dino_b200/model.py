@@ -526,6 +526,119 @@ class DinoModel:
             return q.cpu().numpy()
         return [q.cpu().numpy(), J.cpu().numpy()]
 
+    # ---- one optimiser step ------------------------------------------------------------------------
+    def _ensure_opt_state(self):
+        import torch
+        opt, P = self.optimizer, self.core.n_params
+        dev = self.core.device_params().device
+        if opt.kind == "adam" and (opt._m is None or opt._m.numel() != P):
+            opt._m = torch.zeros(P, dtype=torch.float32, device=dev)
+            opt._v = torch.zeros(P, dtype=torch.float32, device=dev)
+
+    def _train_step(self, plan, batch, Bl, Bg, grad, stats_row, dp, st):
+        """fwd + Jacobian + losses + double backward on this rank's Bl samples of a global minibatch
+        of Bg, gradient all-reduce (world > 1), optimiser update.  Asynchronous: no host sync."""
+        lib = plan.lib
+        params = self.core.device_params()
+        opt, P = self.optimizer, self.core.n_params
+        if Bl > 0:
+            _lib.check(lib.dino_h1_fwd_bwd(plan.handle, C.c_void_p(params.data_ptr()), C.byref(batch), Bl,
+                                           self.loss_weights[0], self.loss_weights[1], 1.0 / Bg,
+                                           C.c_void_p(grad.data_ptr()), C.c_void_p(stats_row.data_ptr()), st),
+                       "dino_h1_fwd_bwd")
+        else:
+            grad.zero_()
+        if dp.world > 1:
+            dp.all_reduce_sum(grad)
+        opt.iterations += 1
+        if opt.kind == "adam":
+            _lib.check(lib.dino_adam(C.c_void_p(params.data_ptr()), C.c_void_p(grad.data_ptr()),
+                                     C.c_void_p(opt._m.data_ptr()), C.c_void_p(opt._v.data_ptr()), P,
+                                     opt.learning_rate, opt.beta_1, opt.beta_2, opt.epsilon, opt.iterations, st),
+                       "dino_adam")
+        else:
+            _lib.check(lib.dino_sgd(C.c_void_p(params.data_ptr()), C.c_void_p(grad.data_ptr()), P,
+                                    opt.learning_rate, st), "dino_sgd")
+        self.core.mark_device_updated()
+
+    def make_dataset(self, x, y):
+        """Upload (x, y) to HBM once; the result can be passed to fit / evaluate / train_on_indices."""
+        return self._dataset(x, y)
+
+    def train_on_indices(self, ds, idx_dev, lo, Bg, stats_row=None):
+        """One optimiser step on the global minibatch ds[idx_dev[lo:lo+Bg]] (device int32 indices),
+        sharded over the data-parallel ranks.  No host synchronisation."""
+        import torch
+        dp = parallel.context()
+        off, Bl = parallel.shard_bounds(Bg, dp.rank, dp.world)
+        plan = self._plan(max(-(-Bg // dp.world), 1))
+        self._ensure_opt_state()
+        if getattr(self, "_grad", None) is None or self._grad.numel() != self.core.n_params:
+            self._grad = torch.zeros(self.core.n_params, dtype=torch.float32, device=self.core.device_params().device)
+            self._scratch_stats = torch.zeros(_lib.STAT_SLOTS, dtype=torch.float32, device=self._grad.device)
+        row = self._scratch_stats if stats_row is None else stats_row
+        batch = ds.batch(idx_dev.data_ptr() + 4 * (lo + off)) if Bl > 0 else None
+        self._train_step(plan, batch, Bl, Bg, self._grad, row, dp, _stream())
+
+    def train_on_batch(self, x, y, **_ignored):
+        """Keras ``train_on_batch``: one optimiser step on HOST arrays.  Under data parallelism each
+        rank passes ITS shard of the global minibatch (equal shard sizes).  The shard is copied
+        host->device (pinned torch tensors are copied asynchronously), the step runs, and the
+        step's [loss, l2, h1, metrics...] are read back (device->host), like Keras does."""
+        import torch
+        if not self._compiled:
+            raise RuntimeError("You must compile your model before training/testing.")
+        lib = _lib.load()
+        dp = parallel.context()
+        x = list(x) if isinstance(x, (list, tuple)) else [x]
+        y = list(y) if isinstance(y, (list, tuple)) else [y]
+        dev = self.core.device_params().device
+        stage = getattr(self, "_stage", None)
+        if stage is None:
+            stage = self._stage = {}
+
+        def up(key, a):
+            t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))
+            buf = stage.get(key)
+            if buf is None or buf.shape != t.shape:
+                buf = stage[key] = torch.empty(t.shape, dtype=torch.float32, device=dev)
+            buf.copy_(t, non_blocking=True)
+            return buf
+
+        ds = DeviceDataset.__new__(DeviceDataset)
+        ds.m = up("m", x[0]); ds.n = Bl = int(ds.m.shape[0])
+        ds.U = ds.V = ds.J = ds.jn2 = ds.seed = None
+        if self.jac_mode == _lib.JAC_SKETCHED:
+            ds.U, ds.V = up("U", x[1]), up("V", x[2])
+        if self.output_basis is not None:
+            ds.seed = up("seed", np.ascontiguousarray(self.output_basis.T))
+        ds.q = up("q", y[0])
+        st = _stream()
+        norms = stage.get("norms")
+        if norms is None or norms.shape[1] != Bl:
+            norms = stage["norms"] = torch.empty(2, Bl, dtype=torch.float32, device=dev)
+            stage["stats"] = torch.zeros(_lib.STAT_SLOTS, dtype=torch.float32, device=dev)
+            stage["grad"] = torch.zeros(self.core.n_params, dtype=torch.float32, device=dev)
+        ds.qn2 = norms[0]
+        _lib.check(lib.dino_sample_sqnorms(C.c_void_p(ds.q.data_ptr()), Bl, ds.q[0].numel(),
+                                           C.c_void_p(ds.qn2.data_ptr()), st), "dino_sample_sqnorms")
+        if self.jac_mode != _lib.JAC_NONE:
+            ds.J = up("J", y[1])
+            ds.jn2 = norms[1]
+            _lib.check(lib.dino_sample_sqnorms(C.c_void_p(ds.J.data_ptr()), Bl, ds.J[0].numel(),
+                                               C.c_void_p(ds.jn2.data_ptr()), st), "dino_sample_sqnorms")
+        stats = stage["stats"]
+        stats.zero_()
+        plan = self._plan(Bl)
+        self._ensure_opt_state()
+        self._train_step(plan, ds.batch(None), Bl, Bl * dp.world, stage["grad"], stats, dp, st)
+        if dp.world > 1:
+            dp.all_reduce_sum(stats)
+        host = stats.cpu().numpy()[None, :]          # device->host read of the step's result
+        self.last_h2d_bytes = sum(int(t.numel()) * 4 for k, t in stage.items() if k in ("m", "q", "J", "U", "V"))
+        self.last_d2h_bytes = int(stats.numel()) * 4
+        return _combine_stats(host, self.loss_weights, self.jac_mode != _lib.JAC_NONE)
+
     # ---- fit -----------------------------------------------------------------------------------------
     def fit(self, x, y, validation_data=None, epochs=1, batch_size=32, verbose=0, callbacks=None,
             shuffle=True, initial_epoch=0, perms=None, **_ignored):
@@ -548,10 +661,7 @@ class DinoModel:
         dev = params.device
         local_max = -(-min(batch_size, n) // dp.world)
         plan = self._plan(max(local_max, 1))
-        opt = self.optimizer
-        if opt.kind == "adam" and (opt._m is None or opt._m.numel() != P):
-            opt._m = torch.zeros(P, dtype=torch.float32, device=dev)
-            opt._v = torch.zeros(P, dtype=torch.float32, device=dev)
+        self._ensure_opt_state()
         grad = torch.zeros(P, dtype=torch.float32, device=dev)
         steps = (n + batch_size - 1) // batch_size
         hist = History()
@@ -583,24 +693,8 @@ class DinoModel:
                 lo = step * batch_size
                 Bg = min(batch_size, n - lo)
                 off, Bl = parallel.shard_bounds(Bg, dp.rank, dp.world)
-                if Bl > 0:
-                    batch = ds.batch(idx.data_ptr() + 4 * (lo + off))
-                    _lib.check(lib.dino_h1_fwd_bwd(plan.handle, C.c_void_p(params.data_ptr()), C.byref(batch), Bl,
-                                                   w0, w1, 1.0 / Bg, C.c_void_p(grad.data_ptr()),
-                                                   C.c_void_p(stats[step].data_ptr()), st), "dino_h1_fwd_bwd")
-                else:
-                    grad.zero_()
-                if dp.world > 1:
-                    dp.all_reduce_sum(grad)
-                opt.iterations += 1
-                if opt.kind == "adam":
-                    _lib.check(lib.dino_adam(C.c_void_p(params.data_ptr()), C.c_void_p(grad.data_ptr()),
-                                             C.c_void_p(opt._m.data_ptr()), C.c_void_p(opt._v.data_ptr()), P,
-                                             opt.learning_rate, opt.beta_1, opt.beta_2, opt.epsilon,
-                                             opt.iterations, st), "dino_adam")
-                else:
-                    _lib.check(lib.dino_sgd(C.c_void_p(params.data_ptr()), C.c_void_p(grad.data_ptr()), P,
-                                            opt.learning_rate, st), "dino_sgd")
+                batch = ds.batch(idx.data_ptr() + 4 * (lo + off)) if Bl > 0 else None
+                self._train_step(plan, batch, Bl, Bg, grad, stats[step], dp, st)
             self.core.mark_device_updated()
             if dp.world > 1:
                 dp.all_reduce_sum(stats)
