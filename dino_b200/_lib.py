@@ -17,6 +17,7 @@ JAC_NONE, JAC_FULL, JAC_OUT_REDUCED, JAC_SKETCHED = 0, 1, 2, 3
 PREC_FP32, PREC_TF32 = 0, 1
 STAT_L2_SUM, STAT_H1_SUM, STAT_EQ_SUM, STAT_NQ_SUM, STAT_JROW_SUM, STAT_COUNT, STAT_JROWS = range(7)
 STAT_SLOTS = 8
+NOALLOC_MAX_BATCH, NOALLOC_MAX_WIDTH = 256, 1024
 
 JAC_MODES = {"none": JAC_NONE, "full": JAC_FULL, "out_reduced": JAC_OUT_REDUCED, "sketched": JAC_SKETCHED}
 PRECISIONS = {"fp32": PREC_FP32, "tf32": PREC_TF32}
@@ -57,6 +58,8 @@ SIGNATURES = {
                             C.c_float, C.c_float, C.c_int64, C.c_void_p]),
     "dino_sgd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p]),
     "dino_sample_sqnorms": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]),
+    "dino_forward_noalloc": (C.c_int, [C.POINTER(DinoNetSpec), C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                       C.c_void_p]),
     "dino_launch_count": (C.c_int64, []),
     "dino_last_error": (C.c_char_p, []),
     "dino_version": (C.c_char_p, []),

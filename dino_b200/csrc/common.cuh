@@ -77,6 +77,16 @@ cudaError_t launch_sqnorms(const float* x, long long n, long long len, float* ou
 cudaError_t launch_copy2d(const float* src, long long ld_src, float* dst, long long ld_dst, int rows,
                           int cols, cudaStream_t st);
 
+}  // namespace dino
+#ifdef __cplusplus
+#include <string>
+namespace dino {
+int set_last_error(const std::string& msg);   // sets dino_last_error(), returns 1   (plan.cu)
+void count_launch();                           // dino_launch_count() += 1            (plan.cu)
+}
+#endif
+namespace dino {
+
 // statistics slots accumulated by the loss kernels (floats)
 enum { ST_L2_SUM = 0, ST_H1_SUM = 1, ST_EQ_SUM = 2, ST_NQ_SUM = 3, ST_JROW_SUM = 4, ST_COUNT = 5,
        ST_JROWS = 6, ST_SLOTS = 8 };

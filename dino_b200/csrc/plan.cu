@@ -34,6 +34,12 @@ static int fail(const std::string& msg) {
   return 1;
 }
 
+namespace dino {
+// used by translation units that hold entry points of their own (noalloc.cu)
+int set_last_error(const std::string& msg) { return fail(msg); }
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+}  // namespace dino
+
 #define DINO_CUDA(expr)                                                                      \
   do {                                                                                       \
     cudaError_t _e = (expr);                                                                 \

@@ -132,6 +132,30 @@ int dino_sgd(float* d_params, const float* d_grad, int64_t count, float lr, dino
  * dataset because the targets do not change during fit. */
 int dino_sample_sqnorms(const float* d_x, int64_t n, int64_t len, float* d_out, dino_stream_t stream);
 
+/* No counterpart in the reference.  q_hat = net(m) like dino_forward, for callers that have no
+ * device memory to hand over as a workspace and are not in a position to obtain any: code that
+ * runs between the nodes of somebody else's solver loop (e.g. the inverse-problem iterations
+ * that drive InferenceOracle-style evaluations) and owns nothing but its input and output
+ * buffers; processes in which another framework's caching pool has already reserved the whole
+ * HBM, so a cudaMalloc here would fail; and latency-critical loops in which the implicit
+ * device-wide synchronisation of cudaMalloc/cudaFree is not acceptable.  The call performs no
+ * cudaMalloc/cudaFree and calls no allocating library routine: activations live in a fixed
+ * 3 MiB array inside the library image (held by every GPU that loads the library until the
+ * process exits).  Limits: 1 <= B <= DINO_NOALLOC_MAX_BATCH, every layer width <=
+ * DINO_NOALLOC_MAX_WIDTH (d_in is not limited); larger problems are rejected with an error and
+ * must use dino_forward.  `spec` is the same description dino_plan_create takes (jac_mode,
+ * seed_dim, max_batch, precision are ignored); d_params is the flat arena in the layout of
+ * dino_plan_layer_offsets; d_m is [B, d_in] dense, d_q_out [B, d_out] dense.
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress) with
+ * that device current; make that first call before starting any stream capture.  All calls on a
+ * device share the one array: two calls whose kernels may overlap on the GPU (different streams,
+ * or different host threads) race on it - serialise them.  Nothing in the array needs to be zero
+ * on entry and its contents after a call are unspecified. */
+#define DINO_NOALLOC_MAX_BATCH 256
+#define DINO_NOALLOC_MAX_WIDTH 1024
+int dino_forward_noalloc(const DinoNetSpec* spec, const float* d_params, const float* d_m, int32_t B,
+                         float* d_q_out, dino_stream_t stream);
+
 /* number of kernels this library has launched in the calling process (bench.py gpu_launches) */
 int64_t dino_launch_count(void);
 
