@@ -370,7 +370,7 @@ def h1_step_grads(net: ONet, batch: Batch, loss_weights=(1.0, 1.0), jac_mode="fu
     grads = [torch.zeros_like(p) if g is None else g for p, g in zip(params, grads)]
     for p in params:
         p.requires_grad_(False)
-    return (float(total), float(l2), float(h1)), grads
+    return (float(total.detach()), float(l2.detach()), float(h1.detach())), grads
 
 
 def fit(net: ONet, data: Batch, *, epochs=1, batch_size=32, lr=1e-3, opt="adam",
