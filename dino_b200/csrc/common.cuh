@@ -30,6 +30,8 @@ struct GemmOp {
   const float* add_pre; long long ld_ap;
   const float* scale; long long ld_sc;
   const float* add_post; long long ld_apo;
+  int round_tf32;                                    // round the stored result to nearest TF32 (it feeds a TF32 MMA,
+                                                     // which would otherwise TRUNCATE it: a systematic bias per layer)
 };
 
 inline GemmOp gemm_op_zero() {
@@ -41,12 +43,26 @@ inline GemmOp gemm_op_zero() {
   o.bias = nullptr; o.act = 0; o.s_out = nullptr; o.ld_s = 0;
   o.yref = nullptr; o.ld_y = 0; o.rowsum = nullptr; o.ld_rs = 0;
   o.add_pre = nullptr; o.ld_ap = 0; o.scale = nullptr; o.ld_sc = 0;
-  o.add_post = nullptr; o.ld_apo = 0;
+  o.add_post = nullptr; o.ld_apo = 0; o.round_tf32 = 0;
   return o;
 }
 
 // fp32 SIMT engine (exact-parity mode).  Returns a cudaError_t from the launch.
 cudaError_t launch_gemm_simt(const GemmOp& op, int num_sms, cudaStream_t st);
+// tcgen05 TF32 engine (gemm_tc.cu): both operands K-major (a_sk == b_sk == 1), 16-byte row pitches,
+// epilogue limited to add_pre / scale / add_post.  gemm_tc_supported() says whether an op qualifies.
+bool gemm_tc_supported(const GemmOp& op);
+cudaError_t launch_gemm_tc(const GemmOp& op, cudaStream_t st);
+
+// weight staging for the TMA-fed engine: padded copy Wp[n_in][r4(n_out)] and transpose WTp[n_out][r4(n_in)]
+struct PrepEntry { long long koff, wp_off, wtp_off; int n_in, n_out, ld_wp, ld_wtp; };
+struct PrepTable { int n; PrepEntry e[32]; };
+cudaError_t launch_prep_weights(const float* params, float* ws, const PrepTable& t, int max_in, int max_out,
+                                cudaStream_t st);
+// rowsum[b,n] = sum_i dq[b*s+i,n]*q[b*s+i,n];  dq[row,n] = dq[row,n]*scale[b,n] + add_post[row,n]   (in place)
+cudaError_t launch_rowsum_scale(float* dq, long long ld_dq, const float* q, long long ld_q, const float* scale,
+                                long long ld_sc, const float* add_post, long long ld_apo, float* rowsum,
+                                long long ld_rs, int B, int sdim, int n, int write_out, int round_tf32, cudaStream_t st);
 
 // ---- elementwise / reduction kernels (elementwise.cu) ---------------------------------------
 cudaError_t launch_gather_rows(const float* src, const int* idx, int rows, int cols, long long ld_src,
@@ -93,6 +109,11 @@ enum { ST_L2_SUM = 0, ST_H1_SUM = 1, ST_EQ_SUM = 2, ST_NQ_SUM = 3, ST_JROW_SUM =
 
 __device__ __forceinline__ float softplus_f(float x) {
   return fmaxf(x, 0.f) + log1pf(expf(-fabsf(x)));
+}
+__device__ __forceinline__ float round_tf32_f(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
 }
 __device__ __forceinline__ float sigmoid_f(float x) {
   return 1.f / (1.f + expf(-x));

@@ -189,19 +189,22 @@ cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, const f
 
 // da = dz * s + rowsum * (1 - s)   and   dbias[n] = sum_b da[b,n]
 // (s == nullptr: linear layer, da = dz; rowsum == nullptr: no Jacobian term)
-__global__ void mlp_da_kernel(const float* __restrict__ dz, long long ld_dz, const float* __restrict__ s,
-                              long long ld_s, const float* __restrict__ rowsum, long long ld_rs, int B, int n,
-                              float* __restrict__ da, long long ld_da, float* __restrict__ dbias) {
-  __shared__ float red[8][33];
+__global__ void __launch_bounds__(1024) mlp_da_kernel(const float* __restrict__ dz, long long ld_dz,
+                                                      const float* __restrict__ s, long long ld_s,
+                                                      const float* __restrict__ rowsum, long long ld_rs, int B, int n,
+                                                      float* __restrict__ da, long long ld_da,
+                                                      float* __restrict__ dbias) {
+  __shared__ float red[32][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   float acc = 0.f;
   if (c < n) {
-    for (int b = threadIdx.y; b < B; b += 8) {
+#pragma unroll 2
+    for (int b = threadIdx.y; b < B; b += 32) {
       float v = dz[(long long)b * ld_dz + c];
       if (s != nullptr) {
         const float sv = s[(long long)b * ld_s + c];
-        v *= sv;
-        if (rowsum != nullptr) v = fmaf(rowsum[(long long)b * ld_rs + c], 1.f - sv, v);
+        const float rs = rowsum != nullptr ? rowsum[(long long)b * ld_rs + c] : 0.f;
+        v = fmaf(rs, 1.f - sv, v * sv);
       }
       if (da != nullptr) da[(long long)b * ld_da + c] = v;
       acc += v;
@@ -211,14 +214,78 @@ __global__ void mlp_da_kernel(const float* __restrict__ dz, long long ld_dz, con
   __syncthreads();
   if (threadIdx.y == 0 && c < n && dbias != nullptr) {
     float v = 0.f;
-    for (int r = 0; r < 8; ++r) v += red[r][threadIdx.x];
+#pragma unroll 8
+    for (int r = 0; r < 32; ++r) v += red[r][threadIdx.x];
     dbias[c] = v;
   }
 }
 cudaError_t launch_mlp_da(const float* dz, long long ld_dz, const float* s, long long ld_s, const float* rowsum,
                           long long ld_rs, int B, int n, float* da, long long ld_da, float* dbias, cudaStream_t st) {
   if (n <= 0) return cudaSuccess;
-  mlp_da_kernel<<<cdiv(n, 32), dim3(32, 8), 0, st>>>(dz, ld_dz, s, ld_s, rowsum, ld_rs, B, n, da, ld_da, dbias);
+  mlp_da_kernel<<<cdiv(n, 32), dim3(32, 32), 0, st>>>(dz, ld_dz, s, ld_s, rowsum, ld_rs, B, n, da, ld_da, dbias);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Weight staging for the TMA-fed tensor-core engine (row pitches must be multiples of 16 bytes and
+// both GEMM operands K-major): one launch covers every layer; blockIdx.z selects the layer.
+__global__ void prep_weights_kernel(const float* __restrict__ params, float* __restrict__ ws, const PrepTable t) {
+  __shared__ float tile[32][33];
+  const PrepEntry e = t.e[blockIdx.z];
+  const int k0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
+  if (k0 >= e.n_in || n0 >= e.n_out) return;
+  const float* W = params + e.koff;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int k = k0 + i, n = n0 + threadIdx.x;
+    const float v = (k < e.n_in && n < e.n_out) ? round_tf32_f(W[(long long)k * e.n_out + n]) : 0.f;
+    tile[i][threadIdx.x] = v;
+    if (k < e.n_in && n < e.ld_wp) ws[e.wp_off + (long long)k * e.ld_wp + n] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int n = n0 + i, k = k0 + threadIdx.x;
+    if (n < e.n_out && k < e.ld_wtp) ws[e.wtp_off + (long long)n * e.ld_wtp + k] = tile[threadIdx.x][i];
+  }
+}
+cudaError_t launch_prep_weights(const float* params, float* ws, const PrepTable& t, int max_in, int max_out,
+                                cudaStream_t st) {
+  if (t.n <= 0) return cudaSuccess;
+  dim3 grid(cdiv(max_out, 32), cdiv(max_in, 32), t.n), block(32, 8);
+  prep_weights_kernel<<<grid, block, 0, st>>>(params, ws, t);
+  return cudaGetLastError();
+}
+
+// d sigma row-sum and per-sample scaling after a tensor-core data-gradient GEMM (its epilogue has no
+// cross-row reduction): one CTA per (sample, 64 columns), threads own columns, so no atomics.
+__global__ void __launch_bounds__(64) rowsum_scale_kernel(float* __restrict__ dq, long long ld_dq,
+                                                          const float* __restrict__ q, long long ld_q,
+                                                          const float* __restrict__ scale, long long ld_sc,
+                                                          const float* __restrict__ add_post, long long ld_apo,
+                                                          float* __restrict__ rowsum, long long ld_rs, int sdim, int n,
+                                                          int write_out, int round_out) {
+  const int c = blockIdx.x * 64 + threadIdx.x;
+  if (c >= n) return;
+  const long long b = blockIdx.y;
+  const float sc = scale ? scale[b * ld_sc + c] : 1.f;
+  float acc = 0.f;
+#pragma unroll 4
+  for (int i = 0; i < sdim; ++i) {
+    const long long row = b * sdim + i;
+    const float v = dq[row * ld_dq + c];
+    acc = fmaf(v, q[row * ld_q + c], acc);
+    if (write_out) {
+      const float o = add_post ? fmaf(v, sc, add_post[row * ld_apo + c]) : v * sc;
+      dq[row * ld_dq + c] = round_out ? round_tf32_f(o) : o;
+    }
+  }
+  if (rowsum) rowsum[b * ld_rs + c] = acc;
+}
+cudaError_t launch_rowsum_scale(float* dq, long long ld_dq, const float* q, long long ld_q, const float* scale,
+                                long long ld_sc, const float* add_post, long long ld_apo, float* rowsum,
+                                long long ld_rs, int B, int sdim, int n, int write_out, int round_tf32, cudaStream_t st) {
+  if (B <= 0 || n <= 0) return cudaSuccess;
+  rowsum_scale_kernel<<<dim3(cdiv(n, 64), B), 64, 0, st>>>(dq, ld_dq, q, ld_q, scale, ld_sc, add_post, ld_apo,
+                                                            rowsum, ld_rs, sdim, n, write_out, round_tf32);
   return cudaGetLastError();
 }
 

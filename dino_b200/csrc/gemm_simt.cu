@@ -20,7 +20,8 @@ __global__ void __launch_bounds__(NT) gemm_simt_kernel(const GemmOp op) {
   static_assert((BM / TM) * (BN / TN) == NT, "thread layout");
   constexpr int LDA_S = BM + 4, LDB_S = BN + 4;
   constexpr int A_PER_T = BM * BK / NT, B_PER_T = BK * BN / NT;
-  __shared__ __align__(16) float smem[2 * BK * LDA_S + 2 * BK * LDB_S];
+  constexpr int TILE_FLOATS = 2 * BK * LDA_S + 2 * BK * LDB_S, STAGE_FLOATS = BM * (BN + 1);
+  __shared__ __align__(16) float smem[TILE_FLOATS > STAGE_FLOATS ? TILE_FLOATS : STAGE_FLOATS];
   float* As = smem;
   float* Bs = smem + 2 * BK * LDA_S;
 
@@ -96,7 +97,7 @@ __global__ void __launch_bounds__(NT) gemm_simt_kernel(const GemmOp op) {
     if (kt + 1 < nk) load_regs(kbeg + (kt + 1) * BK);
     const float* as = As + buf * BK * LDA_S + ty * TM;
     const float* bs = Bs + buf * BK * LDB_S + tx * TN;
-#pragma unroll
+#pragma unroll 4
     for (int kk = 0; kk < BK; ++kk) {
       float a[TM], b[TN];
       if constexpr (TM % 4 == 0) {
@@ -126,81 +127,88 @@ __global__ void __launch_bounds__(NT) gemm_simt_kernel(const GemmOp op) {
     __syncthreads();
   }
 
+  // ---- stage the accumulator tile in shared memory -----------------------------------------------
+  // The main-loop buffers are free now.  Everything after this point is written as ROLLED loops over
+  // the staged tile: the epilogue runs once per launch, so straight-line unrolled code would cost an
+  // instruction fetch per instruction executed (measured: profiles/r01a_summary.md), and the staged
+  // order also makes every global access row-contiguous.
+  constexpr int LDC_S = BN + 1;
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) smem[(ty * TM + i) * LDC_S + tx * TN + j] = acc[i][j];
+  __syncthreads();
+  const int rows_here = min(BM, op.M - m0);
+  const int cols_here = min(BN, op.N - n0);
+
   // ---- rowsum[b,n] += sum over the sample's rows of acc * yref  (pre-epilogue accumulators) ----
   if (op.rowsum != nullptr) {
-    const int sdim = op.sdim;
-    const int b_first = m0 / sdim;
-    const int m_last = min(op.M, m0 + BM) - 1;
-    const int ns = m_last / sdim - b_first + 1;
-    constexpr int SMEM_FLOATS = 2 * BK * LDA_S + 2 * BK * LDB_S;
-    const bool use_smem = ns * BN <= SMEM_FLOATS;      // main loop is over: tiles are free
-    if (use_smem) {
-      for (int e = tid; e < ns * BN; e += NT) smem[e] = 0.f;
-      __syncthreads();
-    }
-    float part[TN];
-    int cur_b = -1;
-    auto flush = [&]() {
-      if (cur_b < 0) return;
+    constexpr int GROUPS = NT / BN, ROWS_PER_GROUP = BM / GROUPS;
+    const int n = tid % BN, rg = tid / BN;
+    if (n < cols_here) {
+      const int gn = n0 + n;
+      const int r_end = min(rows_here, (rg + 1) * ROWS_PER_GROUP);
+      float part = 0.f;
+      int cur_b = -1;
+#pragma unroll 1
+      for (int r0 = rg * ROWS_PER_GROUP; r0 < r_end; r0 += 4) {
+        float y[4];                       // batch the global loads: 4 independent requests in flight
 #pragma unroll
-      for (int j = 0; j < TN; ++j) {
-        const int gn = n0 + tx * TN + j;
-        if (gn < op.N) {
-          if (use_smem) atomicAdd(&smem[(cur_b - b_first) * BN + tx * TN + j], part[j]);
-          else atomicAdd(op.rowsum + (long long)cur_b * op.ld_rs + gn, part[j]);
+        for (int u = 0; u < 4; ++u)
+          y[u] = (r0 + u < r_end) ? op.yref[(long long)(m0 + r0 + u) * op.ld_y + gn] : 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int r = r0 + u;
+          if (r < r_end) {
+            const int b = (m0 + r) / op.sdim;
+            if (b != cur_b) {
+              if (cur_b >= 0) atomicAdd(op.rowsum + (long long)cur_b * op.ld_rs + gn, part);
+              cur_b = b;
+              part = 0.f;
+            }
+            part = fmaf(smem[r * LDC_S + n], y[u], part);
+          }
         }
       }
-    };
-#pragma unroll
-    for (int i = 0; i < TM; ++i) {
-      const int gm = m0 + ty * TM + i;
-      if (gm >= op.M) break;
-      const int b = gm / sdim;
-      if (b != cur_b) {
-        flush();
-        cur_b = b;
-#pragma unroll
-        for (int j = 0; j < TN; ++j) part[j] = 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < TN; ++j) {
-        const int gn = n0 + tx * TN + j;
-        if (gn < op.N) part[j] = fmaf(acc[i][j], op.yref[(long long)gm * op.ld_y + gn], part[j]);
-      }
-    }
-    flush();
-    if (use_smem) {
-      __syncthreads();
-      for (int e = tid; e < ns * BN; e += NT) {
-        const int lb = e / BN, n = e % BN;
-        if (n0 + n < op.N) atomicAdd(op.rowsum + (long long)(b_first + lb) * op.ld_rs + n0 + n, smem[e]);
-      }
+      if (cur_b >= 0) atomicAdd(op.rowsum + (long long)cur_b * op.ld_rs + gn, part);
     }
   }
 
   // ---- epilogue -------------------------------------------------------------------------------
   if (op.C == nullptr) return;
+  const int total = rows_here * BN;
+#pragma unroll 1
+  for (int e0 = tid; e0 < total; e0 += 4 * NT) {
+    // gather every operand of 4 tile elements first (independent loads in flight), then finish them
+    float v[4], bi[4], ap[4], sc[4], apo[4];
+    bool ok[4];
 #pragma unroll
-  for (int i = 0; i < TM; ++i) {
-    const int gm = m0 + ty * TM + i;
-    if (gm >= op.M) break;
-    const int b = gm / op.sdim;
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + u * NT;
+      const int r = e / BN, n = e % BN;
+      ok[u] = e < total && n < cols_here;
+      const int gm = m0 + r, gn = n0 + n;
+      v[u] = ok[u] ? smem[r * LDC_S + n] : 0.f;
+      bi[u] = (ok[u] && op.bias != nullptr) ? op.bias[gn] : 0.f;
+      ap[u] = (ok[u] && op.add_pre != nullptr) ? op.add_pre[(long long)gm * op.ld_ap + gn] : 0.f;
+      sc[u] = (ok[u] && op.scale != nullptr) ? op.scale[(long long)(gm / op.sdim) * op.ld_sc + gn] : 1.f;
+      apo[u] = (ok[u] && op.add_post != nullptr) ? op.add_post[(long long)gm * op.ld_apo + gn] : 0.f;
+    }
 #pragma unroll
-    for (int j = 0; j < TN; ++j) {
-      const int gn = n0 + tx * TN + j;
-      if (gn >= op.N) continue;
-      float v = acc[i][j];
-      if (op.bias != nullptr) v += op.bias[gn];
+    for (int u = 0; u < 4; ++u) {
+      if (!ok[u]) continue;
+      const int e = e0 + u * NT;
+      const int gm = m0 + e / BN, gn = n0 + e % BN;
+      float x = v[u] + bi[u];
       if (op.act) {
-        if (op.s_out != nullptr) op.s_out[(long long)gm * op.ld_s + gn] = sigmoid_f(v);
-        v = softplus_f(v);
+        if (op.s_out != nullptr) op.s_out[(long long)gm * op.ld_s + gn] = sigmoid_f(x);
+        x = softplus_f(x);
       }
-      if (op.add_pre != nullptr) v += op.add_pre[(long long)gm * op.ld_ap + gn];
-      if (op.scale != nullptr) v *= op.scale[(long long)b * op.ld_sc + gn];
-      if (op.add_post != nullptr) v += op.add_post[(long long)gm * op.ld_apo + gn];
+      x = (x + ap[u]) * sc[u] + apo[u];
+      if (op.round_tf32) x = round_tf32_f(x);
       float* c = op.C + (long long)gm * op.ldc + gn;
-      if (op.atomic_c) atomicAdd(c, v);
-      else *c = v;
+      if (op.atomic_c) atomicAdd(c, x);
+      else *c = x;
     }
   }
 }

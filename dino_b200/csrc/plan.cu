@@ -58,6 +58,7 @@ struct LayerPlan {
   int n_in, n_out, act, has_bias, trainable, skip_from;
   long long koff, boff;      // offsets in the parameter arena (floats)
   long long z_off, sg_off, q_off, rs_off;   // workspace offsets (floats); -1 when absent
+  long long wp_off, wtp_off, ld_wp, ld_wtp; // TF32 mode: padded W [n_in][ld_wp] and W^T [n_out][ld_wtp]
   long long ld_out;          // r4(n_out)
   int lands_skip;            // index l2 of the skip layer whose source is THIS layer's input, or -1
 };
@@ -74,6 +75,8 @@ struct DinoPlan {
   long long ld_in, ld_dr, ld_dz, ld_ident;
   long long ws_floats;
   float* ws;
+  PrepTable prep;            // TF32 mode: weight staging table
+  int max_in, max_out;
 };
 
 static cudaStream_t S(dino_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
@@ -181,6 +184,21 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
       for (int i = 0; i < 3; ++i) p->off_dr[i] = take(Ms * p->ld_dr);
     if (p->jac_mode == DINO_JAC_SKETCHED) p->off_sk = take(Bm * (long long)p->s * p->s);
   }
+  p->prep.n = 0;
+  p->max_in = p->max_out = 1;
+  for (auto& lp : p->layers) { lp.wp_off = lp.wtp_off = -1; lp.ld_wp = r4(lp.n_out); lp.ld_wtp = r4(lp.n_in); }
+  if (p->precision == DINO_PREC_TF32 && p->jac_mode != DINO_JAC_NONE) {
+    if (p->L > 32) { delete p; return fail("dino_plan_create: TF32 mode supports at most 32 layers"); }
+    for (auto& lp : p->layers) {
+      lp.wp_off = take((long long)lp.n_in * lp.ld_wp);
+      lp.wtp_off = take((long long)lp.n_out * lp.ld_wtp);
+      PrepEntry& e = p->prep.e[p->prep.n++];
+      e.koff = lp.koff; e.wp_off = lp.wp_off; e.wtp_off = lp.wtp_off;
+      e.n_in = lp.n_in; e.n_out = lp.n_out; e.ld_wp = (int)lp.ld_wp; e.ld_wtp = (int)lp.ld_wtp;
+      if (lp.n_in > p->max_in) p->max_in = lp.n_in;
+      if (lp.n_out > p->max_out) p->max_out = lp.n_out;
+    }
+  }
   p->ws_floats = off;
   *out = p;
   return 0;
@@ -229,6 +247,10 @@ static int check_call(const DinoPlan* p, const float* params, const DinoBatch* b
 }
 
 static int gemm(const DinoPlan* p, const GemmOp& op, cudaStream_t st) {
+  if (p->precision == DINO_PREC_TF32 && gemm_tc_supported(op)) {
+    DINO_LAUNCH(launch_gemm_tc(op, st));
+    return 0;
+  }
   DINO_LAUNCH(launch_gemm_simt(op, p->num_sms, st));
   return 0;
 }
@@ -287,13 +309,17 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
     top = {seed, ld_seed, s};
   }
   *top_out = top;
+  const bool tc = p->precision == DINO_PREC_TF32;
+  if (tc) DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
   for (int l = L - 1; l >= 0; --l) {
     const LayerPlan& lp = p->layers[l];
     GemmOp op = gemm_op_zero();
     if (l == L - 1) { op.A = top.ptr; op.a_sm = top.ld; op.a_mod = top.mod; }
     else { op.A = ws + lp.q_off; op.a_sm = lp.ld_out; }
     op.a_sk = 1;
-    op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out;     // W_l^T
+    // W_l^T: element (k = out index, n = in index) = W_l[n][k]; the TF32 engine reads the 16-byte-pitch copy
+    if (tc) { op.B = ws + lp.wp_off; op.b_sk = 1; op.b_sn = lp.ld_wp; }
+    else { op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out; }
     op.M = M; op.N = lp.n_in; op.K = lp.n_out; op.sdim = s;
     if (lp.lands_skip >= 0) {
       const LayerPlan& sk = p->layers[lp.lands_skip];
@@ -303,6 +329,7 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
       const LayerPlan& below = p->layers[l - 1];
       if (below.act == DINO_ACT_SOFTPLUS) { op.scale = ws + below.sg_off; op.ld_sc = below.ld_out; }
       op.C = ws + below.q_off; op.ldc = below.ld_out;
+      op.round_tf32 = tc ? 1 : 0;
     } else {
       op.C = ws + p->off_r0; op.ldc = p->ld_in;
     }
@@ -357,8 +384,22 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
     if (!need_rs && !need_out) continue;
     GemmOp op = gemm_op_zero();
     op.A = dr_ptr(l); op.a_sm = dr_ld(l); op.a_sk = 1;
-    op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1;      // W_l
     op.M = M; op.N = lp.n_out; op.K = lp.n_in; op.sdim = s;
+    const float* skip_add = nullptr; long long ld_skip = 0;
+    if (need_out && lp.skip_from >= 0) { skip_add = dr_ptr(lp.skip_from); ld_skip = dr_ld(lp.skip_from); }
+    if (p->precision == DINO_PREC_TF32 && need_out && lp.n_out <= p->ld_dr) {
+      // tensor-core path: dQ_l = dR_l W_l with the K-major copy W_l^T; the cross-row d sigma sum and the
+      // per-sample scaling follow in one pass over the tile (rowsum_scale_kernel)
+      op.B = ws + lp.wtp_off; op.b_sk = 1; op.b_sn = lp.ld_wtp;
+      op.C = dr_ptr(l + 1); op.ldc = dr_ld(l + 1);
+      if (!need_rs) { op.add_post = skip_add; op.ld_apo = ld_skip; op.round_tf32 = 1; }
+      if (gemm(p, op, st)) return 1;
+      if (need_rs)
+        DINO_LAUNCH(launch_rowsum_scale(dr_ptr(l + 1), dr_ld(l + 1), q, ldq, ws + lp.sg_off, lp.ld_out, skip_add,
+                                        ld_skip, ws + lp.rs_off, lp.ld_out, B, s, lp.n_out, 1, 1, st));
+      continue;
+    }
+    op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1;      // W_l
     if (need_rs) {
       op.yref = q; op.ld_y = ldq;       // softplus top layers are always materialised (qmod == 0)
       op.rowsum = ws + lp.rs_off; op.ld_rs = lp.ld_out;
@@ -366,7 +407,7 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
     }
     if (need_out) {
       op.C = dr_ptr(l + 1); op.ldc = dr_ld(l + 1);
-      if (lp.skip_from >= 0) { op.add_post = dr_ptr(lp.skip_from); op.ld_apo = dr_ld(lp.skip_from); }
+      op.add_post = skip_add; op.ld_apo = ld_skip;
     }
     if (gemm(p, op, st)) return 1;
   }
@@ -491,5 +532,24 @@ extern "C" int dino_sgd(float* params, const float* grad, int64_t count, float l
 extern "C" int dino_sample_sqnorms(const float* x, int64_t n, int64_t len, float* out, dino_stream_t stream) {
   if (!x || !out) return fail("dino_sample_sqnorms: null argument");
   DINO_LAUNCH(launch_sqnorms(x, n, len, out, S(stream)));
+  return 0;
+}
+
+extern "C" int dino_gemm_nt(int engine, const float* A, int64_t lda, const float* Bt, int64_t ldb, float* C,
+                            int64_t ldc, int32_t M, int32_t N, int32_t K, dino_stream_t stream) {
+  if (!A || !Bt || !C) return fail("dino_gemm_nt: null argument");
+  GemmOp op = gemm_op_zero();
+  op.A = A; op.a_sm = lda; op.a_sk = 1;
+  op.B = Bt; op.b_sk = 1; op.b_sn = ldb;
+  op.M = M; op.N = N; op.K = K; op.C = C; op.ldc = ldc;
+  if (engine == DINO_PREC_TF32) {
+    if (!gemm_tc_supported(op)) return fail("dino_gemm_nt: operands do not meet the TF32 engine's alignment rules");
+    DINO_LAUNCH(launch_gemm_tc(op, S(stream)));
+  } else {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    DINO_LAUNCH(launch_gemm_simt(op, sms, S(stream)));
+  }
   return 0;
 }

@@ -156,6 +156,13 @@ int dino_sample_sqnorms(const float* d_x, int64_t n, int64_t len, float* d_out, 
 int dino_forward_noalloc(const DinoNetSpec* spec, const float* d_params, const float* d_m, int32_t B,
                          float* d_q_out, dino_stream_t stream);
 
+/* The contraction primitive of the Jacobian chain on its own: C[M,N] = A[M,K] * Bt[N,K]^T, fp32 in and
+ * out (what a TF MatMul inside tape.batch_jacobian computes, jacobianConstruction.py:149).  engine =
+ * DINO_PREC_FP32 (SIMT FFMA) or DINO_PREC_TF32 (tcgen05 + TMA; needs lda, ldb, ldc multiples of 4 and
+ * 16-byte aligned bases).  Used by the parity tests and the kernel micro-benchmarks. */
+int dino_gemm_nt(int engine, const float* d_A, int64_t lda, const float* d_Bt, int64_t ldb, float* d_C,
+                 int64_t ldc, int32_t M, int32_t N, int32_t K, dino_stream_t stream);
+
 /* number of kernels this library has launched in the calling process (bench.py gpu_launches) */
 int64_t dino_launch_count(void);
 
