@@ -49,6 +49,30 @@ inline GemmOp gemm_op_zero() {
 
 // fp32 SIMT engine (exact-parity mode).  Returns a cudaError_t from the launch.
 cudaError_t launch_gemm_simt(const GemmOp& op, int num_sms, cudaStream_t st);
+// several independent split-K weight-gradient contractions in one launch (passed as a kernel parameter)
+constexpr int GEMM_GROUP_MAX = 24;
+struct GemmGroup { int n; int z_start[GEMM_GROUP_MAX + 1]; GemmOp ops[GEMM_GROUP_MAX]; };
+cudaError_t launch_gemm_simt_grouped(GemmGroup& g, int num_sms, cudaStream_t st);
+
+// Fused small-network MLP kernels (mlp_fused.cu): one CTA runs every layer for a tile of samples.
+struct MlpLayerDev {
+  long long koff, boff;        // parameter arena offsets (boff < 0: no bias)
+  long long z_off, sg_off, rs_off, da_off;   // workspace offsets (floats); < 0 when absent
+  int n_in, n_out, ld_out, act, trainable, skip_from, lands_skip;
+};
+constexpr int MLP_FUSED_MAX_LAYERS = 24;
+struct MlpNetDev {
+  int L, d_in, ld_in, lowest_trainable;
+  long long z0_off;            // gathered input [B, ld_in]
+  long long dz_top_off;        // dz_L = d loss / d q_hat [B, ld_dz]
+  int ld_dz;
+  MlpLayerDev layer[MLP_FUSED_MAX_LAYERS];
+};
+bool mlp_fused_supported(const MlpNetDev& net);
+cudaError_t launch_mlp_forward_fused(const MlpNetDev& net, const float* params, float* ws, const float* m,
+                                     const int* idx, int B, cudaStream_t st);
+cudaError_t launch_mlp_backward_fused(const MlpNetDev& net, const float* params, float* ws, float* grad, int B,
+                                      int with_rowsum, cudaStream_t st);
 // tcgen05 TF32 engine (gemm_tc.cu): both operands K-major (a_sk == b_sk == 1), 16-byte row pitches,
 // epilogue limited to add_pre / scale / add_post.  gemm_tc_supported() says whether an op qualifies.
 bool gemm_tc_supported(const GemmOp& op);

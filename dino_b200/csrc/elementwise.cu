@@ -257,35 +257,44 @@ cudaError_t launch_prep_weights(const float* params, float* ws, const PrepTable&
 
 // d sigma row-sum and per-sample scaling after a tensor-core data-gradient GEMM (its epilogue has no
 // cross-row reduction): one CTA per (sample, 64 columns), threads own columns, so no atomics.
-__global__ void __launch_bounds__(64) rowsum_scale_kernel(float* __restrict__ dq, long long ld_dq,
-                                                          const float* __restrict__ q, long long ld_q,
-                                                          const float* __restrict__ scale, long long ld_sc,
-                                                          const float* __restrict__ add_post, long long ld_apo,
-                                                          float* __restrict__ rowsum, long long ld_rs, int sdim, int n,
-                                                          int write_out, int round_out) {
-  const int c = blockIdx.x * 64 + threadIdx.x;
-  if (c >= n) return;
+__global__ void __launch_bounds__(256) rowsum_scale_kernel(float* __restrict__ dq, long long ld_dq,
+                                                           const float* __restrict__ q, long long ld_q,
+                                                           const float* __restrict__ scale, long long ld_sc,
+                                                           const float* __restrict__ add_post, long long ld_apo,
+                                                           float* __restrict__ rowsum, long long ld_rs, int sdim, int n,
+                                                           int write_out, int round_out) {
+  __shared__ float red[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
   const long long b = blockIdx.y;
-  const float sc = scale ? scale[b * ld_sc + c] : 1.f;
   float acc = 0.f;
+  if (c < n) {
+    const float sc = scale ? scale[b * ld_sc + c] : 1.f;
 #pragma unroll 4
-  for (int i = 0; i < sdim; ++i) {
-    const long long row = b * sdim + i;
-    const float v = dq[row * ld_dq + c];
-    acc = fmaf(v, q[row * ld_q + c], acc);
-    if (write_out) {
-      const float o = add_post ? fmaf(v, sc, add_post[row * ld_apo + c]) : v * sc;
-      dq[row * ld_dq + c] = round_out ? round_tf32_f(o) : o;
+    for (int i = threadIdx.y; i < sdim; i += 8) {
+      const long long row = b * sdim + i;
+      const float v = dq[row * ld_dq + c];
+      acc = fmaf(v, q[row * ld_q + c], acc);
+      if (write_out) {
+        const float o = add_post ? fmaf(v, sc, add_post[row * ld_apo + c]) : v * sc;
+        dq[row * ld_dq + c] = round_out ? round_tf32_f(o) : o;
+      }
     }
   }
-  if (rowsum) rowsum[b * ld_rs + c] = acc;
+  red[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < n && rowsum) {
+    float v = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) v += red[r][threadIdx.x];
+    rowsum[b * ld_rs + c] = v;
+  }
 }
 cudaError_t launch_rowsum_scale(float* dq, long long ld_dq, const float* q, long long ld_q, const float* scale,
                                 long long ld_sc, const float* add_post, long long ld_apo, float* rowsum,
                                 long long ld_rs, int B, int sdim, int n, int write_out, int round_tf32, cudaStream_t st) {
   if (B <= 0 || n <= 0) return cudaSuccess;
-  rowsum_scale_kernel<<<dim3(cdiv(n, 64), B), 64, 0, st>>>(dq, ld_dq, q, ld_q, scale, ld_sc, add_post, ld_apo,
-                                                            rowsum, ld_rs, sdim, n, write_out, round_tf32);
+  rowsum_scale_kernel<<<dim3(cdiv(n, 32), B), dim3(32, 8), 0, st>>>(dq, ld_dq, q, ld_q, scale, ld_sc, add_post, ld_apo,
+                                                                    rowsum, ld_rs, sdim, n, write_out, round_tf32);
   return cudaGetLastError();
 }
 

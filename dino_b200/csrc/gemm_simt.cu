@@ -16,7 +16,7 @@ constexpr int BK = 16;
 constexpr int NT = 256;
 
 template <int BM, int BN, int TM, int TN, bool A_KC, bool B_NC>
-__global__ void __launch_bounds__(NT) gemm_simt_kernel(const GemmOp op) {
+__device__ __forceinline__ void gemm_simt_tile(const GemmOp& op, const int bx, const int by, const int bz) {
   static_assert((BM / TM) * (BN / TN) == NT, "thread layout");
   constexpr int LDA_S = BM + 4, LDB_S = BN + 4;
   constexpr int A_PER_T = BM * BK / NT, B_PER_T = BK * BN / NT;
@@ -27,8 +27,8 @@ __global__ void __launch_bounds__(NT) gemm_simt_kernel(const GemmOp op) {
 
   const int tid = threadIdx.x;
   const int tx = tid % (BN / TN), ty = tid / (BN / TN);
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-  const int kbeg = blockIdx.z * op.k_per_split;
+  const int m0 = by * BM, n0 = bx * BN;
+  const int kbeg = bz * op.k_per_split;
   const int kend = min(op.K, kbeg + op.k_per_split);
   const int nk = (kend - kbeg + BK - 1) / BK;
 
@@ -213,6 +213,22 @@ __global__ void __launch_bounds__(NT) gemm_simt_kernel(const GemmOp op) {
   }
 }
 
+template <int BM, int BN, int TM, int TN, bool A_KC, bool B_NC>
+__global__ void __launch_bounds__(NT) gemm_simt_kernel(const GemmOp op) {
+  gemm_simt_tile<BM, BN, TM, TN, A_KC, B_NC>(op, blockIdx.x, blockIdx.y, blockIdx.z);
+}
+
+// Several independent split-K contractions (the weight gradients of every layer) in ONE launch:
+// blockIdx.z enumerates (op, K-split) pairs, CTAs outside an op's tile range exit.
+template <int BM, int BN, int TM, int TN, bool A_KC, bool B_NC>
+__global__ void __launch_bounds__(NT) gemm_simt_grouped_kernel(const __grid_constant__ GemmGroup g) {
+  int i = 0;
+  while (i + 1 < g.n && (int)blockIdx.z >= g.z_start[i + 1]) ++i;
+  const GemmOp& op = g.ops[i];
+  if ((int)blockIdx.x * BN >= op.N || (int)blockIdx.y * BM >= op.M) return;
+  gemm_simt_tile<BM, BN, TM, TN, A_KC, B_NC>(op, blockIdx.x, blockIdx.y, blockIdx.z - g.z_start[i]);
+}
+
 template <int BM, int BN, int TM, int TN>
 static cudaError_t launch_cfg(const GemmOp& op, int splits, cudaStream_t st) {
   dim3 grid((op.N + BN - 1) / BN, (op.M + BM - 1) / BM, splits);
@@ -249,6 +265,43 @@ cudaError_t launch_gemm_simt(const GemmOp& op_in, int num_sms, cudaStream_t st) 
   if (BM == 32) return launch_cfg<32, 64, 2, 4>(op, splits, st);
   if (BM == 64) return launch_cfg<64, 64, 4, 4>(op, splits, st);
   return launch_cfg<128, 64, 8, 4>(op, splits, st);
+}
+
+// All ops must be atomic-accumulate weight gradients with the same operand layout (A M-contiguous,
+// B N-contiguous).  Splits are sized so that the whole group fills the GPU about twice.
+cudaError_t launch_gemm_simt_grouped(GemmGroup& g, int num_sms, cudaStream_t st) {
+  if (g.n <= 0) return cudaSuccess;
+  int maxM = 0, maxN = 0;
+  long long total_work = 0;
+  for (int i = 0; i < g.n; ++i) {
+    const GemmOp& op = g.ops[i];
+    if (!op.atomic_c || op.a_sm != 1 || op.b_sn != 1) return cudaErrorInvalidValue;
+    maxM = op.M > maxM ? op.M : maxM;
+    maxN = op.N > maxN ? op.N : maxN;
+    total_work += (long long)op.K;
+  }
+  const int BM = 64;     // weight matrices are 50..100 wide at the headline configs: 64x64 tiles waste least
+  int z = 0, tiles_xy_max = 1;
+  for (int i = 0; i < g.n; ++i) {
+    GemmOp& op = g.ops[i];
+    const int tiles = ((op.M + BM - 1) / BM) * ((op.N + 63) / 64);
+    tiles_xy_max = tiles > tiles_xy_max ? tiles : tiles_xy_max;
+    const int kchunks = (op.K + BK - 1) / BK;
+    // share 2*num_sms CTAs between the ops in proportion to their reduction length
+    int splits = (int)((2LL * num_sms * op.K + total_work * tiles - 1) / (total_work * tiles));
+    if (splits > (kchunks + 1) / 2) splits = (kchunks + 1) / 2;
+    if (splits < 1) splits = 1;
+    int kps = (op.K + splits - 1) / splits;
+    kps = ((kps + BK - 1) / BK) * BK;
+    op.k_per_split = kps < BK ? BK : kps;
+    op.sdim = op.sdim > 0 ? op.sdim : 1;
+    g.z_start[i] = z;
+    z += (op.K + op.k_per_split - 1) / op.k_per_split;
+  }
+  g.z_start[g.n] = z;
+  dim3 grid((maxN + 63) / 64, (maxM + BM - 1) / BM, z);
+  gemm_simt_grouped_kernel<64, 64, 4, 4, false, true><<<grid, NT, 0, st>>>(g);
+  return cudaGetLastError();
 }
 
 }  // namespace dino

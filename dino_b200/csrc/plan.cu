@@ -59,6 +59,8 @@ struct LayerPlan {
   long long koff, boff;      // offsets in the parameter arena (floats)
   long long z_off, sg_off, q_off, rs_off;   // workspace offsets (floats); -1 when absent
   long long wp_off, wtp_off, ld_wp, ld_wtp; // TF32 mode: padded W [n_in][ld_wp] and W^T [n_out][ld_wtp]
+  long long dr_off;          // dR_{l+1} = gradient wrt the chain state above this layer [B*s, ld_out]; -1 for the top layer
+  long long da_off;          // da_l [B, ld_out] (fused MLP backward keeps every layer's for the grouped weight gradient)
   long long ld_out;          // r4(n_out)
   int lands_skip;            // index l2 of the skip layer whose source is THIS layer's input, or -1
 };
@@ -71,12 +73,14 @@ struct DinoPlan {
   bool seed_shared;          // FULL / OUT_REDUCED
   bool top_materialised;     // Q_{L-1} stored in the workspace (else it is the shared seed itself)
   // workspace offsets (floats)
-  long long off_ident, off_z0, off_r0, off_sk, off_dr[3], off_dz[3], off_da, off_rs_begin, rs_floats;
-  long long ld_in, ld_dr, ld_dz, ld_ident;
+  long long off_ident, off_z0, off_r0, off_sk, off_dz[3], off_da, off_rs_begin, rs_floats;
+  long long ld_in, ld_dz, ld_ident;
   long long ws_floats;
   float* ws;
   PrepTable prep;            // TF32 mode: weight staging table
   int max_in, max_out;
+  MlpNetDev mlp;             // descriptor of the fused small-network MLP kernels
+  bool mlp_fused;
 };
 
 static cudaStream_t S(dino_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
@@ -170,19 +174,38 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   for (int i = 0; i < 3; ++i) p->off_dz[i] = take(Bm * max_w);
   p->off_da = take(Bm * max_w);
   p->off_r0 = p->off_sk = -1;
-  p->ld_dr = 0;
-  for (int i = 0; i < 3; ++i) p->off_dr[i] = -1;
-  for (auto& lp : p->layers) lp.q_off = -1;
+  for (auto& lp : p->layers) { lp.q_off = -1; lp.dr_off = -1; lp.da_off = -1; }
   if (p->jac_mode != DINO_JAC_NONE) {
     for (int l = 0; l < p->L; ++l) {
       LayerPlan& lp = p->layers[l];
       if (l < p->L - 1 || p->top_materialised) lp.q_off = take(Ms * lp.ld_out);
-      if (l < p->L - 1 && lp.ld_out > p->ld_dr) p->ld_dr = lp.ld_out;
     }
     p->off_r0 = take(Ms * p->ld_in);
-    if (p->ld_dr > 0)
-      for (int i = 0; i < 3; ++i) p->off_dr[i] = take(Ms * p->ld_dr);
+    for (int l = 0; l < p->L - 1; ++l) p->layers[l].dr_off = take(Ms * p->layers[l].ld_out);
     if (p->jac_mode == DINO_JAC_SKETCHED) p->off_sk = take(Bm * (long long)p->s * p->s);
+  }
+  // fused small-network MLP path
+  {
+    MlpNetDev& n = p->mlp;
+    memset(&n, 0, sizeof(n));
+    n.L = p->L; n.d_in = p->d_in; n.ld_in = (int)p->ld_in; n.z0_off = p->off_z0;
+    n.dz_top_off = p->off_dz[p->L % 3]; n.ld_dz = (int)p->ld_dz;
+    n.lowest_trainable = p->L;
+    for (int l = 0; l < p->L; ++l)
+      if (p->layers[l].trainable) { n.lowest_trainable = l; break; }
+    p->mlp_fused = p->L <= MLP_FUSED_MAX_LAYERS;
+    if (p->mlp_fused) {
+      for (int l = 0; l < p->L; ++l) {
+        LayerPlan& lp = p->layers[l];
+        lp.da_off = take(Bm * lp.ld_out);
+        MlpLayerDev& d = n.layer[l];
+        d.koff = lp.koff; d.boff = lp.boff; d.z_off = lp.z_off; d.sg_off = lp.sg_off; d.rs_off = lp.rs_off;
+        d.da_off = lp.da_off; d.n_in = lp.n_in; d.n_out = lp.n_out; d.ld_out = (int)lp.ld_out;
+        d.act = lp.act == DINO_ACT_SOFTPLUS; d.trainable = lp.trainable; d.skip_from = lp.skip_from;
+        d.lands_skip = lp.lands_skip;
+      }
+      p->mlp_fused = mlp_fused_supported(n);
+    }
   }
   p->prep.n = 0;
   p->max_in = p->max_out = 1;
@@ -257,6 +280,10 @@ static int gemm(const DinoPlan* p, const GemmOp& op, cudaStream_t st) {
 
 static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b, int B, cudaStream_t st) {
   float* ws = p->ws;
+  if (p->mlp_fused) {
+    DINO_LAUNCH(launch_mlp_forward_fused(p->mlp, params, ws, b->m, b->idx, B, st));
+    return 0;
+  }
   DINO_LAUNCH(launch_gather_rows(b->m, b->idx, B, p->d_in, p->d_in, ws + p->off_z0, p->ld_in, st));
   const float* zin = ws + p->off_z0;
   long long ld_zin = p->ld_in;
@@ -360,12 +387,29 @@ static int run_losses(DinoPlan* p, const DinoBatch* b, int B, float w_l2, float 
   return 0;
 }
 
-static int run_chain_backward(DinoPlan* p, const float* params, int B, float* grad, const TopQ& top, cudaStream_t st) {
+// Appends one weight-gradient contraction to the pending group; flushes the group when it is full.
+static int push_wgrad(DinoPlan* p, GemmGroup& g, const GemmOp& op, cudaStream_t st) {
+  if (g.n == GEMM_GROUP_MAX) {
+    DINO_LAUNCH(launch_gemm_simt_grouped(g, p->num_sms, st));
+    g.n = 0;
+  }
+  g.ops[g.n++] = op;
+  return 0;
+}
+static int flush_wgrad(DinoPlan* p, GemmGroup& g, cudaStream_t st) {
+  if (g.n > 0) DINO_LAUNCH(launch_gemm_simt_grouped(g, p->num_sms, st));
+  g.n = 0;
+  return 0;
+}
+
+static int run_chain_backward(DinoPlan* p, const float* params, int B, float* grad, const TopQ& top, GemmGroup& wg,
+                              cudaStream_t st) {
   float* ws = p->ws;
   const int s = p->s, L = p->L, M = B * s;
-  // dR_l lives in: l == 0 -> R0 buffer; l >= 1 -> off_dr[(l-1) % 3]
-  auto dr_ptr = [&](int l) { return l == 0 ? ws + p->off_r0 : ws + p->off_dr[(l - 1) % 3]; };
-  auto dr_ld = [&](int l) { return l == 0 ? p->ld_in : p->ld_dr; };
+  // dR_l (gradient wrt the chain state entering layer l from below): l == 0 -> R0 buffer (holds G);
+  // l >= 1 -> the buffer of layer l-1.  All are kept: the weight gradients run afterwards in one launch.
+  auto dr_ptr = [&](int l) { return l == 0 ? ws + p->off_r0 : ws + p->layers[l - 1].dr_off; };
+  auto dr_ld = [&](int l) { return l == 0 ? p->ld_in : p->layers[l - 1].ld_out; };
   for (int l = 0; l < L; ++l) {
     const LayerPlan& lp = p->layers[l];
     const float* q; long long ldq; int qmod;
@@ -377,7 +421,7 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
       op.B = q; op.b_sk = ldq; op.b_sn = 1; op.b_kmod = qmod;
       op.M = lp.n_in; op.N = lp.n_out; op.K = M;
       op.C = grad + lp.koff; op.ldc = lp.n_out; op.atomic_c = 1;
-      if (gemm(p, op, st)) return 1;
+      if (push_wgrad(p, wg, op, st)) return 1;
     }
     const bool need_rs = lp.act == DINO_ACT_SOFTPLUS;
     const bool need_out = l < L - 1;
@@ -387,7 +431,7 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
     op.M = M; op.N = lp.n_out; op.K = lp.n_in; op.sdim = s;
     const float* skip_add = nullptr; long long ld_skip = 0;
     if (need_out && lp.skip_from >= 0) { skip_add = dr_ptr(lp.skip_from); ld_skip = dr_ld(lp.skip_from); }
-    if (p->precision == DINO_PREC_TF32 && need_out && lp.n_out <= p->ld_dr) {
+    if (p->precision == DINO_PREC_TF32 && need_out) {
       // tensor-core path: dQ_l = dR_l W_l with the K-major copy W_l^T; the cross-row d sigma sum and the
       // per-sample scaling follow in one pass over the tile (rowsum_scale_kernel)
       op.B = ws + lp.wtp_off; op.b_sk = 1; op.b_sn = lp.ld_wtp;
@@ -414,9 +458,26 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
   return 0;
 }
 
-static int run_mlp_backward(DinoPlan* p, const float* params, int B, float* grad, cudaStream_t st) {
+static int run_mlp_backward(DinoPlan* p, const float* params, int B, float* grad, GemmGroup& wg, cudaStream_t st) {
   float* ws = p->ws;
   const int L = p->L;
+  if (p->mlp_fused) {
+    // one launch produces da_l for every layer (and the bias gradients); the weight gradients
+    // dW_l += z_l^T da_l join the chain's in the grouped launch
+    DINO_LAUNCH(launch_mlp_backward_fused(p->mlp, params, ws, grad, B, p->jac_mode != DINO_JAC_NONE ? 1 : 0, st));
+    for (int l = p->mlp.lowest_trainable; l < L; ++l) {
+      const LayerPlan& lp = p->layers[l];
+      if (!lp.trainable) continue;
+      GemmOp op = gemm_op_zero();
+      op.A = l == 0 ? ws + p->off_z0 : ws + p->layers[l - 1].z_off;
+      op.a_sm = 1; op.a_sk = l == 0 ? p->ld_in : p->layers[l - 1].ld_out;
+      op.B = ws + lp.da_off; op.b_sk = lp.ld_out; op.b_sn = 1;
+      op.M = lp.n_in; op.N = lp.n_out; op.K = B;
+      op.C = grad + lp.koff; op.ldc = lp.n_out; op.atomic_c = 1;
+      if (push_wgrad(p, wg, op, st)) return 1;
+    }
+    return 0;
+  }
   auto dz_ptr = [&](int l) { return ws + p->off_dz[l % 3]; };
   int lowest_trainable = L;
   for (int l = 0; l < L; ++l)
@@ -498,9 +559,11 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
   TopQ top = {nullptr, 0, 0};
   if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
   if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st)) return 1;
-  if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, st)) return 1;
-  if (run_mlp_backward(p, params, B, grad, st)) return 1;
-  return 0;
+  GemmGroup wg;
+  wg.n = 0;
+  if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, wg, st)) return 1;
+  if (run_mlp_backward(p, params, B, grad, wg, st)) return 1;
+  return flush_wgrad(p, wg, st);
 }
 
 extern "C" int dino_h1_eval(DinoPlan* p, const float* params, const DinoBatch* b, int32_t B, float* stats,
