@@ -56,6 +56,10 @@ SIGNATURES = {
     "dino_h1_eval": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(DinoBatch), C.c_int32, C.c_void_p, C.c_void_p]),
     "dino_adam": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
                             C.c_float, C.c_float, C.c_int64, C.c_void_p]),
+    "dino_stage_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
+    "dino_adam_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
+                                C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
+    "dino_roll_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "dino_sgd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p]),
     "dino_sample_sqnorms": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]),
     "dino_forward_noalloc": (C.c_int, [C.POINTER(DinoNetSpec), C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,

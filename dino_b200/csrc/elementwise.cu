@@ -425,6 +425,51 @@ cudaError_t launch_sgd(float* p, const float* g, long long n, float lr, cudaStre
   return cudaGetLastError();
 }
 
+// ---- device-side cursors: let a CUDA graph of the training step be replayed with no host arguments ----
+// idx_stage[i] = idx_all[*pos + i]
+__global__ void stage_batch_kernel(const int* __restrict__ idx_all, const int* __restrict__ pos, int* __restrict__ idx_stage, int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B) idx_stage[i] = idx_all[*pos + i];
+}
+cudaError_t launch_stage_batch(const int* idx_all, const int* pos, int* idx_stage, int B, cudaStream_t st) {
+  if (B <= 0) return cudaSuccess;
+  stage_batch_kernel<<<cdiv(B, 256), 256, 0, st>>>(idx_all, pos, idx_stage, B);
+  return cudaGetLastError();
+}
+// hist[*step] = stage; stage = 0; *pos += advance; *step += 1; *t += 1
+__global__ void roll_stats_kernel(float* stage, float* hist, int* pos, int advance, int* step, long long* t) {
+  const int i = threadIdx.x;
+  const int s = *step;
+  if (i < ST_SLOTS) { hist[(long long)s * ST_SLOTS + i] = stage[i]; stage[i] = 0.f; }
+  __syncthreads();
+  if (i == 0) { *pos += advance; *step = s + 1; *t += 1; }
+}
+cudaError_t launch_roll_stats(float* stage, float* hist, int* pos, int advance, int* step, long long* t, cudaStream_t st) {
+  roll_stats_kernel<<<1, 32, 0, st>>>(stage, hist, pos, advance, step, t);
+  return cudaGetLastError();
+}
+// Adam whose step number lives on the device: t = *t_done + 1
+__global__ void adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                float* __restrict__ v, long long n, float lr, float b1, float b2, float eps,
+                                const long long* __restrict__ t_done) {
+  const double t = (double)(*t_done + 1);
+  const float lr_t = (float)((double)lr * sqrt(1.0 - pow((double)b2, t)) / (1.0 - pow((double)b1, t)));
+  const float ob1 = 1.f - b1, ob2 = 1.f - b2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float G = g[i];
+    const float M = b1 * m[i] + ob1 * G;
+    const float V = b2 * v[i] + ob2 * G * G;
+    m[i] = M; v[i] = V;
+    p[i] -= lr_t * M / (sqrtf(V) + eps);
+  }
+}
+cudaError_t launch_adam_dev(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
+                            float eps, const long long* t_done, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  adam_dev_kernel<<<min(cdiv(n, 256), 148 * 4), 256, 0, st>>>(p, g, m, v, n, lr, b1, b2, eps, t_done);
+  return cudaGetLastError();
+}
+
 // out[i] = sum_j x[i,j]^2 : one CTA per row (rows are Jacobians of 2.5k .. 1.7M floats, or q rows)
 __global__ void __launch_bounds__(256) sqnorms_kernel(const float* __restrict__ x, long long len,
                                                       float* __restrict__ out) {

@@ -586,6 +586,29 @@ extern "C" int dino_adam(float* params, const float* grad, float* m, float* v, i
   return 0;
 }
 
+extern "C" int dino_adam_dev(float* params, const float* grad, float* m, float* v, int64_t count, float lr, float b1,
+                             float b2, float eps, const int64_t* d_steps_done, dino_stream_t stream) {
+  if (!params || !grad || !m || !v || !d_steps_done) return fail("dino_adam_dev: null argument");
+  DINO_LAUNCH(launch_adam_dev(params, grad, m, v, count, lr, b1, b2, eps,
+                              reinterpret_cast<const long long*>(d_steps_done), S(stream)));
+  return 0;
+}
+
+extern "C" int dino_stage_batch(const int32_t* d_idx_all, const int32_t* d_pos, int32_t* d_idx_stage, int32_t B,
+                                dino_stream_t stream) {
+  if (!d_idx_all || !d_pos || !d_idx_stage) return fail("dino_stage_batch: null argument");
+  DINO_LAUNCH(launch_stage_batch(d_idx_all, d_pos, d_idx_stage, B, S(stream)));
+  return 0;
+}
+
+extern "C" int dino_roll_stats(float* d_stats_stage, float* d_stats_hist, int32_t* d_pos, int32_t advance,
+                               int32_t* d_step, int64_t* d_steps_done, dino_stream_t stream) {
+  if (!d_stats_stage || !d_stats_hist || !d_pos || !d_step || !d_steps_done) return fail("dino_roll_stats: null argument");
+  DINO_LAUNCH(launch_roll_stats(d_stats_stage, d_stats_hist, d_pos, advance, d_step,
+                                reinterpret_cast<long long*>(d_steps_done), S(stream)));
+  return 0;
+}
+
 extern "C" int dino_sgd(float* params, const float* grad, int64_t count, float lr, dino_stream_t stream) {
   if (!params || !grad) return fail("dino_sgd: null argument");
   DINO_LAUNCH(launch_sgd(params, grad, count, lr, S(stream)));

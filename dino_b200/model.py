@@ -310,6 +310,152 @@ class DeviceDataset:
                               p(self.U), p(self.V), None if self.seed is None else self.seed.data_ptr())
 
 
+class TrainEngine:
+    """Static device state of a training run and the CUDA graphs of its step.
+
+    Everything a step consumes lives at fixed device addresses: the epoch's permutation, a cursor into
+    it, the staged sample indices of the current minibatch, the statistics row, the flat gradient and
+    the optimiser step counter.  The step (stage indices -> dino_h1_fwd_bwd -> [all-reduce] ->
+    optimiser -> roll cursors) therefore has no host-side arguments that change from step to step and
+    is captured once per minibatch size in a CUDA graph; afterwards a step costs the host one graph
+    launch.  The first step of every size runs eagerly (it also triggers one-time kernel attribute
+    set-up inside the library, which may not happen during capture)."""
+
+    def __init__(self, model: "DinoModel", ds: "DeviceDataset", batch_size: int, use_graph: bool = True):
+        import torch
+        self.model, self.ds = model, ds
+        self.dp = parallel.context()
+        self.lib = _lib.load()
+        core = model.core
+        self.params = core.device_params()
+        dev = self.params.device
+        self.batch_size = int(batch_size)
+        self.steps_cap = (ds.n + self.batch_size - 1) // self.batch_size
+        local_max = -(-min(self.batch_size, ds.n) // self.dp.world)
+        self.plan = model._plan(max(local_max, 1))
+        model._ensure_opt_state()
+        opt = model.optimizer
+        if getattr(opt, "_t_dev", None) is None or opt._t_dev.device != dev:
+            opt._t_dev = torch.tensor([opt.iterations], dtype=torch.int64, device=dev)
+        self.idx_all = torch.zeros(ds.n, dtype=torch.int32, device=dev)
+        self.cursors = torch.zeros(2, dtype=torch.int32, device=dev)          # [pos, step]
+        self.idx_stage = torch.zeros(max(local_max, 1), dtype=torch.int32, device=dev)
+        self.stats_stage = torch.zeros(_lib.STAT_SLOTS, dtype=torch.float32, device=dev)
+        self.stats_hist = torch.zeros(self.steps_cap + 1, _lib.STAT_SLOTS, dtype=torch.float32, device=dev)
+        self.grad = torch.zeros(core.n_params, dtype=torch.float32, device=dev)
+        self.batch_struct = ds.batch(self.idx_stage.data_ptr())
+        self.use_graph = use_graph and os.environ.get("DINO_B200_NO_GRAPH", "0") != "1"
+        self.graphs = {}           # Bg -> (CUDAGraph, key, kernels per replay)
+        self.replayed_kernels = 0  # kernels of ours executed through graph replays
+        self.captured_kernels = 0  # kernels recorded during capture (the library counted them, they did not run)
+        self.seen = set()
+        self.host_pos = 0
+        self.host_step = 0
+
+    def set_order(self, order: np.ndarray):
+        """Install the sample order of the next epoch and rewind the cursors."""
+        import torch
+        t = torch.from_numpy(np.ascontiguousarray(order, dtype=np.int32))
+        self.idx_all[:t.numel()].copy_(t, non_blocking=False)
+        self.cursors.zero_()
+        self.stats_stage.zero_()
+        self.n_order = int(t.numel())
+        self.host_pos = 0
+        self.host_step = 0
+
+    def rewind(self):
+        """Walk the installed order again from the start (asynchronous; no host->device traffic)."""
+        self.cursors.zero_()
+        self.stats_stage.zero_()
+        self.host_pos = 0
+        self.host_step = 0
+
+    def remaining(self) -> int:
+        return self.n_order - self.host_pos
+
+    def _key(self):
+        opt = self.model.optimizer
+        return (opt.kind, float(opt.learning_rate), tuple(self.model.loss_weights))
+
+    def _enqueue(self, Bg: int):
+        lib, m = self.lib, self.model
+        opt, P = m.optimizer, m.core.n_params
+        st = _stream()
+        off, Bl = parallel.shard_bounds(Bg, self.dp.rank, self.dp.world)
+        pos_ptr, step_ptr = self.cursors.data_ptr(), self.cursors.data_ptr() + 4
+        if Bl > 0:
+            _lib.check(lib.dino_stage_batch(C.c_void_p(self.idx_all.data_ptr() + 4 * off), C.c_void_p(pos_ptr),
+                                            C.c_void_p(self.idx_stage.data_ptr()), Bl, st), "dino_stage_batch")
+            _lib.check(lib.dino_h1_fwd_bwd(self.plan.handle, C.c_void_p(self.params.data_ptr()),
+                                           C.byref(self.batch_struct), Bl, m.loss_weights[0], m.loss_weights[1],
+                                           1.0 / Bg, C.c_void_p(self.grad.data_ptr()),
+                                           C.c_void_p(self.stats_stage.data_ptr()), st), "dino_h1_fwd_bwd")
+        else:
+            self.grad.zero_()
+        if self.dp.world > 1:
+            self.dp.all_reduce_sum(self.grad)
+        if opt.kind == "adam":
+            _lib.check(lib.dino_adam_dev(C.c_void_p(self.params.data_ptr()), C.c_void_p(self.grad.data_ptr()),
+                                         C.c_void_p(opt._m.data_ptr()), C.c_void_p(opt._v.data_ptr()), P,
+                                         opt.learning_rate, opt.beta_1, opt.beta_2, opt.epsilon,
+                                         C.c_void_p(opt._t_dev.data_ptr()), st), "dino_adam_dev")
+        else:
+            _lib.check(lib.dino_sgd(C.c_void_p(self.params.data_ptr()), C.c_void_p(self.grad.data_ptr()), P,
+                                    opt.learning_rate, st), "dino_sgd")
+        _lib.check(lib.dino_roll_stats(C.c_void_p(self.stats_stage.data_ptr()), C.c_void_p(self.stats_hist.data_ptr()),
+                                       C.c_void_p(pos_ptr), Bg, C.c_void_p(step_ptr),
+                                       C.c_void_p(opt._t_dev.data_ptr()), st), "dino_roll_stats")
+
+    def step(self, Bg: int = None):
+        """One optimiser step on the next Bg samples of the installed order.  Asynchronous."""
+        import torch
+        Bg = self.batch_size if Bg is None else int(Bg)
+        if Bg > self.remaining() or self.host_step >= self.steps_cap + 1:
+            raise RuntimeError("TrainEngine.step: not enough samples left in the installed order")
+        key = self._key()
+        entry = self.graphs.get(Bg)
+        if entry is not None and entry[1] != key:
+            entry = None
+            self.graphs.pop(Bg)
+        if entry is not None:
+            entry[0].replay()
+            self.replayed_kernels += entry[2]
+        elif self.use_graph and (Bg, key) in self.seen:
+            try:
+                g = torch.cuda.CUDAGraph()
+                cur = torch.cuda.current_stream()
+                side = torch.cuda.Stream()
+                side.wait_stream(cur)
+                before = _lib.launch_count()
+                with torch.cuda.graph(g, stream=side):
+                    self._enqueue(Bg)
+                cur.wait_stream(side)
+                kernels = _lib.launch_count() - before          # our kernel nodes in the captured step
+                self.graphs[Bg] = (g, key, kernels)
+                self.captured_kernels += kernels                # counted by the library but not executed
+                g.replay()
+                self.replayed_kernels += kernels
+            except Exception:
+                self.use_graph = False          # e.g. a collective that cannot be captured: stay eager
+                torch.cuda.synchronize()
+                self._enqueue(Bg)
+        else:
+            self._enqueue(Bg)
+            self.seen.add((Bg, key))
+        self.host_pos += Bg
+        self.host_step += 1
+        self.model.optimizer.iterations += 1
+        self.model.core.mark_device_updated()
+
+    def epoch_stats(self) -> np.ndarray:
+        """Per-step statistics rows of the steps run since set_order (synchronises)."""
+        if self.dp.world > 1:
+            h = self.stats_hist[:self.host_step].clone()
+            self.dp.all_reduce_sum(h)
+            return h.cpu().numpy()
+        return self.stats_hist[:self.host_step].cpu().numpy()
+
+
 class History:
     def __init__(self):
         self.history: Dict[str, List[float]] = {}
@@ -551,6 +697,8 @@ class DinoModel:
         if dp.world > 1:
             dp.all_reduce_sum(grad)
         opt.iterations += 1
+        if getattr(opt, "_t_dev", None) is not None:
+            opt._t_dev += 1
         if opt.kind == "adam":
             _lib.check(lib.dino_adam(C.c_void_p(params.data_ptr()), C.c_void_p(grad.data_ptr()),
                                      C.c_void_p(opt._m.data_ptr()), C.c_void_p(opt._v.data_ptr()), P,
@@ -565,20 +713,11 @@ class DinoModel:
         """Upload (x, y) to HBM once; the result can be passed to fit / evaluate / train_on_indices."""
         return self._dataset(x, y)
 
-    def train_on_indices(self, ds, idx_dev, lo, Bg, stats_row=None):
-        """One optimiser step on the global minibatch ds[idx_dev[lo:lo+Bg]] (device int32 indices),
-        sharded over the data-parallel ranks.  No host synchronisation."""
-        import torch
-        dp = parallel.context()
-        off, Bl = parallel.shard_bounds(Bg, dp.rank, dp.world)
-        plan = self._plan(max(-(-Bg // dp.world), 1))
-        self._ensure_opt_state()
-        if getattr(self, "_grad", None) is None or self._grad.numel() != self.core.n_params:
-            self._grad = torch.zeros(self.core.n_params, dtype=torch.float32, device=self.core.device_params().device)
-            self._scratch_stats = torch.zeros(_lib.STAT_SLOTS, dtype=torch.float32, device=self._grad.device)
-        row = self._scratch_stats if stats_row is None else stats_row
-        batch = ds.batch(idx_dev.data_ptr() + 4 * (lo + off)) if Bl > 0 else None
-        self._train_step(plan, batch, Bl, Bg, self._grad, row, dp, _stream())
+    def make_engine(self, ds, batch_size, use_graph=True) -> TrainEngine:
+        """A TrainEngine over a resident dataset: ``set_order(perm)`` then ``step()`` per minibatch."""
+        if not self._compiled:
+            raise RuntimeError("You must compile your model before training/testing.")
+        return TrainEngine(self, ds, batch_size, use_graph)
 
     def train_on_batch(self, x, y, **_ignored):
         """Keras ``train_on_batch``: one optimiser step on HOST arrays.  Under data parallelism each
@@ -647,34 +786,25 @@ class DinoModel:
         order, a short last batch averaged over its own size, validation after every epoch.
         With torch.distributed initialised every global minibatch is split contiguously over the
         ranks and the flat gradient is sum-all-reduced before the (replicated) optimiser step."""
-        import torch
         if not self._compiled:
             raise RuntimeError("You must compile your model before training/testing.")
-        lib = _lib.load()
         ds = x if isinstance(x, DeviceDataset) else self._dataset(x, y)
         val = None
         if validation_data is not None:
             val = self._dataset(validation_data[0], validation_data[1])
         dp = parallel.context()
-        n, P = ds.n, self.core.n_params
-        params = self.core.device_params()
-        dev = params.device
-        local_max = -(-min(batch_size, n) // dp.world)
-        plan = self._plan(max(local_max, 1))
-        self._ensure_opt_state()
-        grad = torch.zeros(P, dtype=torch.float32, device=dev)
+        n = ds.n
+        eng = TrainEngine(self, ds, batch_size)
         steps = (n + batch_size - 1) // batch_size
         hist = History()
         names = self.metrics_names
         jac = self.jac_mode != _lib.JAC_NONE
-        w0, w1 = self.loss_weights[0], self.loss_weights[1]
         callbacks = callbacks or []
         for cb in callbacks:
             if hasattr(cb, "set_model"):
                 cb.set_model(self)
             if hasattr(cb, "on_train_begin"):
                 cb.on_train_begin({})
-        st = _stream()
         for epoch in range(initial_epoch, epochs):
             if perms is not None:
                 order = np.asarray(perms[epoch - initial_epoch])
@@ -684,21 +814,13 @@ class DinoModel:
                 order = np.arange(n)
             if dp.world > 1:
                 order = dp.broadcast_order(order)
-            idx = torch.from_numpy(np.ascontiguousarray(order, dtype=np.int32)).to(dev)
-            stats = torch.zeros(steps, _lib.STAT_SLOTS, dtype=torch.float32, device=dev)
+            eng.set_order(order)
             for cb in callbacks:
                 if hasattr(cb, "on_epoch_begin"):
                     cb.on_epoch_begin(epoch, {})
             for step in range(steps):
-                lo = step * batch_size
-                Bg = min(batch_size, n - lo)
-                off, Bl = parallel.shard_bounds(Bg, dp.rank, dp.world)
-                batch = ds.batch(idx.data_ptr() + 4 * (lo + off)) if Bl > 0 else None
-                self._train_step(plan, batch, Bl, Bg, grad, stats[step], dp, st)
-            self.core.mark_device_updated()
-            if dp.world > 1:
-                dp.all_reduce_sum(stats)
-            vals = _combine_stats(stats.cpu().numpy(), self.loss_weights, jac)
+                eng.step(min(batch_size, n - step * batch_size))
+            vals = _combine_stats(eng.epoch_stats(), self.loss_weights, jac)
             logs = dict(zip(names, vals))
             if val is not None:
                 vv = _combine_stats(self._eval_stats(val, batch_size), self.loss_weights, jac)

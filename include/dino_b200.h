@@ -124,6 +124,19 @@ int dino_h1_eval(DinoPlan* plan, const float* d_params, const DinoBatch* batch, 
  * g == 0 and m == v == 0 and therefore do not move. */
 int dino_adam(float* d_params, const float* d_grad, float* d_m, float* d_v, int64_t count,
               float lr, float beta1, float beta2, float eps, int64_t t, dino_stream_t stream);
+/* Device-side cursors, so that a whole training step can be captured once in a CUDA graph and replayed
+ * without host-supplied arguments (the Keras fit loop, trainingUtilities.py:135, feeds slices of a
+ * shuffled index array; here that slicing happens on the device):
+ *   dino_stage_batch : d_idx_stage[i] = d_idx_all[*d_pos + i], i < B        (this step's sample indices)
+ *   dino_adam_dev    : dino_adam with t = *d_steps_done + 1 read on the device
+ *   dino_roll_stats  : d_stats_hist[*d_step] = d_stats_stage; d_stats_stage = 0; *d_pos += advance;
+ *                      *d_step += 1; *d_steps_done += 1                     (end of step) */
+int dino_stage_batch(const int32_t* d_idx_all, const int32_t* d_pos, int32_t* d_idx_stage, int32_t B,
+                     dino_stream_t stream);
+int dino_adam_dev(float* d_params, const float* d_grad, float* d_m, float* d_v, int64_t count, float lr,
+                  float beta1, float beta2, float eps, const int64_t* d_steps_done, dino_stream_t stream);
+int dino_roll_stats(float* d_stats_stage, float* d_stats_hist, int32_t* d_pos, int32_t advance, int32_t* d_step,
+                    int64_t* d_steps_done, dino_stream_t stream);
 /* Keras SGD (trainingUtilities.py:92): p -= lr g. */
 int dino_sgd(float* d_params, const float* d_grad, int64_t count, float lr, dino_stream_t stream);
 

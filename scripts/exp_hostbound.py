@@ -16,30 +16,20 @@ for B in (32, 256, 1024):
     model.compile(optimizer=Adam(1e-3), loss=[normalized_mse, normalized_mse_matrix], loss_weights=[1.0, 1.0],
                   metrics=[l2_accuracy, f_accuracy_matrix])
     ds = model.make_dataset([data["m"]], [data["q"], data["J"]])
-    idx = torch.arange(4096, dtype=torch.int32, device="cuda")
-    for i in range(10):
-        model.train_on_indices(ds, idx, 0, B)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for i in range(100):
-        model.train_on_indices(ds, idx, 0, B)
-    t_enq = time.perf_counter() - t0
-    torch.cuda.synchronize()
-    t_all = time.perf_counter() - t0
-    s = torch.cuda.Stream()
-    with torch.cuda.stream(s):
-        model.train_on_indices(ds, idx, 0, B)
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g, stream=s):
-            model.train_on_indices(ds, idx, 0, B)
-        for i in range(5):
-            g.replay()
+    order = np.arange(4096, dtype=np.int32)
+    for graph in (False, True):
+        eng = model.make_engine(ds, B, use_graph=graph)
+        eng.set_order(order)
+        def run(k):
+            for i in range(k):
+                if eng.remaining() < B:
+                    eng.rewind()
+                eng.step(B)
+        run(10)
         torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(s)
-        for i in range(200):
-            g.replay()
-        e1.record(s)
+        t0 = time.perf_counter()
+        run(200)
+        t_enq = time.perf_counter() - t0
         torch.cuda.synchronize()
-    print(f"B={B}: eager enqueue {t_enq*10:.3f} ms/step, eager total {t_all*10:.3f} ms/step, "
-          f"graph replay {e0.elapsed_time(e1)/200:.3f} ms/step", flush=True)
+        t_all = time.perf_counter() - t0
+        print(f"B={B} graph={graph}: host enqueue {t_enq*5:.3f} ms/step, total {t_all*5:.3f} ms/step", flush=True)
