@@ -108,8 +108,7 @@ def cpu_reference_rate(arch, data, weights, batch, seconds, max_steps=None, thre
     import torch
     import helpers as H
     from oracle import dino_oracle as O
-    if threads:
-        torch.set_num_threads(threads)
+    torch.set_num_threads(threads or os.cpu_count() or 1)
     net = H.oracle_net(arch, weights, dtype=torch.float32)
     opt = O.KerasAdam(net.trainable_tensors(), 1e-3)
     n = data["m"].shape[0]
@@ -145,6 +144,8 @@ def run_reference(args, arch, batch):
     w = H.student_weights(arch, 1234 + 2, tw)
     import torch
     from oracle import dino_oracle as O
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm is entitled to every host core
+    torch.set_num_threads(os.cpu_count() or 1)
     net = H.oracle_net(arch, w, dtype=torch.float32)
     opt = O.KerasAdam(net.trainable_tensors(), 1e-3)
     full = H.oracle_batch(data, None, dtype=torch.float32)
@@ -296,7 +297,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": workload_name(args.config, arch, batch), "per_gpu_batch": batch,
                        "global_batch": Bg, "resident_samples": n, "optimizer": "adam", "precision": args.precision,
-                       "parallelism": f"dp{world}",
+                       "parallelism": f"dp{world}", "cuda_graph_step": bool(eng.use_graph and eng.graphs),
                        "l2_policy": f"inputs larger than L2: {dataset_bytes / 1e6:.0f} MB dataset cycled, "
                                     f"a different minibatch every step"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

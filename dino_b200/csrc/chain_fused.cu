@@ -1,0 +1,475 @@
+// Fused Jacobian-chain kernel (tcgen05 + TMA): forward chain, H1 loss and backward chain for a tile
+// of samples in ONE CTA, for networks whose widths fit one UMMA tile (<= 128; every BASELINE
+// reduced-basis config with r <= 128).
+//
+// A CTA owns G = floor(128/s) whole samples = G*s <= 128 chain rows (s seed rows per sample).  The
+// current chain state X [128 rows, K <= 128] lives in shared memory in the UMMA K-major SWIZZLE_128B
+// layout; it is the A operand of every contraction.  Per layer one elected thread waits for the
+// layer's weight tile (TMA, double-buffered, prefetched one layer ahead), issues tcgen05.mma
+// kind::tf32 into a TMEM accumulator and commits to an mbarrier; the 128 epilogue threads (thread =
+// chain row = TMEM lane) read the accumulator with tcgen05.ld, apply the per-sample sigmoid scaling /
+// residual adds / loss, write the result BACK INTO X as the next layer's operand and stream it to
+// global memory once (Q_l and dR_l are needed later by the weight-gradient launch).  No chain state
+// is ever re-read from global memory inside the kernel except Q_l in the backward epilogue.
+//
+//   forward  l = L-1..0 :  R_l = X W_l^T (+ Q_skip) ;  X <- Q_{l-1} = R_l * sg_{l-1}      (X_0 = seed)
+//   loss                :  X <- G = coef (R_0 - J) / ||J_b||^2 ; statistics
+//   backward l = 0..L-1 :  dQ_l = X W_l ; rs_l[b,:] = sum_rows dQ_l * Q_l ; X <- dR_{l+1} = dQ_l * sg_l (+ dR_skip)
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace dino {
+
+constexpr int CF_ROWS = 128, CF_MAXW = 128, CF_CHUNK_BYTES = CF_ROWS * 128;       // 16 KB per 32-float K chunk
+constexpr int CF_X_BYTES = (CF_MAXW / 32) * CF_CHUNK_BYTES;                        // 64 KB
+constexpr int CF_EPI = 256;                                                        // 8 epilogue warps: 2 per TMEM lane quarter
+constexpr int CF_THREADS = CF_EPI + 32;                                            // + 1 control warp
+
+__device__ __forceinline__ uint32_t cf_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cf_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(cf_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void cf_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(cf_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cf_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(cf_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void cf_mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "CF_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra CF_DONE;\n\t"
+      "bra CF_WAIT;\n\t"
+      "CF_DONE:\n\t"
+      "}" ::"r"(cf_smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void cf_tma_load(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(cf_smem_u32(dst)), "l"(map), "r"(cf_smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void cf_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(cf_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void cf_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ uint64_t cf_desc(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void cf_tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+}
+// byte offset of (row r, float column k..k+3, k % 4 == 0) inside X (K-major, 128-byte rows, SWIZZLE_128B)
+__device__ __forceinline__ uint32_t cf_xoff(int r, int k) {
+  const int c = k >> 5, j = (k & 31) >> 2;
+  return (uint32_t)(c * CF_CHUNK_BYTES + (r >> 3) * 1024 + (r & 7) * 128 + ((j ^ (r & 7)) << 4));
+}
+// After the call lane j holds sum over the 32 lanes of v[j] (31 shuffles instead of 160).
+__device__ __forceinline__ float cf_colsum32(float* v, int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = up ? v[i] : v[i + off];
+      const float keep = up ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
+__global__ void __launch_bounds__(CF_THREADS, 1)
+chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ ChainNetDev net,
+                   float* __restrict__ ws, const float* __restrict__ jt, const float* __restrict__ jn2,
+                   const int* __restrict__ idx, const float* __restrict__ seed, int B, float coef, int do_loss,
+                   int do_backward, float* __restrict__ stats) {
+  extern __shared__ uint8_t cf_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cf_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* X = smem;
+  uint8_t* Wb[2] = {smem + CF_X_BYTES, smem + 2 * CF_X_BYTES};
+  uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + 3 * CF_X_BYTES);     // [2]
+  uint64_t* mma_done = w_full + 2;
+  uint64_t* x_ready = w_full + 3;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 4);
+  float* rs_acc = reinterpret_cast<float*>(w_full + 6);                       // [G <= 16][128] row-sum staging
+  float* sc_s = rs_acc + 16 * 128;                                            // [G <= 16][128] per-sample scale vectors of the step
+  float* ex_s = sc_s + 16 * 128;                                              // [2][128][2] loss partials of the two row halves
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int s = net.s, G = net.G, L = net.L;
+  const int b0 = blockIdx.x * G;
+  const int nsamp = min(G, B - b0);
+  const int R = nsamp * s;                       // valid chain rows of this CTA
+  const long long row0 = (long long)b0 * s;      // first global chain row
+  // the backward contraction of a LINEAR top layer produces nothing anybody reads (R_L is the constant seed)
+  const int n_steps = L + (do_backward ? (net.layer[L - 1].act ? L : L - 1) : 0);
+
+  // ---- set-up --------------------------------------------------------------------------------------
+  for (int e = tid; e < CF_X_BYTES / 16; e += CF_THREADS) reinterpret_cast<float4*>(X)[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int e = tid; e < 16 * 128; e += CF_THREADS) rs_acc[e] = 0.f;
+  if (warp == 8) {
+    if (lane == 0) {
+      cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(x_ready, CF_EPI);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(cf_smem_u32(tmem_slot)), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the zero fill of X must be visible to the tensor core
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  // step t: t < L -> forward layer l = L-1-t ; t >= L -> backward layer l = t-L
+  auto step_layer = [&](int t) { return t < L ? L - 1 - t : t - L; };
+  auto step_K = [&](int t) { const ChainLayerDev& ly = net.layer[step_layer(t)]; return t < L ? ly.n_out : ly.n_in; };
+  auto step_N = [&](int t) { const ChainLayerDev& ly = net.layer[step_layer(t)]; return t < L ? ly.n_in : ly.n_out; };
+
+  if (warp == 8) {
+    // ===== control thread: weight TMA (one step ahead) and MMA issue =====
+    if (lane == 0) {
+      auto load_w = [&](int t) {
+        const int K = step_K(t), nch = (K + 31) >> 5, buf = t & 1;
+        const CUtensorMap* map = t < L ? &maps.fwd[step_layer(t)] : &maps.bwd[step_layer(t)];
+        cf_mbar_expect_tx(w_full + buf, (uint32_t)nch * CF_CHUNK_BYTES);
+        for (int c = 0; c < nch; ++c) cf_tma_load(Wb[buf] + c * CF_CHUNK_BYTES, map, c * 32, 0, w_full + buf);
+      };
+      load_w(0);
+      for (int t = 0; t < n_steps; ++t) {
+        const int buf = t & 1;
+        cf_mbar_wait(x_ready, t & 1);                       // operand X written by the epilogue threads
+        cf_mbar_wait(w_full + buf, (t >> 1) & 1);           // weight tile landed
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int K = step_K(t), N = step_N(t);
+        const uint32_t n16 = (uint32_t)((N + 15) & ~15);
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((n16 >> 3) << 17) | ((128u >> 4) << 24);
+        const uint32_t xa = cf_smem_u32(X), wa = cf_smem_u32(Wb[buf]);
+        const int ksteps = (K + 7) >> 3;
+        for (int k = 0; k < ksteps; ++k) {
+          const uint32_t off = (uint32_t)((k >> 2) * CF_CHUNK_BYTES + (k & 3) * 32);
+          cf_mma(tmem_base, cf_desc(xa + off), cf_desc(wa + off), idesc, k > 0 ? 1u : 0u);
+        }
+        cf_commit(mma_done);
+        if (t + 1 < n_steps) load_w(t + 1);                 // the other buffer was released by step t-1
+      }
+    }
+  } else {
+    // ===== epilogue threads: thread = chain row = TMEM lane =====
+    const int r = tid & 127;                                // chain row = TMEM lane; two threads per row
+    const int half = tid >> 7;                              // 0: even 32-column chunks, 1: odd chunks
+    const int qw = warp & 3;                                // TMEM lane quarter of this warp
+    const bool row_ok = r < R;
+    const int g = row_ok ? r / s : 0;                       // local sample
+    const int i_seed = r - g * s;                           // seed row within the sample
+    const long long b = b0 + g;                             // batch sample
+    const long long grow = row0 + r;                        // global chain row
+    const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16);
+    // samples present in this warp (for the segmented row-sum): rows [32w, 32w+31]
+    const int g_lo = min(32 * qw, R > 0 ? R - 1 : 0) / s, g_hi = min(32 * qw + 31, R > 0 ? R - 1 : 0) / s;
+
+    // X_0 = Q_{L-1} = seed (* sg_{L-1})
+    {
+      const ChainLayerDev& top = net.layer[L - 1];
+      for (int k = half * 4; k < top.n_out; k += 8) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row_ok) {
+          float t4[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int kk = k + u;
+            float x = 0.f;
+            if (kk < top.n_out) {
+              x = seed ? __ldg(seed + (long long)i_seed * top.n_out + kk) : (kk == i_seed ? 1.f : 0.f);
+              if (top.act) x *= ws[top.sg_off + b * top.ld_out + kk];
+            }
+            t4[u] = x;
+          }
+          v = make_float4(t4[0], t4[1], t4[2], t4[3]);
+          if (net.top_materialised) {
+            *reinterpret_cast<float4*>(ws + top.q_off + grow * top.ld_out + k) = v;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (k + u < top.n_out) ws[top.qt_off + (long long)(k + u) * net.ldT + grow] = t4[u];
+          }
+        }
+        *reinterpret_cast<float4*>(X + cf_xoff(r, k)) = v;
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      cf_mbar_arrive(x_ready);
+    }
+
+    float st_h1 = 0.f, st_rr = 0.f, st_rows = 0.f;
+    for (int t = 0; t < n_steps; ++t) {
+      const int l = step_layer(t);
+      const ChainLayerDev& ly = net.layer[l];
+      const bool fwd = t < L;
+      const int N = fwd ? ly.n_in : ly.n_out;
+      // operands of this epilogue
+      long long sc_off = -1; int sc_ld = 0;   // per-sample column scale [*, N] (workspace offset)
+      const float* addv = nullptr;       // residual row [*, N]
+      float* gout = nullptr;             // global destination row
+      float* goutT = nullptr;            // transposed destination: element (n, row) at goutT[n * ldT]
+      const float* qrow = nullptr;       // Q_l row (backward row-sum)
+      bool last_fwd = false, write_x = true;
+      if (fwd) {
+        if (l > 0) {
+          const ChainLayerDev& below = net.layer[l - 1];
+          if (below.act) { sc_off = below.sg_off; sc_ld = below.ld_out; }
+          gout = ws + below.q_off + grow * below.ld_out;
+          goutT = ws + below.qt_off + grow;
+        } else {
+          last_fwd = true;
+          gout = ws + net.r0_off + grow * net.ld_in;
+          goutT = ws + net.r0t_off + grow;
+          write_x = do_backward != 0;
+        }
+        if (ly.lands_skip >= 0) { const ChainLayerDev& sk = net.layer[ly.lands_skip]; addv = ws + sk.q_off + grow * sk.ld_out; }
+      } else {
+        if (ly.act) { sc_off = ly.sg_off; sc_ld = ly.ld_out; }
+        if (l < L - 1) { gout = ws + ly.dr_off + grow * ly.ld_out; goutT = ws + ly.drt_off + grow; } else write_x = false;
+        if (ly.skip_from >= 0 && l < L - 1) {
+          const int j = ly.skip_from;
+          addv = j == 0 ? ws + net.r0_off + grow * net.ld_in : ws + net.layer[j - 1].dr_off + grow * net.layer[j - 1].ld_out;
+        }
+        if (ly.act) qrow = ws + ly.q_off + grow * ly.ld_out;      // softplus layers are always materialised
+      }
+      const bool rs_step = !fwd && ly.act;
+      // while the MMA runs: stage the per-sample scale vectors of this step in shared memory (coalesced)
+      if (sc_off >= 0) {
+        for (int e = tid; e < nsamp * 128; e += CF_EPI) {
+          const int gg = e >> 7, n = e & 127;
+          sc_s[e] = n < N ? ws[sc_off + (long long)(b0 + gg) * sc_ld + n] : 0.f;
+        }
+      }
+      const float* jrow = nullptr;
+      float gscale = 0.f, inv_nj = 0.f;
+      if (last_fwd && do_loss && row_ok) {
+        const long long sb = idx ? idx[b] : b;
+        jrow = jt + (sb * s + i_seed) * (long long)net.d_in;
+        inv_nj = 1.f / __ldg(jn2 + sb);
+        gscale = coef * inv_nj;
+      }
+      // prefetch the first chunk of the per-row operand (Q_l row, target-Jacobian row or residual row)
+      const float* prow = rs_step ? qrow : ((last_fwd && do_loss) ? jrow : addv);
+      const bool vec_ok = prow != nullptr && ((reinterpret_cast<uintptr_t>(prow) & 15) == 0);
+      float pre[32];
+      auto prefetch = [&](int c0) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (row_ok && prow != nullptr && c0 + j < N) {
+            if (vec_ok && c0 + j + 3 < N) q4 = *reinterpret_cast<const float4*>(prow + c0 + j);
+            else {
+              q4.x = prow[c0 + j];
+              if (c0 + j + 1 < N) q4.y = prow[c0 + j + 1];
+              if (c0 + j + 2 < N) q4.z = prow[c0 + j + 2];
+              if (c0 + j + 3 < N) q4.w = prow[c0 + j + 3];
+            }
+          }
+          pre[j] = q4.x; pre[j + 1] = q4.y; pre[j + 2] = q4.z; pre[j + 3] = q4.w;
+        }
+      };
+      if (half * 32 < N) prefetch(half * 32);
+      asm volatile("bar.sync 1, 256;" ::: "memory");           // scale vectors staged
+      cf_mbar_wait(mma_done, t & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const float* scale = sc_off >= 0 ? sc_s + g * 128 : nullptr;
+      float e_row = 0.f, n_row = 0.f;
+      for (int c0 = half * 32; c0 < N; c0 += 64) {
+        float v[32], opnd[32];
+        cf_tmem_ld32(taddr + (uint32_t)c0, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) opnd[j] = pre[j];
+        if (c0 + 64 < N) prefetch(c0 + 64);                     // next chunk of this thread, overlapped
+        if (rs_step) {
+          // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l  (segmented over the <= 2 samples of this warp)
+          for (int gg = g_lo; gg <= g_hi; ++gg) {
+            float m[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) m[j] = (row_ok && g == gg) ? v[j] * opnd[j] : 0.f;
+            const float tot = cf_colsum32(m, lane);
+            if (c0 + lane < N) atomicAdd(&rs_acc[gg * 128 + c0 + lane], tot);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const int n = c0 + j;
+          float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (row_ok && n < N) {
+            float x[4] = {v[j], v[j + 1], v[j + 2], v[j + 3]};
+            if (fwd && addv) {
+              if (prow == addv) { x[0] += opnd[j]; x[1] += opnd[j + 1]; x[2] += opnd[j + 2]; x[3] += opnd[j + 3]; }
+              else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) if (n + u < N) x[u] += addv[n + u];
+              }
+            }
+            if (scale) { const float4 a = *reinterpret_cast<const float4*>(scale + n); x[0] *= a.x; x[1] *= a.y; x[2] *= a.z; x[3] *= a.w; }
+            if (!fwd && addv) {
+              // (a softplus layer never carries the skip, so opnd holds the residual row here)
+              x[0] += opnd[j]; x[1] += opnd[j + 1]; x[2] += opnd[j + 2]; x[3] += opnd[j + 3];
+            }
+            if (last_fwd && do_loss) {
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                if (n + u < N) {
+                  const float tv = opnd[j + u];
+                  const float d = x[u] - tv;
+                  e_row = fmaf(d, d, e_row);
+                  n_row = fmaf(tv, tv, n_row);
+                  x[u] = gscale * d;
+                } else {
+                  x[u] = 0.f;
+                }
+              }
+            } else {
+#pragma unroll
+              for (int u = 0; u < 4; ++u) x[u] = (n + u < N) ? x[u] : 0.f;
+            }
+            if (!last_fwd || do_loss) {            // everything that feeds a later TF32 contraction
+#pragma unroll
+              for (int u = 0; u < 4; ++u) x[u] = round_tf32_f(x[u]);
+            }
+            o = make_float4(x[0], x[1], x[2], x[3]);
+            if (gout && (do_backward || !last_fwd || !do_loss)) {
+              *reinterpret_cast<float4*>(gout + n) = o;
+              if (do_backward) {                   // transposed copy: consecutive threads = consecutive rows
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                  if (n + u < N) goutT[(long long)(n + u) * net.ldT] = x[u];
+              }
+            }
+          }
+          if (write_x && n < CF_MAXW) *reinterpret_cast<float4*>(X + cf_xoff(r, n)) = o;
+        }
+      }
+      // clear the operand columns between N and the 32-float chunk boundary (owner: the half that holds that chunk)
+      if (write_x && N > 0 && (((N - 1) >> 5) & 1) == half) {
+        for (int n = (N + 3) & ~3; n < ((N + 31) & ~31); n += 4)
+          *reinterpret_cast<float4*>(X + cf_xoff(r, n)) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      if (last_fwd && do_loss) {
+        if (row_ok) st_h1 += e_row * inv_nj;
+        ex_s[(half * 128 + r) * 2 + 0] = e_row;               // the per-row metric needs the FULL row sums
+        ex_s[(half * 128 + r) * 2 + 1] = n_row;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");           // end of step: sc_s / rs_acc / ex_s are consistent
+      if (last_fwd && do_loss && half == 0 && row_ok) {
+        const float e_all = e_row + ex_s[(128 + r) * 2 + 0], n_all = n_row + ex_s[(128 + r) * 2 + 1];
+        st_rr += e_all / n_all;
+        st_rows += 1.f;
+      }
+      // publish the row sums of this layer
+      if (rs_step) {
+        for (int e = tid; e < nsamp * 128; e += CF_EPI) {
+          const int gg = e >> 7, n = e & 127;
+          if (n < N) ws[ly.rs_off + (long long)(b0 + gg) * ly.ld_out + n] = rs_acc[e];
+          rs_acc[e] = 0.f;
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      if (t + 1 < n_steps) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        cf_mbar_arrive(x_ready);
+      }
+    }
+    if (do_loss) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        st_h1 += __shfl_xor_sync(0xffffffffu, st_h1, o);
+        st_rr += __shfl_xor_sync(0xffffffffu, st_rr, o);
+        st_rows += __shfl_xor_sync(0xffffffffu, st_rows, o);
+      }
+      if (lane == 0) {                 // both column halves of a row carry part of its squared error
+        if (st_h1 != 0.f) atomicAdd(stats + ST_H1_SUM, st_h1);
+        if (st_rows > 0.f) { atomicAdd(stats + ST_JROW_SUM, st_rr); atomicAdd(stats + ST_JROWS, st_rows); }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 8)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+}
+
+// ---- host ---------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_cfEncode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const float* ws, const long long* wp_off,
+                             const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp) {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess)
+    return false;
+  PFN_cfEncode enc = reinterpret_cast<PFN_cfEncode>(fn);
+  auto mk = [&](CUtensorMap* m, const float* base, int rows, int cols, long long ld) {
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)ld * sizeof(float)};
+    cuuint32_t box[2] = {32, (cuuint32_t)CF_ROWS};
+    cuuint32_t es[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, es,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  };
+  for (int l = 0; l < net.L; ++l) {
+    const ChainLayerDev& ly = net.layer[l];
+    // forward: B operand stored [N = n_in][K = n_out] = padded W_l ; backward: [N = n_out][K = n_in] = padded W_l^T
+    if (!mk(&maps->fwd[l], ws + wp_off[l], ly.n_in, ly.n_out, ld_wp[l])) return false;
+    if (!mk(&maps->bwd[l], ws + wtp_off[l], ly.n_out, ly.n_in, ld_wtp[l])) return false;
+  }
+  return true;
+}
+
+bool chain_fused_supported(const ChainNetDev& net) {
+  if (net.L < 1 || net.L > CHAIN_FUSED_MAX_LAYERS) return false;
+  if (net.s < 1 || net.s > CF_ROWS || net.G < 1 || net.G > 16) return false;
+  if (net.d_in > CF_MAXW) return false;
+  for (int l = 0; l < net.L; ++l)
+    if (net.layer[l].n_in > CF_MAXW || net.layer[l].n_out > CF_MAXW) return false;
+  return true;
+}
+
+cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, float* ws, const float* jt, const float* jn2,
+                               const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
+                               float* stats, cudaStream_t st) {
+  constexpr int SMEM = 3 * CF_X_BYTES + 64 + 2 * 16 * 128 * 4 + 2 * 128 * 2 * 4 + 1024;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(chain_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  const int ctas = (B + net.G - 1) / net.G;
+  chain_fused_kernel<<<ctas, CF_THREADS, SMEM, st>>>(maps, net, ws, jt, jn2, idx, seed, B, coef, do_loss, do_backward, stats);
+  return cudaGetLastError();
+}
+
+}  // namespace dino

@@ -1,5 +1,6 @@
 // Shared declarations for the dino_b200 CUDA library (sm_100a only).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -53,6 +54,9 @@ cudaError_t launch_gemm_simt(const GemmOp& op, int num_sms, cudaStream_t st);
 constexpr int GEMM_GROUP_MAX = 24;
 struct GemmGroup { int n; int z_start[GEMM_GROUP_MAX + 1]; GemmOp ops[GEMM_GROUP_MAX]; };
 cudaError_t launch_gemm_simt_grouped(GemmGroup& g, int num_sms, cudaStream_t st);
+// the same group on the tensor cores (wgrad_tc.cu): X^T Y with MN-major TF32 UMMA operands, widths <= 128
+bool wgrad_tc_supported(const GemmOp& op);
+cudaError_t launch_wgrad_tc(const GemmGroup& g, int num_sms, cudaStream_t st);
 
 // Fused small-network MLP kernels (mlp_fused.cu): one CTA runs every layer for a tile of samples.
 struct MlpLayerDev {
@@ -130,6 +134,19 @@ void count_launch();                           // dino_launch_count() += 1      
 }
 #endif
 namespace dino {
+
+// Fused tcgen05 chain kernel (chain_fused.cu)
+constexpr int CHAIN_FUSED_MAX_LAYERS = 16;
+// qt_off / drt_off: TRANSPOSED copies [n_out, ldT] of Q_l and dR_{l+1} (operands of the tensor-core weight gradient)
+struct ChainLayerDev { long long q_off, sg_off, rs_off, dr_off, qt_off, drt_off; int n_in, n_out, ld_out, act, skip_from, lands_skip; };
+struct ChainNetDev { int L, s, G, d_in, ld_in, top_materialised; long long r0_off, r0t_off, ldT; ChainLayerDev layer[CHAIN_FUSED_MAX_LAYERS]; };
+struct ChainMaps { CUtensorMap fwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap bwd[CHAIN_FUSED_MAX_LAYERS]; };
+bool chain_fused_supported(const ChainNetDev& net);
+bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const float* ws, const long long* wp_off,
+                             const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp);
+cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, float* ws, const float* jt, const float* jn2,
+                               const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
+                               float* stats, cudaStream_t st);
 
 // statistics slots accumulated by the loss kernels (floats)
 enum { ST_L2_SUM = 0, ST_H1_SUM = 1, ST_EQ_SUM = 2, ST_NQ_SUM = 3, ST_JROW_SUM = 4, ST_COUNT = 5,

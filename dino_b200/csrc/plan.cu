@@ -15,6 +15,7 @@
 // (softplus'' = sg(1-sg), which is why only the post-scaling Q_l has to be kept.)  The formulas
 // are checked against autograd double-backward in tests/test_pipeline_model.py.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -60,6 +61,7 @@ struct LayerPlan {
   long long z_off, sg_off, q_off, rs_off;   // workspace offsets (floats); -1 when absent
   long long wp_off, wtp_off, ld_wp, ld_wtp; // TF32 mode: padded W [n_in][ld_wp] and W^T [n_out][ld_wtp]
   long long dr_off;          // dR_{l+1} = gradient wrt the chain state above this layer [B*s, ld_out]; -1 for the top layer
+  long long qt_off, drt_off; // transposed copies [n_out, ldT] of Q_l and dR_{l+1} (fused tensor-core path)
   long long da_off;          // da_l [B, ld_out] (fused MLP backward keeps every layer's for the grouped weight gradient)
   long long ld_out;          // r4(n_out)
   int lands_skip;            // index l2 of the skip layer whose source is THIS layer's input, or -1
@@ -81,6 +83,9 @@ struct DinoPlan {
   int max_in, max_out;
   MlpNetDev mlp;             // descriptor of the fused small-network MLP kernels
   bool mlp_fused;
+  ChainNetDev chain;         // descriptor + weight tensor maps of the fused tcgen05 chain kernel
+  ChainMaps chain_maps;
+  bool chain_fused;
 };
 
 static cudaStream_t S(dino_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
@@ -150,7 +155,8 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   p->seed_shared = (p->jac_mode == DINO_JAC_FULL || p->jac_mode == DINO_JAC_OUT_REDUCED);
   const LayerPlan& last = p->layers[p->L - 1];
   p->top_materialised = p->jac_mode != DINO_JAC_NONE &&
-                        (!p->seed_shared || last.act == DINO_ACT_SOFTPLUS || last.skip_from >= 0);
+                        (!p->seed_shared || last.act == DINO_ACT_SOFTPLUS || last.skip_from >= 0 ||
+                         p->precision == DINO_PREC_TF32 /* TMA-addressable operand for the tensor-core weight gradient */);
 
   // ---- workspace layout ------------------------------------------------------------------------
   const long long Bm = p->max_batch, Ms = Bm * (long long)p->s;
@@ -174,7 +180,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   for (int i = 0; i < 3; ++i) p->off_dz[i] = take(Bm * max_w);
   p->off_da = take(Bm * max_w);
   p->off_r0 = p->off_sk = -1;
-  for (auto& lp : p->layers) { lp.q_off = -1; lp.dr_off = -1; lp.da_off = -1; }
+  for (auto& lp : p->layers) { lp.q_off = -1; lp.dr_off = -1; lp.da_off = -1; lp.qt_off = -1; lp.drt_off = -1; }
   if (p->jac_mode != DINO_JAC_NONE) {
     for (int l = 0; l < p->L; ++l) {
       LayerPlan& lp = p->layers[l];
@@ -222,6 +228,32 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
       if (lp.n_out > p->max_out) p->max_out = lp.n_out;
     }
   }
+  p->chain_fused = false;
+  if (p->precision == DINO_PREC_TF32 && (p->jac_mode == DINO_JAC_FULL || p->jac_mode == DINO_JAC_OUT_REDUCED) &&
+      p->L <= CHAIN_FUSED_MAX_LAYERS && getenv("DINO_B200_NO_FUSED_CHAIN") == nullptr) {
+    ChainNetDev& c = p->chain;
+    memset(&c, 0, sizeof(c));
+    c.L = p->L; c.s = p->s; c.G = p->s <= 128 ? 128 / p->s : 0; if (c.G > 16) c.G = 16;
+    c.d_in = p->d_in; c.ld_in = (int)p->ld_in; c.top_materialised = p->top_materialised ? 1 : 0; c.r0_off = p->off_r0;
+    for (int l = 0; l < p->L; ++l) {
+      const LayerPlan& lp = p->layers[l];
+      ChainLayerDev& d = c.layer[l];
+      d.q_off = lp.q_off; d.sg_off = lp.sg_off; d.rs_off = lp.rs_off; d.dr_off = lp.dr_off;
+      d.n_in = lp.n_in; d.n_out = lp.n_out; d.ld_out = (int)lp.ld_out; d.act = lp.act == DINO_ACT_SOFTPLUS;
+      d.skip_from = lp.skip_from; d.lands_skip = lp.lands_skip;
+    }
+    p->chain_fused = chain_fused_supported(c);
+    if (p->chain_fused) {
+      c.ldT = r4(Ms);
+      c.r0t_off = take((long long)p->d_in * c.ldT);
+      for (int l = 0; l < p->L; ++l) {
+        LayerPlan& lp = p->layers[l];
+        lp.qt_off = take((long long)lp.n_out * c.ldT);
+        lp.drt_off = l < p->L - 1 ? take((long long)lp.n_out * c.ldT) : -1;
+        c.layer[l].qt_off = lp.qt_off; c.layer[l].drt_off = lp.drt_off;
+      }
+    }
+  }
   p->ws_floats = off;
   *out = p;
   return 0;
@@ -249,6 +281,15 @@ extern "C" int dino_plan_bind_workspace(DinoPlan* plan, void* d_ws, size_t bytes
   if (bytes < (size_t)plan->ws_floats * sizeof(float)) return fail("dino_plan_bind_workspace: workspace too small");
   if ((reinterpret_cast<uintptr_t>(d_ws) & 255) != 0) return fail("dino_plan_bind_workspace: workspace must be 256-byte aligned");
   plan->ws = static_cast<float*>(d_ws);
+  if (plan->chain_fused) {
+    long long wp[CHAIN_FUSED_MAX_LAYERS], lwp[CHAIN_FUSED_MAX_LAYERS], wtp[CHAIN_FUSED_MAX_LAYERS], lwtp[CHAIN_FUSED_MAX_LAYERS];
+    for (int l = 0; l < plan->L; ++l) {
+      wp[l] = plan->layers[l].wp_off; lwp[l] = plan->layers[l].ld_wp;
+      wtp[l] = plan->layers[l].wtp_off; lwtp[l] = plan->layers[l].ld_wtp;
+    }
+    if (!chain_fused_encode_maps(&plan->chain_maps, plan->chain, plan->ws, wp, lwp, wtp, lwtp))
+      return fail("dino_plan_bind_workspace: cuTensorMapEncodeTiled failed for the fused chain kernel");
+  }
   if (plan->off_ident >= 0)
     DINO_LAUNCH(launch_fill_identity(plan->ws + plan->off_ident, plan->d_out, plan->ld_ident, S(stream)));
   return 0;
@@ -365,14 +406,58 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
   return 0;
 }
 
+static int push_wgrad(DinoPlan* p, GemmGroup& g, const GemmOp& op, cudaStream_t st);
+
+// Fused tcgen05 path: prep weights, then ONE kernel runs chain forward [+ H1 loss [+ chain backward]].
+static int run_chain_fused(DinoPlan* p, const float* params, const DinoBatch* b, int B, float coef, int do_loss,
+                           int do_backward, float* stats, cudaStream_t st, TopQ* top_out) {
+  float* ws = p->ws;
+  const LayerPlan& last = p->layers[p->L - 1];
+  const float* seed = p->jac_mode == DINO_JAC_OUT_REDUCED ? b->seed : nullptr;
+  if (p->top_materialised) *top_out = {ws + last.q_off, last.ld_out, 0};
+  else if (p->jac_mode == DINO_JAC_FULL) *top_out = {ws + p->off_ident, p->ld_ident, p->s};
+  else *top_out = {b->seed, (long long)p->d_out, p->s};
+  DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
+  DINO_LAUNCH(launch_chain_fused(p->chain_maps, p->chain, ws, b->J, b->J_sqnorm, b->idx, seed, B, coef, do_loss,
+                                 do_backward, stats, st));
+  return 0;
+}
+
+// weight gradients of the chain: dW_l += dR_l^T Q_l for every trainable layer (joins the grouped launch)
+static int push_chain_wgrads(DinoPlan* p, int B, float* grad, const TopQ& top, GemmGroup& wg, cudaStream_t st) {
+  float* ws = p->ws;
+  const int L = p->L, M = B * p->s;
+  for (int l = 0; l < L; ++l) {
+    const LayerPlan& lp = p->layers[l];
+    if (!lp.trainable) continue;
+    GemmOp op = gemm_op_zero();
+    if (p->chain_fused && lp.n_in <= 128 && lp.n_out <= 128) {
+      // dW_l += dRT_l QT_l^T : both factors transposed by the fused kernel -> K-major tensor-core contraction
+      op.A = l == 0 ? ws + p->chain.r0t_off : ws + p->layers[l - 1].drt_off;
+      op.a_sm = p->chain.ldT; op.a_sk = 1;
+      op.B = ws + lp.qt_off; op.b_sk = 1; op.b_sn = p->chain.ldT;
+    } else {
+      op.A = l == 0 ? ws + p->off_r0 : ws + p->layers[l - 1].dr_off;
+      op.a_sm = 1; op.a_sk = l == 0 ? p->ld_in : p->layers[l - 1].ld_out;
+      if (l == L - 1) { op.B = top.ptr; op.b_sk = top.ld; op.b_kmod = top.mod; }
+      else { op.B = ws + lp.q_off; op.b_sk = lp.ld_out; }
+      op.b_sn = 1;
+    }
+    op.M = lp.n_in; op.N = lp.n_out; op.K = M;
+    op.C = grad + lp.koff; op.ldc = lp.n_out; op.atomic_c = 1;
+    if (push_wgrad(p, wg, op, st)) return 1;
+  }
+  return 0;
+}
+
 static int run_losses(DinoPlan* p, const DinoBatch* b, int B, float w_l2, float w_h1, float inv_gb, bool grads,
-                      float* stats, cudaStream_t st) {
+                      float* stats, cudaStream_t st, bool q_only = false) {
   float* ws = p->ws;
   const LayerPlan& last = p->layers[p->L - 1];
   float* dq = grads ? ws + p->off_dz[p->L % 3] : nullptr;
   DINO_LAUNCH(launch_loss_q(ws + last.z_off, last.ld_out, b->q, b->q_sqnorm, b->idx, B, p->d_out,
                             2.f * w_l2 * inv_gb, dq, p->ld_dz, stats, st));
-  if (p->jac_mode == DINO_JAC_NONE) return 0;
+  if (p->jac_mode == DINO_JAC_NONE || q_only) return 0;
   const float cj = 2.f * w_h1 * inv_gb;
   if (p->jac_mode == DINO_JAC_SKETCHED) {
     const int k = p->s;
@@ -388,16 +473,27 @@ static int run_losses(DinoPlan* p, const DinoBatch* b, int B, float w_l2, float 
 }
 
 // Appends one weight-gradient contraction to the pending group; flushes the group when it is full.
+static int flush_wgrad(DinoPlan* p, GemmGroup& g, cudaStream_t st);
 static int push_wgrad(DinoPlan* p, GemmGroup& g, const GemmOp& op, cudaStream_t st) {
-  if (g.n == GEMM_GROUP_MAX) {
-    DINO_LAUNCH(launch_gemm_simt_grouped(g, p->num_sms, st));
-    g.n = 0;
-  }
+  if (g.n == GEMM_GROUP_MAX && flush_wgrad(p, g, st)) return 1;
   g.ops[g.n++] = op;
   return 0;
 }
 static int flush_wgrad(DinoPlan* p, GemmGroup& g, cudaStream_t st) {
-  if (g.n > 0) DINO_LAUNCH(launch_gemm_simt_grouped(g, p->num_sms, st));
+  if (g.n > 0 && p->precision == DINO_PREC_TF32) {
+    // tensor-core weight gradients for every op that qualifies; the rest stays on the SIMT engine
+    static GemmGroup tc, rest;
+    tc.n = rest.n = 0;
+    for (int i = 0; i < g.n; ++i) {
+      if (wgrad_tc_supported(g.ops[i])) tc.ops[tc.n++] = g.ops[i];
+      else if (g.ops[i].a_sm == 1 && g.ops[i].b_sn == 1) rest.ops[rest.n++] = g.ops[i];
+      else DINO_LAUNCH(launch_gemm_simt(g.ops[i], p->num_sms, st));
+    }
+    if (tc.n > 0) DINO_LAUNCH(launch_wgrad_tc(tc, p->num_sms, st));
+    if (rest.n > 0) DINO_LAUNCH(launch_gemm_simt_grouped(rest, p->num_sms, st));
+  } else if (g.n > 0) {
+    DINO_LAUNCH(launch_gemm_simt_grouped(g, p->num_sms, st));
+  }
   g.n = 0;
   return 0;
 }
@@ -537,7 +633,9 @@ extern "C" int dino_jacobian(DinoPlan* p, const float* params, const DinoBatch* 
   cudaStream_t st = S(stream);
   if (run_mlp_forward(p, params, b, B, st)) return 1;
   TopQ top;
-  if (run_chain_forward(p, params, b, B, st, &top)) return 1;
+  if (p->chain_fused) {
+    if (run_chain_fused(p, params, b, B, 0.f, 0, 0, nullptr, st, &top)) return 1;
+  } else if (run_chain_forward(p, params, b, B, st, &top)) return 1;
   const LayerPlan& last = p->layers[p->L - 1];
   if (q_out) DINO_LAUNCH(launch_copy2d(p->ws + last.z_off, last.ld_out, q_out, p->d_out, B, p->d_out, st));
   if (p->jac_mode == DINO_JAC_SKETCHED)
@@ -557,11 +655,17 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
     DINO_CUDA(cudaMemsetAsync(p->ws + p->off_rs_begin, 0, (size_t)p->rs_floats * sizeof(float), st));
   if (run_mlp_forward(p, params, b, B, st)) return 1;
   TopQ top = {nullptr, 0, 0};
-  if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
-  if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st)) return 1;
   GemmGroup wg;
   wg.n = 0;
-  if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, wg, st)) return 1;
+  if (p->chain_fused) {
+    if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st, true)) return 1;
+    if (run_chain_fused(p, params, b, B, 2.f * w_h1 * inv_gb, 1, 1, stats, st, &top)) return 1;
+    if (push_chain_wgrads(p, B, grad, top, wg, st)) return 1;
+  } else {
+    if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
+    if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st)) return 1;
+    if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, wg, st)) return 1;
+  }
   if (run_mlp_backward(p, params, B, grad, wg, st)) return 1;
   return flush_wgrad(p, wg, st);
 }
@@ -573,6 +677,10 @@ extern "C" int dino_h1_eval(DinoPlan* p, const float* params, const DinoBatch* b
   cudaStream_t st = S(stream);
   if (run_mlp_forward(p, params, b, B, st)) return 1;
   TopQ top = {nullptr, 0, 0};
+  if (p->chain_fused) {
+    if (run_losses(p, b, B, 1.f, 1.f, 1.f, false, stats, st, true)) return 1;
+    return run_chain_fused(p, params, b, B, 2.f, 1, 0, stats, st, &top);
+  }
   if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
   return run_losses(p, b, B, 1.f, 1.f, 1.f, false, stats, st);
 }
@@ -635,6 +743,29 @@ extern "C" int dino_gemm_nt(int engine, const float* A, int64_t lda, const float
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    DINO_LAUNCH(launch_gemm_simt(op, sms, S(stream)));
+  }
+  return 0;
+}
+
+extern "C" int dino_gemm_nt_acc(int engine, const float* XT, int64_t ldx, const float* YT, int64_t ldy, float* C,
+                                int32_t rows, int32_t n_in, int32_t n_out, dino_stream_t stream) {
+  if (!XT || !YT || !C) return fail("dino_gemm_nt_acc: null argument");
+  static GemmGroup g;
+  g.n = 1;
+  GemmOp& op = g.ops[0];
+  op = gemm_op_zero();
+  op.A = XT; op.a_sm = ldx; op.a_sk = 1;
+  op.B = YT; op.b_sk = 1; op.b_sn = ldy;
+  op.M = n_in; op.N = n_out; op.K = rows;
+  op.C = C; op.ldc = n_out; op.atomic_c = 1;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (engine == DINO_PREC_TF32) {
+    if (!wgrad_tc_supported(op)) return fail("dino_gemm_nt_acc: operands do not meet the tensor-core weight-gradient rules");
+    DINO_LAUNCH(launch_wgrad_tc(g, sms, S(stream)));
+  } else {
     DINO_LAUNCH(launch_gemm_simt(op, sms, S(stream)));
   }
   return 0;

@@ -1,0 +1,233 @@
+// Weight gradients of the Jacobian chain on the tensor cores:
+//     dW_l[n_in, n_out] += dR_l^T Q_l = XT[n_in, rows] * YT[n_out, rows]^T        (rows = B*s, tens of thousands)
+// for every layer in ONE launch, split over the rows.  XT / YT are the TRANSPOSED chain states the fused
+// chain kernel streams out next to the row-major ones (its epilogue threads own consecutive rows, so the
+// transposed stores are perfectly coalesced); with them both operands are K-major and the contraction
+// is the standard TMA -> tcgen05.mma.kind::tf32 -> TMEM pipeline of gemm_tc.cu with a red.global.add
+// epilogue.  (Feeding the row-major states as MN-major UMMA operands would avoid the copies, but TF32
+// MN-major tiles need the 32-byte-base swizzle variant, which could not be validated offline.)
+// Requires n_in, n_out <= 128; other layers use the SIMT split-K path.
+#include <cuda.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace dino {
+
+constexpr int WG_BK = 32;                       // reduction rows per stage (one 128-byte swizzle row)
+constexpr int WG_STAGES = 6;
+constexpr int WG_OPER_BYTES = 128 * WG_BK * 4;  // 16 KB: up to 128 operand rows x 32 reduction elements
+constexpr int WG_STAGE_BYTES = 2 * WG_OPER_BYTES;
+constexpr int WG_THREADS = 192;
+
+struct WgOp {
+  float* C;                 // gradient block [n_in, n_out], ldc = n_out
+  int n_in, n_out, rows;    // rows = reduction length
+  int z_start;              // first blockIdx.x of this op
+  int chunks_per_cta;       // reduction chunks (of WG_BK rows) per CTA
+};
+struct WgGroup {
+  int n;
+  WgOp op[GEMM_GROUP_MAX];
+  CUtensorMap mx[GEMM_GROUP_MAX];   // XT [n_in, rows]
+  CUtensorMap my[GEMM_GROUP_MAX];   // YT [n_out, rows]
+};
+
+__device__ __forceinline__ uint32_t wg_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void wg_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WG_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WG_DONE;\n\t"
+      "bra WG_WAIT;\n\t"
+      "WG_DONE:\n\t"
+      "}" ::"r"(wg_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint64_t wg_desc(uint32_t saddr) {    // K-major, SWIZZLE_128B (as gemm_tc.cu)
+  return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+
+__global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_constant__ WgGroup g) {
+  extern __shared__ uint8_t wg_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(wg_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + WG_STAGES * WG_STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + WG_STAGES;
+  uint64_t* done_bar = empty_bar + WG_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+
+  int oi = 0;
+  while (oi + 1 < g.n && (int)blockIdx.x >= g.op[oi + 1].z_start) ++oi;
+  const WgOp& op = g.op[oi];
+  const int total_chunks = (op.rows + WG_BK - 1) / WG_BK;
+  const int c_begin = (blockIdx.x - op.z_start) * op.chunks_per_cta;
+  const int nchunks = min(total_chunks - c_begin, op.chunks_per_cta);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < WG_STAGES; ++i) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(wg_u32(full_bar + i)), "r"(1u));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(wg_u32(empty_bar + i)), "r"(1u));
+      }
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(wg_u32(done_bar)), "r"(1u));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(wg_u32(tmem_slot)), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (nchunks > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        const CUtensorMap* mx = &g.mx[oi];
+        const CUtensorMap* my = &g.my[oi];
+        for (int c = 0; c < nchunks; ++c) {
+          const int st = c % WG_STAGES;
+          wg_wait(empty_bar + st, ((c / WG_STAGES) & 1) ^ 1);
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(wg_u32(full_bar + st)),
+                       "r"((uint32_t)WG_STAGE_BYTES) : "memory");
+          uint8_t* sx = smem + st * WG_STAGE_BYTES;
+          const int k0 = (c_begin + c) * WG_BK;
+          asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                       ::"r"(wg_u32(sx)), "l"(mx), "r"(wg_u32(full_bar + st)), "r"(k0), "r"(0) : "memory");
+          asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                       ::"r"(wg_u32(sx + WG_OPER_BYTES)), "l"(my), "r"(wg_u32(full_bar + st)), "r"(k0), "r"(0) : "memory");
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {
+        const uint32_t n16 = (uint32_t)((op.n_out + 15) & ~15);
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((n16 >> 3) << 17) | ((128u >> 4) << 24);
+        for (int c = 0; c < nchunks; ++c) {
+          const int st = c % WG_STAGES;
+          wg_wait(full_bar + st, (c / WG_STAGES) & 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t sx = wg_u32(smem + st * WG_STAGE_BYTES), sy = sx + WG_OPER_BYTES;
+          const uint64_t ad = wg_desc(sx), bd = wg_desc(sy);
+#pragma unroll
+          for (int k = 0; k < WG_BK / 8; ++k) {
+            const uint32_t acc = (c > 0 || k > 0) ? 1u : 0u;
+            asm volatile(
+                "{\n\t"
+                ".reg .pred p;\n\t"
+                "setp.ne.b32 p, %4, 0;\n\t"
+                "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+                "}" ::"r"(tmem_base), "l"(ad + 2 * k), "l"(bd + 2 * k), "r"(idesc), "r"(acc) : "memory");
+          }
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(wg_u32(empty_bar + st)) : "memory");
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(wg_u32(done_bar)) : "memory");
+      }
+    } else {
+      // epilogue: TMEM lane = n_in index m, columns = n_out index
+      wg_wait(done_bar, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int q = warp & 3;
+      const int m = q * 32 + lane;
+      for (int c0 = 0; c0 < op.n_out; c0 += 32) {
+        uint32_t r[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+              "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+              "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+            : "r"(taddr));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (m < op.n_in) {
+          float* crow = op.C + (long long)m * op.n_out + c0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c0 + j < op.n_out) atomicAdd(crow + j, __uint_as_float(r[j]));
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+}
+
+// ---- host ---------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_wgEncode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_wgEncode wg_encoder() {
+  static PFN_wgEncode enc = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      enc = reinterpret_cast<PFN_wgEncode>(fn);
+  });
+  return enc;
+}
+// operand stored [n, rows] with pitch ld floats: box = 128 operand rows x 32 reduction elements
+static bool wg_map(CUtensorMap* m, const float* base, int n, int rows, long long ld) {
+  PFN_wgEncode enc = wg_encoder();
+  if (!enc) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)rows, (cuuint64_t)n};
+  cuuint64_t gstr[1] = {(cuuint64_t)ld * sizeof(float)};
+  cuuint32_t box[2] = {(cuuint32_t)WG_BK, 128};
+  cuuint32_t es[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, es,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// The ops passed here describe C[M,N] += A[M,K] * Bt[N,K]^T with BOTH operands K-major (a_sk == b_sk == 1):
+// A = XT (pitch a_sm), B = YT (pitch b_sn).
+bool wgrad_tc_supported(const GemmOp& op) {
+  if (!op.atomic_c || op.a_sk != 1 || op.b_sk != 1 || op.b_kmod > 0 || op.a_mod > 0) return false;
+  if (op.M > 128 || op.N > 128 || op.M < 1 || op.N < 1 || op.K < 1) return false;
+  if ((op.a_sm & 3) || (op.b_sn & 3)) return false;
+  if ((reinterpret_cast<uintptr_t>(op.A) & 15) || (reinterpret_cast<uintptr_t>(op.B) & 15)) return false;
+  return op.ldc == op.N;
+}
+
+cudaError_t launch_wgrad_tc(const GemmGroup& gg, int num_sms, cudaStream_t st) {
+  if (gg.n <= 0) return cudaSuccess;
+  static WgGroup g;                      // about 7 KB: keep it off the stack; plans are single-threaded
+  g.n = gg.n;
+  long long total_rows = 0;
+  for (int i = 0; i < gg.n; ++i) total_rows += gg.ops[i].K;
+  const long long target_ctas = 2LL * num_sms;
+  int z = 0;
+  for (int i = 0; i < gg.n; ++i) {
+    const GemmOp& o = gg.ops[i];
+    WgOp& w = g.op[i];
+    w.C = o.C; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
+    const int chunks = (o.K + WG_BK - 1) / WG_BK;
+    long long splits = (target_ctas * o.K + total_rows - 1) / total_rows;
+    if (splits > chunks) splits = chunks;
+    if (splits < 1) splits = 1;
+    w.chunks_per_cta = (int)((chunks + splits - 1) / splits);
+    w.z_start = z;
+    z += (chunks + w.chunks_per_cta - 1) / w.chunks_per_cta;
+    if (!wg_map(&g.mx[i], o.A, o.M, o.K, o.a_sm) || !wg_map(&g.my[i], o.B, o.N, o.K, o.b_sn)) return cudaErrorInvalidValue;
+  }
+  constexpr int SMEM = WG_STAGES * WG_STAGE_BYTES + 128 + 1024;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  wgrad_tc_kernel<<<z, WG_THREADS, SMEM, st>>>(g);
+  return cudaGetLastError();
+}
+
+}  // namespace dino

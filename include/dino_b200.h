@@ -176,6 +176,13 @@ int dino_forward_noalloc(const DinoNetSpec* spec, const float* d_params, const f
 int dino_gemm_nt(int engine, const float* d_A, int64_t lda, const float* d_Bt, int64_t ldb, float* d_C,
                  int64_t ldc, int32_t M, int32_t N, int32_t K, dino_stream_t stream);
 
+/* The split-K weight-gradient contraction on its own: C[n_in, n_out] += XT[n_in, rows] YT[n_out, rows]^T, i.e.
+ * dW += X^T Y with both factors given TRANSPOSED (reduction index contiguous), as the fused chain kernel
+ * stores them (what the second-order graph of network.fit reduces over the batch, trainingUtilities.py:135).
+ * engine as above; the TF32 engine needs n_in, n_out <= 128, ldx, ldy multiples of 4, 16-byte aligned bases. */
+int dino_gemm_nt_acc(int engine, const float* d_XT, int64_t ldx, const float* d_YT, int64_t ldy, float* d_C,
+                     int32_t rows, int32_t n_in, int32_t n_out, dino_stream_t stream);
+
 /* number of kernels this library has launched in the calling process (bench.py gpu_launches) */
 int64_t dino_launch_count(void);
 

@@ -48,6 +48,27 @@ def test_tf32_gemm_matches_fp64(cuda_device, M, N, K):
     assert np.abs(got - want).max() < 2e-3 * np.sqrt(K) * 4, np.abs(got - want).max()
 
 
+@pytest.mark.parametrize("rows,n_in,n_out", [(64, 32, 32), (240, 13, 8), (1000, 50, 50), (12800, 100, 50), (300, 128, 128),
+                                             (77, 5, 100)])
+def test_tf32_weight_gradient_contraction(cuda_device, rows, n_in, n_out):
+    """C += XT YT^T (split over the reduction, red.global.add epilogue) vs fp64, onto a non-zero C."""
+    lib = _lib.load()
+    rng = np.random.default_rng(rows + n_in + n_out)
+    ld = (rows + 3) & ~3
+    XT = np.full((n_in, ld), 1e30, np.float32); XT[:, :rows] = rng.normal(size=(n_in, rows))
+    YT = np.full((n_out, ld), 1e30, np.float32); YT[:, :rows] = rng.normal(size=(n_out, rows))
+    C0 = rng.normal(size=(n_in, n_out)).astype(np.float32)
+    want = C0 + XT[:, :rows].astype(np.float64) @ YT[:, :rows].astype(np.float64).T
+    for engine, tol in ((_lib.PREC_FP32, 1e-5), (_lib.PREC_TF32, 2e-3)):
+        dX, dY, dC = torch.from_numpy(XT).cuda(), torch.from_numpy(YT).cuda(), torch.from_numpy(C0.copy()).cuda()
+        _lib.check(lib.dino_gemm_nt_acc(engine, C.c_void_p(dX.data_ptr()), ld, C.c_void_p(dY.data_ptr()), ld,
+                                        C.c_void_p(dC.data_ptr()), rows, n_in, n_out, _stream()), "dino_gemm_nt_acc")
+        torch.cuda.synchronize()
+        got = dC.cpu().numpy()
+        assert np.isfinite(got).all()
+        assert np.abs(got - want).max() < tol * np.sqrt(rows) * 4, (engine, np.abs(got - want).max())
+
+
 def _compile(model):
     model.compile(optimizer=Adam(1e-3), loss=[normalized_mse, normalized_mse_matrix], loss_weights=[1.0, 1.0],
                   metrics=[l2_accuracy, f_accuracy_matrix])
