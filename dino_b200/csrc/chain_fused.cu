@@ -21,10 +21,21 @@
 
 namespace dino {
 
+// Per-phase %globaltimer stamps of CTA 0 (debug aid; enabled with -DDINO_CF_TRACE, read by scripts/trace_chain.py)
+__device__ unsigned long long g_cf_trace[64 * 8];
+#ifdef DINO_CF_TRACE
+#define CF_STAMP(t, slot) do { if (blockIdx.x == 0) { unsigned long long _c; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_c)); g_cf_trace[(t) * 8 + (slot)] = _c; } } while (0)
+#else
+#define CF_STAMP(t, slot) do {} while (0)
+#endif
+
 constexpr int CF_ROWS = 128, CF_MAXW = 128, CF_CHUNK_BYTES = CF_ROWS * 128;       // 16 KB per 32-float K chunk
 constexpr int CF_X_BYTES = (CF_MAXW / 32) * CF_CHUNK_BYTES;                        // 64 KB
-constexpr int CF_EPI = 256;                                                        // 8 epilogue warps: 2 per TMEM lane quarter
+constexpr int CF_PARTS = 4;                                                        // threads per chain row (column split)
+constexpr int CF_EPI = 128 * CF_PARTS;                                             // 16 epilogue warps: 4 per TMEM lane quarter
+constexpr int CF_EPI_WARPS = CF_EPI / 32;
 constexpr int CF_THREADS = CF_EPI + 32;                                            // + 1 control warp
+constexpr int CF_CW = 16;                                                          // columns per TMEM load / work item
 
 __device__ __forceinline__ uint32_t cf_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void cf_mbar_init(uint64_t* bar, uint32_t count) {
@@ -66,30 +77,29 @@ __device__ __forceinline__ void cf_mma(uint32_t tmem_d, uint64_t adesc, uint64_t
 __device__ __forceinline__ uint64_t cf_desc(uint32_t saddr) {
   return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
-__device__ __forceinline__ void cf_tmem_ld32(uint32_t taddr, float* v) {
-  uint32_t r[32];
+__device__ __forceinline__ void cf_tmem_ld16(uint32_t taddr, float (&v)[CF_CW]) {
+  uint32_t r[16];
   asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr));
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+  for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
 }
 // byte offset of (row r, float column k..k+3, k % 4 == 0) inside X (K-major, 128-byte rows, SWIZZLE_128B)
 __device__ __forceinline__ uint32_t cf_xoff(int r, int k) {
   const int c = k >> 5, j = (k & 31) >> 2;
   return (uint32_t)(c * CF_CHUNK_BYTES + (r >> 3) * 1024 + (r & 7) * 128 + ((j ^ (r & 7)) << 4));
 }
-// After the call lane j holds sum over the 32 lanes of v[j] (31 shuffles instead of 160).
-__device__ __forceinline__ float cf_colsum32(float* v, int lane) {
+// After the call lane j (and lane j+16) holds the sum over the 32 lanes of v[j & 15]  (31 shuffles).
+__device__ __forceinline__ float cf_colsum16(float (&v)[CF_CW], int lane) {
 #pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) {
+  for (int i = 0; i < 16; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
+#pragma unroll
+  for (int off = 8; off >= 1; off >>= 1) {
     const bool up = (lane & off) != 0;
 #pragma unroll
     for (int i = 0; i < off; ++i) {
@@ -99,6 +109,23 @@ __device__ __forceinline__ float cf_colsum32(float* v, int lane) {
     }
   }
   return v[0];
+}
+// 16 consecutive floats of a row (zero beyond N / for invalid rows); vector loads when the row is 16-byte aligned
+__device__ __forceinline__ void cf_load16(float (&d)[CF_CW], const float* row, int c0, int N, bool ok, bool vec) {
+#pragma unroll
+  for (int j = 0; j < 16; j += 4) {
+    float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ok && c0 + j < N) {
+      if (vec && c0 + j + 3 < N) q4 = *reinterpret_cast<const float4*>(row + c0 + j);
+      else {
+        q4.x = row[c0 + j];
+        if (c0 + j + 1 < N) q4.y = row[c0 + j + 1];
+        if (c0 + j + 2 < N) q4.z = row[c0 + j + 2];
+        if (c0 + j + 3 < N) q4.w = row[c0 + j + 3];
+      }
+    }
+    d[j] = q4.x; d[j + 1] = q4.y; d[j + 2] = q4.z; d[j + 3] = q4.w;
+  }
 }
 
 __global__ void __launch_bounds__(CF_THREADS, 1)
@@ -116,7 +143,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 4);
   float* rs_acc = reinterpret_cast<float*>(w_full + 6);                       // [G <= 16][128] row-sum staging
   float* sc_s = rs_acc + 16 * 128;                                            // [G <= 16][128] per-sample scale vectors of the step
-  float* ex_s = sc_s + 16 * 128;                                              // [2][128][2] loss partials of the two row halves
+  float* ex_s = sc_s + 16 * 128;                                              // [CF_PARTS][128][2] loss partials of the row parts
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int s = net.s, G = net.G, L = net.L;
@@ -130,9 +157,9 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   // ---- set-up --------------------------------------------------------------------------------------
   for (int e = tid; e < CF_X_BYTES / 16; e += CF_THREADS) reinterpret_cast<float4*>(X)[e] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int e = tid; e < 16 * 128; e += CF_THREADS) rs_acc[e] = 0.f;
-  if (warp == 8) {
+  if (warp == CF_EPI_WARPS) {
     if (lane == 0) {
-      cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(x_ready, CF_EPI);
+      cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(x_ready, CF_EPI_WARPS);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -150,7 +177,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   auto step_K = [&](int t) { const ChainLayerDev& ly = net.layer[step_layer(t)]; return t < L ? ly.n_out : ly.n_in; };
   auto step_N = [&](int t) { const ChainLayerDev& ly = net.layer[step_layer(t)]; return t < L ? ly.n_in : ly.n_out; };
 
-  if (warp == 8) {
+  if (warp == CF_EPI_WARPS) {
     // ===== control thread: weight TMA (one step ahead) and MMA issue =====
     if (lane == 0) {
       auto load_w = [&](int t) {
@@ -163,7 +190,9 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       for (int t = 0; t < n_steps; ++t) {
         const int buf = t & 1;
         cf_mbar_wait(x_ready, t & 1);                       // operand X written by the epilogue threads
+        CF_STAMP(t, 0);
         cf_mbar_wait(w_full + buf, (t >> 1) & 1);           // weight tile landed
+        CF_STAMP(t, 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int K = step_K(t), N = step_N(t);
         const uint32_t n16 = (uint32_t)((N + 15) & ~15);
@@ -175,13 +204,15 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
           cf_mma(tmem_base, cf_desc(xa + off), cf_desc(wa + off), idesc, k > 0 ? 1u : 0u);
         }
         cf_commit(mma_done);
+        CF_STAMP(t, 2);
         if (t + 1 < n_steps) load_w(t + 1);                 // the other buffer was released by step t-1
+        CF_STAMP(t, 3);
       }
     }
   } else {
-    // ===== epilogue threads: thread = chain row = TMEM lane =====
-    const int r = tid & 127;                                // chain row = TMEM lane; two threads per row
-    const int half = tid >> 7;                              // 0: even 32-column chunks, 1: odd chunks
+    // ===== epilogue threads: CF_PARTS threads per chain row (= TMEM lane), each owns every 4th 16-column block =====
+    const int r = tid & 127;
+    const int part = tid >> 7;
     const int qw = warp & 3;                                // TMEM lane quarter of this warp
     const bool row_ok = r < R;
     const int g = row_ok ? r / s : 0;                       // local sample
@@ -189,13 +220,14 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     const long long b = b0 + g;                             // batch sample
     const long long grow = row0 + r;                        // global chain row
     const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16);
-    // samples present in this warp (for the segmented row-sum): rows [32w, 32w+31]
+    // samples present in this warp's 32 rows (for the segmented row-sum)
     const int g_lo = min(32 * qw, R > 0 ? R - 1 : 0) / s, g_hi = min(32 * qw + 31, R > 0 ? R - 1 : 0) / s;
+    const long long ldT = net.ldT;
 
     // X_0 = Q_{L-1} = seed (* sg_{L-1})
     {
       const ChainLayerDev& top = net.layer[L - 1];
-      for (int k = half * 4; k < top.n_out; k += 8) {
+      for (int k = part * 4; k < top.n_out; k += 4 * CF_PARTS) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (row_ok) {
           float t4[4];
@@ -214,13 +246,14 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             *reinterpret_cast<float4*>(ws + top.q_off + grow * top.ld_out + k) = v;
 #pragma unroll
             for (int u = 0; u < 4; ++u)
-              if (k + u < top.n_out) ws[top.qt_off + (long long)(k + u) * net.ldT + grow] = t4[u];
+              if (k + u < top.n_out) ws[top.qt_off + (long long)(k + u) * ldT + grow] = t4[u];
           }
         }
         *reinterpret_cast<float4*>(X + cf_xoff(r, k)) = v;
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      cf_mbar_arrive(x_ready);
+      __syncwarp();
+      if (lane == 0) cf_mbar_arrive(x_ready);
     }
 
     float st_h1 = 0.f, st_rr = 0.f, st_rows = 0.f;
@@ -229,7 +262,6 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       const ChainLayerDev& ly = net.layer[l];
       const bool fwd = t < L;
       const int N = fwd ? ly.n_in : ly.n_out;
-      // operands of this epilogue
       long long sc_off = -1; int sc_ld = 0;   // per-sample column scale [*, N] (workspace offset)
       const float* addv = nullptr;       // residual row [*, N]
       float* gout = nullptr;             // global destination row
@@ -259,6 +291,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         if (ly.act) qrow = ws + ly.q_off + grow * ly.ld_out;      // softplus layers are always materialised
       }
       const bool rs_step = !fwd && ly.act;
+      const bool loss_step = last_fwd && do_loss != 0;
+      const bool store_out = gout != nullptr && (do_backward || !last_fwd || !do_loss);
       // while the MMA runs: stage the per-sample scale vectors of this step in shared memory (coalesced)
       if (sc_off >= 0) {
         for (int e = tid; e < nsamp * 128; e += CF_EPI) {
@@ -268,56 +302,42 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       }
       const float* jrow = nullptr;
       float gscale = 0.f, inv_nj = 0.f;
-      if (last_fwd && do_loss && row_ok) {
+      if (loss_step && row_ok) {
         const long long sb = idx ? idx[b] : b;
         jrow = jt + (sb * s + i_seed) * (long long)net.d_in;
         inv_nj = 1.f / __ldg(jn2 + sb);
         gscale = coef * inv_nj;
       }
-      // prefetch the first chunk of the per-row operand (Q_l row, target-Jacobian row or residual row)
-      const float* prow = rs_step ? qrow : ((last_fwd && do_loss) ? jrow : addv);
+      // per-row operand of this step: Q_l row (row-sum), target-Jacobian row (loss) or residual row
+      const float* prow = rs_step ? qrow : (loss_step ? jrow : addv);
       const bool vec_ok = prow != nullptr && ((reinterpret_cast<uintptr_t>(prow) & 15) == 0);
-      float pre[32];
-      auto prefetch = [&](int c0) {
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (row_ok && prow != nullptr && c0 + j < N) {
-            if (vec_ok && c0 + j + 3 < N) q4 = *reinterpret_cast<const float4*>(prow + c0 + j);
-            else {
-              q4.x = prow[c0 + j];
-              if (c0 + j + 1 < N) q4.y = prow[c0 + j + 1];
-              if (c0 + j + 2 < N) q4.z = prow[c0 + j + 2];
-              if (c0 + j + 3 < N) q4.w = prow[c0 + j + 3];
-            }
-          }
-          pre[j] = q4.x; pre[j + 1] = q4.y; pre[j + 2] = q4.z; pre[j + 3] = q4.w;
-        }
-      };
-      if (half * 32 < N) prefetch(half * 32);
-      asm volatile("bar.sync 1, 256;" ::: "memory");           // scale vectors staged
+      const bool has_p = prow != nullptr;
+      float pre[CF_CW];
+      if (has_p && part * CF_CW < N) cf_load16(pre, prow, part * CF_CW, N, row_ok, vec_ok);
+      asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");       // scale vectors staged
       cf_mbar_wait(mma_done, t & 1);
+      if (tid == 0) CF_STAMP(t, 4);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const float* scale = sc_off >= 0 ? sc_s + g * 128 : nullptr;
       float e_row = 0.f, n_row = 0.f;
-      for (int c0 = half * 32; c0 < N; c0 += 64) {
-        float v[32], opnd[32];
-        cf_tmem_ld32(taddr + (uint32_t)c0, v);
+      for (int c0 = part * CF_CW; c0 < N; c0 += CF_CW * CF_PARTS) {
+        float v[CF_CW], opnd[CF_CW];
+        cf_tmem_ld16(taddr + (uint32_t)c0, v);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) opnd[j] = pre[j];
-        if (c0 + 64 < N) prefetch(c0 + 64);                     // next chunk of this thread, overlapped
+        for (int j = 0; j < CF_CW; ++j) opnd[j] = pre[j];
+        if (has_p && c0 + CF_CW * CF_PARTS < N) cf_load16(pre, prow, c0 + CF_CW * CF_PARTS, N, row_ok, vec_ok);
         if (rs_step) {
-          // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l  (segmented over the <= 2 samples of this warp)
+          // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l  (segmented over the samples of this warp's rows)
           for (int gg = g_lo; gg <= g_hi; ++gg) {
-            float m[32];
+            float m[CF_CW];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) m[j] = (row_ok && g == gg) ? v[j] * opnd[j] : 0.f;
-            const float tot = cf_colsum32(m, lane);
-            if (c0 + lane < N) atomicAdd(&rs_acc[gg * 128 + c0 + lane], tot);
+            for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[j] * opnd[j] : 0.f;
+            const float tot = cf_colsum16(m, lane);
+            if (lane < 16 && c0 + lane < N) atomicAdd(&rs_acc[gg * 128 + c0 + lane], tot);
           }
         }
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
+        for (int j = 0; j < CF_CW; j += 4) {
           const int n = c0 + j;
           float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
           if (row_ok && n < N) {
@@ -330,11 +350,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
               }
             }
             if (scale) { const float4 a = *reinterpret_cast<const float4*>(scale + n); x[0] *= a.x; x[1] *= a.y; x[2] *= a.z; x[3] *= a.w; }
-            if (!fwd && addv) {
-              // (a softplus layer never carries the skip, so opnd holds the residual row here)
-              x[0] += opnd[j]; x[1] += opnd[j + 1]; x[2] += opnd[j + 2]; x[3] += opnd[j + 3];
-            }
-            if (last_fwd && do_loss) {
+            if (!fwd && addv) { x[0] += opnd[j]; x[1] += opnd[j + 1]; x[2] += opnd[j + 2]; x[3] += opnd[j + 3]; }
+            if (loss_step) {
 #pragma unroll
               for (int u = 0; u < 4; ++u) {
                 if (n + u < N) {
@@ -356,31 +373,36 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
               for (int u = 0; u < 4; ++u) x[u] = round_tf32_f(x[u]);
             }
             o = make_float4(x[0], x[1], x[2], x[3]);
-            if (gout && (do_backward || !last_fwd || !do_loss)) {
+            if (store_out) {
               *reinterpret_cast<float4*>(gout + n) = o;
               if (do_backward) {                   // transposed copy: consecutive threads = consecutive rows
 #pragma unroll
                 for (int u = 0; u < 4; ++u)
-                  if (n + u < N) goutT[(long long)(n + u) * net.ldT] = x[u];
+                  if (n + u < N) goutT[(long long)(n + u) * ldT] = x[u];
               }
             }
           }
-          if (write_x && n < CF_MAXW) *reinterpret_cast<float4*>(X + cf_xoff(r, n)) = o;
+          if (write_x) *reinterpret_cast<float4*>(X + cf_xoff(r, n)) = o;
         }
       }
-      // clear the operand columns between N and the 32-float chunk boundary (owner: the half that holds that chunk)
-      if (write_x && N > 0 && (((N - 1) >> 5) & 1) == half) {
-        for (int n = (N + 3) & ~3; n < ((N + 31) & ~31); n += 4)
-          *reinterpret_cast<float4*>(X + cf_xoff(r, n)) = make_float4(0.f, 0.f, 0.f, 0.f);
+      // the next contraction reads X up to the next multiple of 8 columns: clear [round4(N), round8(N))
+      if (write_x) {
+        const int n4 = (N + 3) & ~3;
+        if (n4 < ((N + 7) & ~7) && ((n4 >> 4) & (CF_PARTS - 1)) == part)
+          *reinterpret_cast<float4*>(X + cf_xoff(r, n4)) = make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      if (last_fwd && do_loss) {
+      if (loss_step) {
         if (row_ok) st_h1 += e_row * inv_nj;
-        ex_s[(half * 128 + r) * 2 + 0] = e_row;               // the per-row metric needs the FULL row sums
-        ex_s[(half * 128 + r) * 2 + 1] = n_row;
+        ex_s[(part * 128 + r) * 2 + 0] = e_row;               // the per-row metric needs the FULL row sums
+        ex_s[(part * 128 + r) * 2 + 1] = n_row;
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");           // end of step: sc_s / rs_acc / ex_s are consistent
-      if (last_fwd && do_loss && half == 0 && row_ok) {
-        const float e_all = e_row + ex_s[(128 + r) * 2 + 0], n_all = n_row + ex_s[(128 + r) * 2 + 1];
+      if (tid == 0) CF_STAMP(t, 5);
+      asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");       // end of step: sc_s / rs_acc / ex_s are consistent
+      if (tid == 0) CF_STAMP(t, 6);
+      if (loss_step && part == 0 && row_ok) {
+        float e_all = 0.f, n_all = 0.f;
+#pragma unroll
+        for (int pp = 0; pp < CF_PARTS; ++pp) { e_all += ex_s[(pp * 128 + r) * 2 + 0]; n_all += ex_s[(pp * 128 + r) * 2 + 1]; }
         st_rr += e_all / n_all;
         st_rows += 1.f;
       }
@@ -395,7 +417,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       if (t + 1 < n_steps) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        cf_mbar_arrive(x_ready);
+        __syncwarp();
+        if (lane == 0) cf_mbar_arrive(x_ready);
       }
     }
     if (do_loss) {
@@ -405,7 +428,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         st_rr += __shfl_xor_sync(0xffffffffu, st_rr, o);
         st_rows += __shfl_xor_sync(0xffffffffu, st_rows, o);
       }
-      if (lane == 0) {                 // both column halves of a row carry part of its squared error
+      if (lane == 0) {                 // every column part of a row carries part of its squared error
         if (st_h1 != 0.f) atomicAdd(stats + ST_H1_SUM, st_h1);
         if (st_rows > 0.f) { atomicAdd(stats + ST_JROW_SUM, st_rr); atomicAdd(stats + ST_JROWS, st_rows); }
       }
@@ -413,7 +436,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == 8)
+  if (warp == CF_EPI_WARPS)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
 }
 
@@ -457,10 +480,14 @@ bool chain_fused_supported(const ChainNetDev& net) {
   return true;
 }
 
+cudaError_t chain_fused_read_trace(unsigned long long* out) {
+  return cudaMemcpyFromSymbol(out, g_cf_trace, sizeof(unsigned long long) * 64 * 8);
+}
+
 cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, float* ws, const float* jt, const float* jn2,
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
                                float* stats, cudaStream_t st) {
-  constexpr int SMEM = 3 * CF_X_BYTES + 64 + 2 * 16 * 128 * 4 + 2 * 128 * 2 * 4 + 1024;
+  constexpr int SMEM = 3 * CF_X_BYTES + 64 + 2 * 16 * 128 * 4 + CF_PARTS * 128 * 2 * 4 + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(chain_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);

@@ -148,6 +148,8 @@ cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, fl
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
                                float* stats, cudaStream_t st);
 
+cudaError_t chain_fused_read_trace(unsigned long long* out);
+
 // statistics slots accumulated by the loss kernels (floats)
 enum { ST_L2_SUM = 0, ST_H1_SUM = 1, ST_EQ_SUM = 2, ST_NQ_SUM = 3, ST_JROW_SUM = 4, ST_COUNT = 5,
        ST_JROWS = 6, ST_SLOTS = 8 };

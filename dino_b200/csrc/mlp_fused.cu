@@ -15,18 +15,30 @@ constexpr int MT = 256;          // threads per CTA
 
 static inline int cdiv_i(int a, int b) { return (a + b - 1) / b; }
 
+// Asynchronous copy of one layer's kernel block (a flat run of r4(n_in*n_out) floats, 16-byte aligned in the
+// parameter arena) into shared memory: cp.async, no register staging, one commit group per layer.
+__device__ __forceinline__ void stage_weights_async(float* dst, const float* __restrict__ src, int floats) {
+  const int vecs = (floats + 3) >> 2;
+  for (int e = threadIdx.x; e < vecs; e += MT) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst + 4 * e);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + 4 * e) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void wait_weights_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void wait_weights_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
 // ---- forward: one layer for the CTA's TS samples --------------------------------------------------
 // NC threads span the columns, the remaining MT/NC thread groups split the reduction index k; the
 // partial sums meet in shared memory.  (The layer is a latency chain of L2 weight loads; splitting k
 // shortens it by MT/NC.)
 template <int NC>
-__device__ __forceinline__ void fwd_layer(const MlpLayerDev& ly, const float* __restrict__ params,
+__device__ __forceinline__ void fwd_layer(const MlpLayerDev& ly, const float* __restrict__ params, const float* W,
                                           const float* zin, int ld_zin, float* zout, const float* zskip, int ld_skip,
                                           float* __restrict__ ws, int b0, int nb, float* red) {
   constexpr int KG = MT / NC;
   const int tid = threadIdx.x;
   const int cl = tid % NC, kg = tid / NC;
-  const float* __restrict__ W = params + ly.koff;
   for (int c0 = 0; c0 < ly.n_out; c0 += NC) {
     const int c = c0 + cl;
     float acc[TS];
@@ -35,7 +47,7 @@ __device__ __forceinline__ void fwd_layer(const MlpLayerDev& ly, const float* __
     if (c < ly.n_out) {
 #pragma unroll 4
       for (int k = kg; k < ly.n_in; k += KG) {
-        const float w = __ldg(W + (long long)k * ly.n_out + c);
+        const float w = W[k * ly.n_out + c];                 // shared memory, lanes = consecutive columns
 #pragma unroll
         for (int t = 0; t < TS; ++t) acc[t] = fmaf(zin[t * ld_zin + k], w, acc[t]);
       }
@@ -64,13 +76,16 @@ __device__ __forceinline__ void fwd_layer(const MlpLayerDev& ly, const float* __
 __global__ void __launch_bounds__(MT) mlp_forward_fused_kernel(const __grid_constant__ MlpNetDev net,
                                                                const float* __restrict__ params, float* __restrict__ ws,
                                                                const float* __restrict__ m, const int* __restrict__ idx,
-                                                               int B) {
+                                                               int B, int w_floats) {
   extern __shared__ float sm[];
   __shared__ float red[MT * TS];
   const int b0 = blockIdx.x * TS;
   const int nb = min(TS, B - b0);
-  // shared layout: z_0 [TS, ld_in], then the output of every layer [TS, ld_out]
-  float* z0 = sm;
+  // shared layout: weight tiles [2][w_floats] | z_0 [TS, ld_in] | the output of every layer [TS, ld_out]
+  float* Wbuf[2] = {sm, sm + w_floats};
+  float* z0 = sm + 2 * w_floats;
+  auto wsize = [&](int l) { return (net.layer[l].n_in * net.layer[l].n_out + 3) & ~3; };
+  stage_weights_async(Wbuf[0], params + net.layer[0].koff, wsize(0));
   for (int e = threadIdx.x; e < TS * net.ld_in; e += MT) {
     const int t = e / net.ld_in, k = e % net.ld_in;
     float v = 0.f;
@@ -81,25 +96,30 @@ __global__ void __launch_bounds__(MT) mlp_forward_fused_kernel(const __grid_cons
     }
     z0[e] = v;
   }
-  __syncthreads();
   int off = TS * net.ld_in;
   const float* zin = z0;
   int ld_zin = net.ld_in;
 #pragma unroll 1
   for (int l = 0; l < net.L; ++l) {
     const MlpLayerDev& ly = net.layer[l];
-    float* zout = sm + off;
+    // prefetch the next layer's weights into the other buffer (its previous reader, layer l-1, has finished:
+    // every fwd_layer ends with a block-wide barrier), then wait for this layer's tile
+    if (l + 1 < net.L) { stage_weights_async(Wbuf[(l + 1) & 1], params + net.layer[l + 1].koff, wsize(l + 1)); wait_weights_but_one(); }
+    else wait_weights_all();
+    __syncthreads();
+    const float* W = Wbuf[l & 1];
+    float* zout = z0 + off;
     const float* zskip = nullptr;
     int ld_skip = 0;
     if (ly.skip_from >= 0) {
       // input of layer skip_from: z_0 or the output of layer skip_from-1
       int so = 0, j = 0, ld = net.ld_in;
       for (; j < ly.skip_from; ++j) { so += TS * ld; ld = net.layer[j].ld_out; }
-      zskip = sm + so; ld_skip = ld;
+      zskip = z0 + so; ld_skip = ld;
     }
-    if (ly.n_out <= 64) fwd_layer<64>(ly, params, zin, ld_zin, zout, zskip, ld_skip, ws, b0, nb, red);
-    else if (ly.n_out <= 128) fwd_layer<128>(ly, params, zin, ld_zin, zout, zskip, ld_skip, ws, b0, nb, red);
-    else fwd_layer<256>(ly, params, zin, ld_zin, zout, zskip, ld_skip, ws, b0, nb, red);
+    if (ly.n_out <= 64) fwd_layer<64>(ly, params, W, zin, ld_zin, zout, zskip, ld_skip, ws, b0, nb, red);
+    else if (ly.n_out <= 128) fwd_layer<128>(ly, params, W, zin, ld_zin, zout, zskip, ld_skip, ws, b0, nb, red);
+    else fwd_layer<256>(ly, params, W, zin, ld_zin, zout, zskip, ld_skip, ws, b0, nb, red);
     zin = zout; ld_zin = ly.ld_out;
     off += TS * ly.ld_out;
   }
@@ -151,9 +171,12 @@ __global__ void __launch_bounds__(MT) mlp_backward_fused_kernel(const __grid_con
   const int b0 = blockIdx.x * TS;
   const int nb = min(TS, B - b0);
   const int ld_dz = net.ld_dz;
-  // shared layout: W tile [w_floats] | dz[3][TS, ld_dz] | da [TS, ld_dz]
-  float* Ws = sm;
-  float* dzb = sm + w_floats;
+  // shared layout: W tiles [2][w_floats] | dz[3][TS, ld_dz] | da [TS, ld_dz]
+  float* Wbuf[2] = {sm, sm + w_floats};
+  float* dzb = sm + 2 * w_floats;
+  if (net.L - 1 > net.lowest_trainable)
+    stage_weights_async(Wbuf[(net.L - 1) & 1], params + net.layer[net.L - 1].koff,
+                        (net.layer[net.L - 1].n_in * net.layer[net.L - 1].n_out + 3) & ~3);
   float* da = dzb + 3 * TS * ld_dz;
   auto dz_buf = [&](int l) { return dzb + (l % 3) * TS * ld_dz; };
   {
@@ -186,10 +209,14 @@ __global__ void __launch_bounds__(MT) mlp_backward_fused_kernel(const __grid_con
       da[t * ld_dz + n] = v;
     }
     const bool need_dz = l > net.lowest_trainable;
-    const int ldw = ly.n_out | 1;                    // odd row pitch: conflict-free column walks
-    if (need_dz) {
-      const float* __restrict__ W = params + ly.koff;
-      for (int e = threadIdx.x; e < ly.n_in * ly.n_out; e += MT) Ws[(e / ly.n_out) * ldw + (e % ly.n_out)] = __ldg(W + e);
+    const int ldw = ly.n_out;                        // natural pitch of the asynchronously staged tile
+    const float* Ws = Wbuf[l & 1];
+    // prefetch the weights of the layer below (needed only if that layer still propagates dz)
+    if (l - 1 > net.lowest_trainable) {
+      stage_weights_async(Wbuf[(l - 1) & 1], params + net.layer[l - 1].koff, (net.layer[l - 1].n_in * net.layer[l - 1].n_out + 3) & ~3);
+      wait_weights_but_one();
+    } else {
+      wait_weights_all();
     }
     __syncthreads();
     if (ly.trainable && ly.boff >= 0) {
@@ -212,21 +239,29 @@ __global__ void __launch_bounds__(MT) mlp_backward_fused_kernel(const __grid_con
 }
 
 // ---- host ---------------------------------------------------------------------------------------------
+static int fwd_w_floats(const MlpNetDev& net) {
+  int w = 0;
+  for (int l = 0; l < net.L; ++l) {
+    const int f = (net.layer[l].n_in * net.layer[l].n_out + 3) & ~3;
+    w = f > w ? f : w;
+  }
+  return w;
+}
 static size_t fwd_smem(const MlpNetDev& net) {
-  size_t f = (size_t)TS * net.ld_in;
+  size_t f = (size_t)TS * net.ld_in + 2 * (size_t)fwd_w_floats(net);
   for (int l = 0; l < net.L; ++l) f += (size_t)TS * net.layer[l].ld_out;
   return f * sizeof(float);
 }
 static int bwd_w_floats(const MlpNetDev& net) {
   int w = 0;
   for (int l = net.lowest_trainable + 1; l < net.L; ++l) {
-    const int f = net.layer[l].n_in * (net.layer[l].n_out | 1);
+    const int f = (net.layer[l].n_in * net.layer[l].n_out + 3) & ~3;
     w = f > w ? f : w;
   }
-  return (w + 3) & ~3;
+  return w > 4 ? w : 4;
 }
 static size_t bwd_smem(const MlpNetDev& net) {
-  return ((size_t)bwd_w_floats(net) + 4 * (size_t)TS * net.ld_dz) * sizeof(float);
+  return (2 * (size_t)bwd_w_floats(net) + 4 * (size_t)TS * net.ld_dz) * sizeof(float);
 }
 
 bool mlp_fused_supported(const MlpNetDev& net) {
@@ -244,12 +279,12 @@ cudaError_t launch_mlp_forward_fused(const MlpNetDev& net, const float* params, 
                                      const int* idx, int B, cudaStream_t st) {
   const size_t smem = fwd_smem(net);
   static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  if (smem > 40 * 1024 && smem > configured) {   // static (4 KB) + dynamic share the 48 KB default limit
     cudaError_t e = cudaFuncSetAttribute(mlp_forward_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     configured = smem;
   }
-  mlp_forward_fused_kernel<<<cdiv_i(B, TS), MT, smem, st>>>(net, params, ws, m, idx, B);
+  mlp_forward_fused_kernel<<<cdiv_i(B, TS), MT, smem, st>>>(net, params, ws, m, idx, B, fwd_w_floats(net));
   return cudaGetLastError();
 }
 
@@ -257,7 +292,7 @@ cudaError_t launch_mlp_backward_fused(const MlpNetDev& net, const float* params,
                                       int with_rowsum, cudaStream_t st) {
   const size_t smem = bwd_smem(net);
   static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  if (smem > 40 * 1024 && smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(mlp_backward_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     configured = smem;

@@ -770,3 +770,11 @@ extern "C" int dino_gemm_nt_acc(int engine, const float* XT, int64_t ldx, const 
   }
   return 0;
 }
+
+// debug aid: per-phase timestamps of the fused chain kernel (zeros unless built with -DDINO_CF_TRACE)
+extern "C" int dino_debug_chain_trace(uint64_t* out_64x8) {
+  if (!out_64x8) return fail("dino_debug_chain_trace: null argument");
+  DINO_CUDA(cudaDeviceSynchronize());
+  DINO_CUDA(chain_fused_read_trace(reinterpret_cast<unsigned long long*>(out_64x8)));
+  return 0;
+}

@@ -183,6 +183,10 @@ int dino_gemm_nt(int engine, const float* d_A, int64_t lda, const float* d_Bt, i
 int dino_gemm_nt_acc(int engine, const float* d_XT, int64_t ldx, const float* d_YT, int64_t ldy, float* d_C,
                      int32_t rows, int32_t n_in, int32_t n_out, dino_stream_t stream);
 
+/* Debug aid: %globaltimer stamps [step][phase] of CTA 0 of the fused chain kernel's last launch (all zero unless
+ * the library was built with -DDINO_CF_TRACE).  Synchronises the device.  No counterpart in the reference. */
+int dino_debug_chain_trace(uint64_t* out_64x8);
+
 /* number of kernels this library has launched in the calling process (bench.py gpu_launches) */
 int64_t dino_launch_count(void);
 
