@@ -31,8 +31,8 @@ __device__ unsigned long long g_cf_trace[64 * 8];
 
 constexpr int CF_ROWS = 128, CF_MAXW = 128, CF_CHUNK_BYTES = CF_ROWS * 128;       // 16 KB per 32-float K chunk
 constexpr int CF_X_BYTES = (CF_MAXW / 32) * CF_CHUNK_BYTES;                        // 64 KB
-constexpr int CF_PARTS = 4;                                                        // threads per chain row (column split)
-constexpr int CF_EPI = 128 * CF_PARTS;                                             // 16 epilogue warps: 4 per TMEM lane quarter
+constexpr int CF_PARTS = 2;                                                        // threads per chain row (column split)
+constexpr int CF_EPI = 128 * CF_PARTS;                                             // 8 epilogue warps: 2 per TMEM lane quarter
 constexpr int CF_EPI_WARPS = CF_EPI / 32;
 constexpr int CF_THREADS = CF_EPI + 32;                                            // + 1 control warp
 constexpr int CF_CW = 16;                                                          // columns per TMEM load / work item
@@ -128,11 +128,18 @@ __device__ __forceinline__ void cf_load16(float (&d)[CF_CW], const float* row, i
   }
 }
 
+// 16 consecutive columns of chain row `grow` from a TRANSPOSED array (element n at base[n * ldT]): lanes =
+// consecutive rows, so every load instruction is one coalesced 128-byte request
+__device__ __forceinline__ void cf_load16T(float (&d)[CF_CW], const float* base, int c0, int N, bool ok, long long ldT) {
+#pragma unroll
+  for (int j = 0; j < CF_CW; ++j) d[j] = (ok && c0 + j < N) ? base[(long long)(c0 + j) * ldT] : 0.f;
+}
+
 __global__ void __launch_bounds__(CF_THREADS, 1)
 chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ ChainNetDev net,
-                   float* __restrict__ ws, const float* __restrict__ jt, const float* __restrict__ jn2,
-                   const int* __restrict__ idx, const float* __restrict__ seed, int B, float coef, int do_loss,
-                   int do_backward, float* __restrict__ stats) {
+                   const __grid_constant__ ChainSteps steps, float* __restrict__ ws, const float* __restrict__ jt,
+                   const float* __restrict__ jn2, const int* __restrict__ idx, const float* __restrict__ seed, int B,
+                   float coef, int do_loss, int do_backward, float* __restrict__ stats) {
   extern __shared__ uint8_t cf_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cf_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* X = smem;
@@ -144,6 +151,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   float* rs_acc = reinterpret_cast<float*>(w_full + 6);                       // [G <= 16][128] row-sum staging
   float* sc_s = rs_acc + 16 * 128;                                            // [G <= 16][128] per-sample scale vectors of the step
   float* ex_s = sc_s + 16 * 128;                                              // [CF_PARTS][128][2] loss partials of the row parts
+  ChainStep* st_s = reinterpret_cast<ChainStep*>(ex_s + CF_PARTS * 128 * 2);   // step table (constant-bank indexed loads are slow)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int s = net.s, G = net.G, L = net.L;
@@ -151,12 +159,22 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   const int nsamp = min(G, B - b0);
   const int R = nsamp * s;                       // valid chain rows of this CTA
   const long long row0 = (long long)b0 * s;      // first global chain row
-  // the backward contraction of a LINEAR top layer produces nothing anybody reads (R_L is the constant seed)
-  const int n_steps = L + (do_backward ? (net.layer[L - 1].act ? L : L - 1) : 0);
+#ifdef DINO_CF_TRACE
+  const int dbg = do_backward >> 8;      // experiment knobs: 1 skip transposed stores, 2 skip X writes, 4 skip TMEM loads, 8 skip rounding
+  do_backward &= 0xff;
+#else
+  const int dbg = 0;
+#endif
+  const int n_steps = do_backward ? steps.n_all : steps.n_fwd;
 
   // ---- set-up --------------------------------------------------------------------------------------
   for (int e = tid; e < CF_X_BYTES / 16; e += CF_THREADS) reinterpret_cast<float4*>(X)[e] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int e = tid; e < 16 * 128; e += CF_THREADS) rs_acc[e] = 0.f;
+  {
+    const int words = (int)(sizeof(ChainStep) / 4) * steps.n_all;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&steps.st[0]);
+    for (int e = tid; e < words; e += CF_THREADS) reinterpret_cast<uint32_t*>(st_s)[e] = src[e];
+  }
   if (warp == CF_EPI_WARPS) {
     if (lane == 0) {
       cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(x_ready, CF_EPI_WARPS);
@@ -172,33 +190,29 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
 
-  // step t: t < L -> forward layer l = L-1-t ; t >= L -> backward layer l = t-L
-  auto step_layer = [&](int t) { return t < L ? L - 1 - t : t - L; };
-  auto step_K = [&](int t) { const ChainLayerDev& ly = net.layer[step_layer(t)]; return t < L ? ly.n_out : ly.n_in; };
-  auto step_N = [&](int t) { const ChainLayerDev& ly = net.layer[step_layer(t)]; return t < L ? ly.n_in : ly.n_out; };
-
   if (warp == CF_EPI_WARPS) {
     // ===== control thread: weight TMA (one step ahead) and MMA issue =====
     if (lane == 0) {
       auto load_w = [&](int t) {
-        const int K = step_K(t), nch = (K + 31) >> 5, buf = t & 1;
-        const CUtensorMap* map = t < L ? &maps.fwd[step_layer(t)] : &maps.bwd[step_layer(t)];
+        const int nch = (st_s[t].K + 31) >> 5, buf = t & 1;
+        const CUtensorMap* map = t < L ? &maps.fwd[L - 1 - t] : &maps.bwd[t - L];
         cf_mbar_expect_tx(w_full + buf, (uint32_t)nch * CF_CHUNK_BYTES);
         for (int c = 0; c < nch; ++c) cf_tma_load(Wb[buf] + c * CF_CHUNK_BYTES, map, c * 32, 0, w_full + buf);
       };
       load_w(0);
+      const uint32_t xa = cf_smem_u32(X);
       for (int t = 0; t < n_steps; ++t) {
         const int buf = t & 1;
+        const int K = st_s[t].K, N = st_s[t].N;
+        const uint32_t n16 = (uint32_t)((N + 15) & ~15);
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((n16 >> 3) << 17) | ((128u >> 4) << 24);
+        const uint32_t wa = cf_smem_u32(Wb[buf]);
+        const int ksteps = (K + 7) >> 3;
         cf_mbar_wait(x_ready, t & 1);                       // operand X written by the epilogue threads
         CF_STAMP(t, 0);
         cf_mbar_wait(w_full + buf, (t >> 1) & 1);           // weight tile landed
         CF_STAMP(t, 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int K = step_K(t), N = step_N(t);
-        const uint32_t n16 = (uint32_t)((N + 15) & ~15);
-        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((n16 >> 3) << 17) | ((128u >> 4) << 24);
-        const uint32_t xa = cf_smem_u32(X), wa = cf_smem_u32(Wb[buf]);
-        const int ksteps = (K + 7) >> 3;
         for (int k = 0; k < ksteps; ++k) {
           const uint32_t off = (uint32_t)((k >> 2) * CF_CHUNK_BYTES + (k & 3) * 32);
           cf_mma(tmem_base, cf_desc(xa + off), cf_desc(wa + off), idesc, k > 0 ? 1u : 0u);
@@ -210,7 +224,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       }
     }
   } else {
-    // ===== epilogue threads: CF_PARTS threads per chain row (= TMEM lane), each owns every 4th 16-column block =====
+    // ===== epilogue threads: CF_PARTS threads per chain row (= TMEM lane), alternating 16-column blocks =====
     const int r = tid & 127;
     const int part = tid >> 7;
     const int qw = warp & 3;                                // TMEM lane quarter of this warp
@@ -220,9 +234,10 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     const long long b = b0 + g;                             // batch sample
     const long long grow = row0 + r;                        // global chain row
     const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16);
-    // samples present in this warp's 32 rows (for the segmented row-sum)
     const int g_lo = min(32 * qw, R > 0 ? R - 1 : 0) / s, g_hi = min(32 * qw + 31, R > 0 ? R - 1 : 0) / s;
     const long long ldT = net.ldT;
+    const uint32_t xrow = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
+    const int xsw = r & 7;
 
     // X_0 = Q_{L-1} = seed (* sg_{L-1})
     {
@@ -242,8 +257,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             t4[u] = x;
           }
           v = make_float4(t4[0], t4[1], t4[2], t4[3]);
-          if (net.top_materialised) {
-            *reinterpret_cast<float4*>(ws + top.q_off + grow * top.ld_out + k) = v;
+          if (net.top_materialised && (do_backward || net.has_skip)) {
 #pragma unroll
             for (int u = 0; u < 4; ++u)
               if (k + u < top.n_out) ws[top.qt_off + (long long)(k + u) * ldT + grow] = t4[u];
@@ -257,76 +271,71 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     }
 
     float st_h1 = 0.f, st_rr = 0.f, st_rows = 0.f;
+#pragma unroll 1
     for (int t = 0; t < n_steps; ++t) {
-      const int l = step_layer(t);
-      const ChainLayerDev& ly = net.layer[l];
-      const bool fwd = t < L;
-      const int N = fwd ? ly.n_in : ly.n_out;
-      long long sc_off = -1; int sc_ld = 0;   // per-sample column scale [*, N] (workspace offset)
-      const float* addv = nullptr;       // residual row [*, N]
-      float* gout = nullptr;             // global destination row
-      float* goutT = nullptr;            // transposed destination: element (n, row) at goutT[n * ldT]
-      const float* qrow = nullptr;       // Q_l row (backward row-sum)
-      bool last_fwd = false, write_x = true;
-      if (fwd) {
-        if (l > 0) {
-          const ChainLayerDev& below = net.layer[l - 1];
-          if (below.act) { sc_off = below.sg_off; sc_ld = below.ld_out; }
-          gout = ws + below.q_off + grow * below.ld_out;
-          goutT = ws + below.qt_off + grow;
-        } else {
-          last_fwd = true;
-          gout = ws + net.r0_off + grow * net.ld_in;
-          goutT = ws + net.r0t_off + grow;
-          write_x = do_backward != 0;
-        }
-        if (ly.lands_skip >= 0) { const ChainLayerDev& sk = net.layer[ly.lands_skip]; addv = ws + sk.q_off + grow * sk.ld_out; }
-      } else {
-        if (ly.act) { sc_off = ly.sg_off; sc_ld = ly.ld_out; }
-        if (l < L - 1) { gout = ws + ly.dr_off + grow * ly.ld_out; goutT = ws + ly.drt_off + grow; } else write_x = false;
-        if (ly.skip_from >= 0 && l < L - 1) {
-          const int j = ly.skip_from;
-          addv = j == 0 ? ws + net.r0_off + grow * net.ld_in : ws + net.layer[j - 1].dr_off + grow * net.layer[j - 1].ld_out;
-        }
-        if (ly.act) qrow = ws + ly.q_off + grow * ly.ld_out;      // softplus layers are always materialised
+      // ---- this step's descriptor (from the shared-memory copy) ----
+      const ChainStep sd = st_s[t];
+      const int N = sd.N;
+      int mode = sd.mode;
+      const bool add_first = sd.add_first != 0;
+      bool write_x = sd.write_x != 0;
+      const long long sc_off = sd.sc_off;
+      const int sc_ld = sd.sc_ld;
+      // row-major output only for the Jacobian itself when it is the product asked for (no loss, no backward);
+      // the training path keeps nothing but the transposed copies, whose stores and loads are coalesced
+      float* out = (sd.mode == 1 && !do_loss) ? ws + sd.out_off + grow * sd.out_ld : nullptr;
+      // (a residual network re-reads earlier chain states, so it needs the transposed copies even without a backward pass)
+      float* outT = ((do_backward || net.has_skip) && sd.outT_off >= 0) ? ws + sd.outT_off + grow : nullptr;
+      const float* addT = sd.add_off >= 0 ? ws + sd.add_off + grow : nullptr;   // transposed residual
+      const long long rs_off = sd.rs_off;
+      const int rs_ld = sd.rs_ld;
+      const float* prow = nullptr;                  // per-row operand: Q_l row (row-sum) or target-Jacobian row (loss)
+      float gscale = 0.f, inv_nj = 0.f;
+      if (mode == 1) {
+        if (!do_loss) mode = 0;                     // Jacobian only: plain row-major output
+        if (!do_backward) write_x = false;
       }
-      const bool rs_step = !fwd && ly.act;
-      const bool loss_step = last_fwd && do_loss != 0;
-      const bool store_out = gout != nullptr && (do_backward || !last_fwd || !do_loss);
-      // while the MMA runs: stage the per-sample scale vectors of this step in shared memory (coalesced)
+      const float* qT = mode == 2 ? ws + sd.q_off + grow : nullptr;    // transposed Q_l (row-sum operand)
+      if (mode == 1 && row_ok) {
+        const long long sb = idx ? idx[b] : b;
+        prow = jt + (sb * s + i_seed) * (long long)net.d_in;
+        inv_nj = 1.f / __ldg(jn2 + sb);
+        gscale = coef * inv_nj;
+      }
+      const bool vec_ok = prow != nullptr && ((reinterpret_cast<uintptr_t>(prow) & 15) == 0);
+      const bool do_round = (write_x || outT != nullptr) && !(dbg & 8);     // only what feeds a later TF32 contraction is rounded
+      // ---- while the MMA runs: stage the per-sample scale vectors, prefetch the first operand block ----
       if (sc_off >= 0) {
         for (int e = tid; e < nsamp * 128; e += CF_EPI) {
           const int gg = e >> 7, n = e & 127;
           sc_s[e] = n < N ? ws[sc_off + (long long)(b0 + gg) * sc_ld + n] : 0.f;
         }
       }
-      const float* jrow = nullptr;
-      float gscale = 0.f, inv_nj = 0.f;
-      if (loss_step && row_ok) {
-        const long long sb = idx ? idx[b] : b;
-        jrow = jt + (sb * s + i_seed) * (long long)net.d_in;
-        inv_nj = 1.f / __ldg(jn2 + sb);
-        gscale = coef * inv_nj;
+      float opnd[CF_CW];
+#pragma unroll
+      for (int j = 0; j < CF_CW; ++j) opnd[j] = 0.f;
+      if (part * CF_CW < N) {
+        if (qT != nullptr) cf_load16T(opnd, qT, part * CF_CW, N, row_ok, ldT);
+        else if (prow != nullptr) cf_load16(opnd, prow, part * CF_CW, N, row_ok, vec_ok);
       }
-      // per-row operand of this step: Q_l row (row-sum), target-Jacobian row (loss) or residual row
-      const float* prow = rs_step ? qrow : (loss_step ? jrow : addv);
-      const bool vec_ok = prow != nullptr && ((reinterpret_cast<uintptr_t>(prow) & 15) == 0);
-      const bool has_p = prow != nullptr;
-      float pre[CF_CW];
-      if (has_p && part * CF_CW < N) cf_load16(pre, prow, part * CF_CW, N, row_ok, vec_ok);
       asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");       // scale vectors staged
       cf_mbar_wait(mma_done, t & 1);
       if (tid == 0) CF_STAMP(t, 4);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const float* scale = sc_off >= 0 ? sc_s + g * 128 : nullptr;
       float e_row = 0.f, n_row = 0.f;
+#pragma unroll 1
       for (int c0 = part * CF_CW; c0 < N; c0 += CF_CW * CF_PARTS) {
-        float v[CF_CW], opnd[CF_CW];
-        cf_tmem_ld16(taddr + (uint32_t)c0, v);
+        float v[CF_CW];
+        if (dbg & 4) {
 #pragma unroll
-        for (int j = 0; j < CF_CW; ++j) opnd[j] = pre[j];
-        if (has_p && c0 + CF_CW * CF_PARTS < N) cf_load16(pre, prow, c0 + CF_CW * CF_PARTS, N, row_ok, vec_ok);
-        if (rs_step) {
+          for (int j = 0; j < CF_CW; ++j) v[j] = 1.f;
+        } else cf_tmem_ld16(taddr + (uint32_t)c0, v);
+        if (c0 != part * CF_CW) {
+          if (qT != nullptr) cf_load16T(opnd, qT, c0, N, row_ok, ldT);
+          else if (prow != nullptr) cf_load16(opnd, prow, c0, N, row_ok, vec_ok);
+        }
+        if (mode == 2) {
           // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l  (segmented over the samples of this warp's rows)
           for (int gg = g_lo; gg <= g_hi; ++gg) {
             float m[CF_CW];
@@ -336,22 +345,67 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             if (lane < 16 && c0 + lane < N) atomicAdd(&rs_acc[gg * 128 + c0 + lane], tot);
           }
         }
+        if (row_ok && addT == nullptr && c0 + CF_CW <= N) {
+          // ---- fast path: a full 16-column block of a valid row, no residual: no per-element guards ----
+          float x[CF_CW];
+          if (scale != nullptr) {
+#pragma unroll
+            for (int j = 0; j < CF_CW; j += 4) {
+              const float4 a = *reinterpret_cast<const float4*>(scale + c0 + j);
+              x[j] = v[j] * a.x; x[j + 1] = v[j + 1] * a.y; x[j + 2] = v[j + 2] * a.z; x[j + 3] = v[j + 3] * a.w;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) x[j] = v[j];
+          }
+          if (mode == 1) {
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) {
+              const float tv = opnd[j];
+              const float d = x[j] - tv;
+              e_row = fmaf(d, d, e_row);
+              n_row = fmaf(tv, tv, n_row);
+              x[j] = gscale * d;
+            }
+          }
+          if (do_round) {
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) x[j] = round_tf32_f(x[j]);
+          }
+          if (outT != nullptr) {                     // transposed copy: one coalesced 128-byte store per column
+            float* pT = outT + (long long)c0 * ldT;
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) { *pT = x[j]; pT += ldT; }
+          }
+          if (out != nullptr) {
+#pragma unroll
+            for (int j = 0; j < CF_CW; j += 4) *reinterpret_cast<float4*>(out + c0 + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+          }
+          if (write_x) {
+            uint8_t* xb = X + (uint32_t)((c0 >> 5) * CF_CHUNK_BYTES) + xrow;
+            const int j0 = (c0 & 31) >> 2;
+#pragma unroll
+            for (int j = 0; j < CF_CW; j += 4)
+              *reinterpret_cast<float4*>(xb + (((j0 + (j >> 2)) ^ xsw) << 4)) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+          }
+        } else if (row_ok) {
+          // ---- generic path: tail block of a row and/or residual add ----
 #pragma unroll
         for (int j = 0; j < CF_CW; j += 4) {
           const int n = c0 + j;
           float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
           if (row_ok && n < N) {
             float x[4] = {v[j], v[j + 1], v[j + 2], v[j + 3]};
-            if (fwd && addv) {
-              if (prow == addv) { x[0] += opnd[j]; x[1] += opnd[j + 1]; x[2] += opnd[j + 2]; x[3] += opnd[j + 3]; }
-              else {
+            if (addT != nullptr && add_first) {
 #pragma unroll
-                for (int u = 0; u < 4; ++u) if (n + u < N) x[u] += addv[n + u];
-              }
+              for (int u = 0; u < 4; ++u) if (n + u < N) x[u] += addT[(long long)(n + u) * ldT];
             }
-            if (scale) { const float4 a = *reinterpret_cast<const float4*>(scale + n); x[0] *= a.x; x[1] *= a.y; x[2] *= a.z; x[3] *= a.w; }
-            if (!fwd && addv) { x[0] += opnd[j]; x[1] += opnd[j + 1]; x[2] += opnd[j + 2]; x[3] += opnd[j + 3]; }
-            if (loss_step) {
+            if (scale != nullptr) { const float4 a = *reinterpret_cast<const float4*>(scale + n); x[0] *= a.x; x[1] *= a.y; x[2] *= a.z; x[3] *= a.w; }
+            if (addT != nullptr && !add_first) {
+#pragma unroll
+              for (int u = 0; u < 4; ++u) if (n + u < N) x[u] += addT[(long long)(n + u) * ldT];
+            }
+            if (mode == 1) {
 #pragma unroll
               for (int u = 0; u < 4; ++u) {
                 if (n + u < N) {
@@ -360,30 +414,22 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                   e_row = fmaf(d, d, e_row);
                   n_row = fmaf(tv, tv, n_row);
                   x[u] = gscale * d;
-                } else {
-                  x[u] = 0.f;
                 }
               }
-            } else {
-#pragma unroll
-              for (int u = 0; u < 4; ++u) x[u] = (n + u < N) ? x[u] : 0.f;
             }
-            if (!last_fwd || do_loss) {            // everything that feeds a later TF32 contraction
 #pragma unroll
-              for (int u = 0; u < 4; ++u) x[u] = round_tf32_f(x[u]);
-            }
+            for (int u = 0; u < 4; ++u) x[u] = (n + u < N) ? (do_round ? round_tf32_f(x[u]) : x[u]) : 0.f;
             o = make_float4(x[0], x[1], x[2], x[3]);
-            if (store_out) {
-              *reinterpret_cast<float4*>(gout + n) = o;
-              if (do_backward) {                   // transposed copy: consecutive threads = consecutive rows
+            if (out != nullptr) *reinterpret_cast<float4*>(out + n) = o;
+            if (outT != nullptr && !(dbg & 1)) {                 // transposed copy: consecutive threads = consecutive rows
 #pragma unroll
-                for (int u = 0; u < 4; ++u)
-                  if (n + u < N) goutT[(long long)(n + u) * ldT] = x[u];
-              }
+              for (int u = 0; u < 4; ++u)
+                if (n + u < N) outT[(long long)(n + u) * ldT] = x[u];
             }
           }
-          if (write_x) *reinterpret_cast<float4*>(X + cf_xoff(r, n)) = o;
+          if (write_x && !(dbg & 2)) *reinterpret_cast<float4*>(X + (uint32_t)((n >> 5) * CF_CHUNK_BYTES) + xrow + ((((n & 31) >> 2) ^ xsw) << 4)) = o;
         }
+              }
       }
       // the next contraction reads X up to the next multiple of 8 columns: clear [round4(N), round8(N))
       if (write_x) {
@@ -391,7 +437,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         if (n4 < ((N + 7) & ~7) && ((n4 >> 4) & (CF_PARTS - 1)) == part)
           *reinterpret_cast<float4*>(X + cf_xoff(r, n4)) = make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      if (loss_step) {
+      if (mode == 1) {
         if (row_ok) st_h1 += e_row * inv_nj;
         ex_s[(part * 128 + r) * 2 + 0] = e_row;               // the per-row metric needs the FULL row sums
         ex_s[(part * 128 + r) * 2 + 1] = n_row;
@@ -399,18 +445,17 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       if (tid == 0) CF_STAMP(t, 5);
       asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");       // end of step: sc_s / rs_acc / ex_s are consistent
       if (tid == 0) CF_STAMP(t, 6);
-      if (loss_step && part == 0 && row_ok) {
+      if (mode == 1 && part == 0 && row_ok) {
         float e_all = 0.f, n_all = 0.f;
 #pragma unroll
         for (int pp = 0; pp < CF_PARTS; ++pp) { e_all += ex_s[(pp * 128 + r) * 2 + 0]; n_all += ex_s[(pp * 128 + r) * 2 + 1]; }
         st_rr += e_all / n_all;
         st_rows += 1.f;
       }
-      // publish the row sums of this layer
-      if (rs_step) {
+      if (mode == 2) {                                          // publish the row sums of this layer
         for (int e = tid; e < nsamp * 128; e += CF_EPI) {
           const int gg = e >> 7, n = e & 127;
-          if (n < N) ws[ly.rs_off + (long long)(b0 + gg) * ly.ld_out + n] = rs_acc[e];
+          if (n < N) ws[rs_off + (long long)(b0 + gg) * rs_ld + n] = rs_acc[e];
           rs_acc[e] = 0.f;
         }
       }
@@ -471,6 +516,55 @@ bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const floa
   return true;
 }
 
+// Execution-order step table: forward l = L-1..0, then backward l = 0..(L-1 or L-2).
+void chain_fused_build_steps(ChainSteps* steps, const ChainNetDev& net) {
+  const int L = net.L;
+  auto blank = [] { ChainStep st; st.K = st.N = 0; st.mode = 0; st.add_first = 0; st.write_x = 1;
+                    st.sc_ld = st.out_ld = st.add_ld = st.q_ld = st.rs_ld = 0;
+                    st.sc_off = st.out_off = st.outT_off = st.add_off = st.q_off = st.rs_off = -1; return st; };
+  int t = 0;
+  for (int l = L - 1; l >= 0; --l, ++t) {
+    const ChainLayerDev& ly = net.layer[l];
+    ChainStep st = blank();
+    st.K = ly.n_out; st.N = ly.n_in;
+    if (l > 0) {
+      const ChainLayerDev& below = net.layer[l - 1];
+      if (below.act) { st.sc_off = below.sg_off; st.sc_ld = below.ld_out; }
+      st.out_off = below.q_off; st.out_ld = below.ld_out; st.outT_off = below.qt_off;
+    } else {
+      st.mode = 1;
+      st.out_off = net.r0_off; st.out_ld = net.ld_in; st.outT_off = net.r0t_off;
+    }
+    if (ly.lands_skip >= 0) { st.add_off = net.layer[ly.lands_skip].qt_off; st.add_first = 1; }   // transposed Q of the skip layer
+    steps->st[t] = st;
+  }
+  steps->n_fwd = t;
+  // the backward contraction of a LINEAR top layer produces nothing anybody reads (R_L is the constant seed)
+  const int n_bwd = net.layer[L - 1].act ? L : L - 1;
+  for (int l = 0; l < n_bwd; ++l, ++t) {
+    const ChainLayerDev& ly = net.layer[l];
+    ChainStep st = blank();
+    st.K = ly.n_in; st.N = ly.n_out;
+    if (ly.act) {
+      st.mode = 2;
+      st.sc_off = ly.sg_off; st.sc_ld = ly.ld_out;
+      st.q_off = ly.qt_off;                                     // transposed Q_l
+      st.rs_off = ly.rs_off; st.rs_ld = ly.ld_out;
+    }
+    if (l < L - 1) {
+      st.out_off = ly.dr_off; st.out_ld = ly.ld_out; st.outT_off = ly.drt_off;
+      if (ly.skip_from >= 0) {
+        const int j = ly.skip_from;
+        st.add_off = j == 0 ? net.r0t_off : net.layer[j - 1].drt_off;      // transposed dR_j
+      }
+    } else {
+      st.write_x = 0;
+    }
+    steps->st[t] = st;
+  }
+  steps->n_all = t;
+}
+
 bool chain_fused_supported(const ChainNetDev& net) {
   if (net.L < 1 || net.L > CHAIN_FUSED_MAX_LAYERS) return false;
   if (net.s < 1 || net.s > CF_ROWS || net.G < 1 || net.G > 16) return false;
@@ -484,10 +578,10 @@ cudaError_t chain_fused_read_trace(unsigned long long* out) {
   return cudaMemcpyFromSymbol(out, g_cf_trace, sizeof(unsigned long long) * 64 * 8);
 }
 
-cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, float* ws, const float* jt, const float* jn2,
+cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, const ChainSteps& steps, float* ws, const float* jt, const float* jn2,
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
                                float* stats, cudaStream_t st) {
-  constexpr int SMEM = 3 * CF_X_BYTES + 64 + 2 * 16 * 128 * 4 + CF_PARTS * 128 * 2 * 4 + 1024;
+  constexpr int SMEM = 3 * CF_X_BYTES + 64 + 2 * 16 * 128 * 4 + CF_PARTS * 128 * 2 * 4 + (int)sizeof(ChainSteps) + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(chain_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
@@ -495,7 +589,7 @@ cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, fl
     configured = true;
   }
   const int ctas = (B + net.G - 1) / net.G;
-  chain_fused_kernel<<<ctas, CF_THREADS, SMEM, st>>>(maps, net, ws, jt, jn2, idx, seed, B, coef, do_loss, do_backward, stats);
+  chain_fused_kernel<<<ctas, CF_THREADS, SMEM, st>>>(maps, net, steps, ws, jt, jn2, idx, seed, B, coef, do_loss, do_backward, stats);
   return cudaGetLastError();
 }
 

@@ -139,12 +139,29 @@ namespace dino {
 constexpr int CHAIN_FUSED_MAX_LAYERS = 16;
 // qt_off / drt_off: TRANSPOSED copies [n_out, ldT] of Q_l and dR_{l+1} (operands of the tensor-core weight gradient)
 struct ChainLayerDev { long long q_off, sg_off, rs_off, dr_off, qt_off, drt_off; int n_in, n_out, ld_out, act, skip_from, lands_skip; };
-struct ChainNetDev { int L, s, G, d_in, ld_in, top_materialised; long long r0_off, r0t_off, ldT; ChainLayerDev layer[CHAIN_FUSED_MAX_LAYERS]; };
+struct ChainNetDev { int L, s, G, d_in, ld_in, top_materialised, has_skip; long long r0_off, r0t_off, ldT; ChainLayerDev layer[CHAIN_FUSED_MAX_LAYERS]; };
+// One contraction + epilogue of the fused kernel, in execution order (built on the host: the device code
+// carries no layer logic).  Offsets are into the workspace, -1 = absent.
+struct ChainStep {
+  int K, N;                       // X [rows, K] times the step's weight tile -> [rows, N]
+  int mode;                       // 0 plain, 1 loss (last forward step), 2 row-sum (backward through a softplus layer)
+  int add_first;                  // residual: 1 -> (acc + add) * scale, 0 -> acc * scale + add
+  int write_x;                    // the result is the next contraction's operand
+  int sc_ld, out_ld, add_ld, q_ld, rs_ld;
+  long long sc_off;               // per-sample scale vectors [B, sc_ld]
+  long long out_off;              // row-major destination rows
+  long long outT_off;             // transposed destination [N, ldT]
+  long long add_off;              // residual rows
+  long long q_off;                // Q_l rows (row-sum operand)
+  long long rs_off;               // row-sum destination [B, rs_ld]
+};
+struct ChainSteps { int n_fwd, n_all; ChainStep st[2 * CHAIN_FUSED_MAX_LAYERS]; };
 struct ChainMaps { CUtensorMap fwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap bwd[CHAIN_FUSED_MAX_LAYERS]; };
 bool chain_fused_supported(const ChainNetDev& net);
 bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const float* ws, const long long* wp_off,
                              const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp);
-cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, float* ws, const float* jt, const float* jn2,
+void chain_fused_build_steps(ChainSteps* steps, const ChainNetDev& net);
+cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, const ChainSteps& steps, float* ws, const float* jt, const float* jn2,
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
                                float* stats, cudaStream_t st);
 

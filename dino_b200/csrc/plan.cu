@@ -85,6 +85,7 @@ struct DinoPlan {
   bool mlp_fused;
   ChainNetDev chain;         // descriptor + weight tensor maps of the fused tcgen05 chain kernel
   ChainMaps chain_maps;
+  ChainSteps chain_steps;
   bool chain_fused;
 };
 
@@ -241,6 +242,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
       d.q_off = lp.q_off; d.sg_off = lp.sg_off; d.rs_off = lp.rs_off; d.dr_off = lp.dr_off;
       d.n_in = lp.n_in; d.n_out = lp.n_out; d.ld_out = (int)lp.ld_out; d.act = lp.act == DINO_ACT_SOFTPLUS;
       d.skip_from = lp.skip_from; d.lands_skip = lp.lands_skip;
+      if (lp.skip_from >= 0) c.has_skip = 1;
     }
     p->chain_fused = chain_fused_supported(c);
     if (p->chain_fused) {
@@ -252,6 +254,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
         lp.drt_off = l < p->L - 1 ? take((long long)lp.n_out * c.ldT) : -1;
         c.layer[l].qt_off = lp.qt_off; c.layer[l].drt_off = lp.drt_off;
       }
+      chain_fused_build_steps(&p->chain_steps, c);
     }
   }
   p->ws_floats = off;
@@ -418,8 +421,12 @@ static int run_chain_fused(DinoPlan* p, const float* params, const DinoBatch* b,
   else if (p->jac_mode == DINO_JAC_FULL) *top_out = {ws + p->off_ident, p->ld_ident, p->s};
   else *top_out = {b->seed, (long long)p->d_out, p->s};
   DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
-  DINO_LAUNCH(launch_chain_fused(p->chain_maps, p->chain, ws, b->J, b->J_sqnorm, b->idx, seed, B, coef, do_loss,
-                                 do_backward, stats, st));
+  {
+    const char* dbg = getenv("DINO_CF_DBG");
+    const int knobs = dbg ? atoi(dbg) << 8 : 0;
+    DINO_LAUNCH(launch_chain_fused(p->chain_maps, p->chain, p->chain_steps, ws, b->J, b->J_sqnorm, b->idx, seed, B, coef, do_loss,
+                                   do_backward | (do_backward ? knobs : 0), stats, st));
+  }
   return 0;
 }
 
