@@ -87,6 +87,10 @@ struct DinoPlan {
   ChainMaps chain_maps;
   ChainSteps chain_steps;
   bool chain_fused;
+  // optional per-kernel timing (dino_plan_profile): CUDA events around the Jacobian-chain stage of each step
+  bool profile;
+  cudaEvent_t ev0, ev1;
+  double prof_ms; long long prof_n; bool ev_pending;
 };
 
 static cudaStream_t S(dino_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
@@ -117,6 +121,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   p->max_batch = spec->max_batch;
   p->precision = spec->precision;
   p->ws = nullptr;
+  p->profile = false; p->prof_ms = 0.0; p->prof_n = 0; p->ev_pending = false; p->ev0 = p->ev1 = nullptr;
   long long poff = 0;
   int n_in = spec->d_in;
   for (int l = 0; l < p->L; ++l) {
@@ -262,7 +267,10 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   return 0;
 }
 
-extern "C" void dino_plan_destroy(DinoPlan* plan) { delete plan; }
+extern "C" void dino_plan_destroy(DinoPlan* plan) {
+  if (plan && plan->ev0) { cudaEventDestroy(plan->ev0); cudaEventDestroy(plan->ev1); }
+  delete plan;
+}
 
 extern "C" int64_t dino_plan_param_count(const DinoPlan* plan) { return plan ? plan->n_params : -1; }
 
@@ -421,12 +429,20 @@ static int run_chain_fused(DinoPlan* p, const float* params, const DinoBatch* b,
   else if (p->jac_mode == DINO_JAC_FULL) *top_out = {ws + p->off_ident, p->ld_ident, p->s};
   else *top_out = {b->seed, (long long)p->d_out, p->s};
   DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
+  if (p->profile) {
+    if (p->ev_pending && cudaEventSynchronize(p->ev1) == cudaSuccess) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, p->ev0, p->ev1) == cudaSuccess) { p->prof_ms += ms; p->prof_n += 1; }
+    }
+    DINO_CUDA(cudaEventRecord(p->ev0, st));
+  }
   {
     const char* dbg = getenv("DINO_CF_DBG");
     const int knobs = dbg ? atoi(dbg) << 8 : 0;
     DINO_LAUNCH(launch_chain_fused(p->chain_maps, p->chain, p->chain_steps, ws, b->J, b->J_sqnorm, b->idx, seed, B, coef, do_loss,
                                    do_backward | (do_backward ? knobs : 0), stats, st));
   }
+  if (p->profile) { DINO_CUDA(cudaEventRecord(p->ev1, st)); p->ev_pending = true; }
   return 0;
 }
 
@@ -783,5 +799,26 @@ extern "C" int dino_debug_chain_trace(uint64_t* out_64x8) {
   if (!out_64x8) return fail("dino_debug_chain_trace: null argument");
   DINO_CUDA(cudaDeviceSynchronize());
   DINO_CUDA(chain_fused_read_trace(reinterpret_cast<unsigned long long*>(out_64x8)));
+  return 0;
+}
+
+// Per-kernel timing of the dominant kernel (the fused Jacobian-chain kernel), measured with CUDA events on the
+// launching stream.  enable=1 starts, enable=0 stops; out_ms_sum / out_count receive the totals so far.
+// Only meaningful for eager (non-graph) steps.
+extern "C" int dino_plan_profile(DinoPlan* p, int enable, double* out_ms_sum, int64_t* out_count) {
+  if (!p) return fail("dino_plan_profile: null plan");
+  if (enable && !p->ev0) {
+    DINO_CUDA(cudaEventCreate(&p->ev0));
+    DINO_CUDA(cudaEventCreate(&p->ev1));
+  }
+  if (p->ev_pending && cudaEventSynchronize(p->ev1) == cudaSuccess) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p->ev0, p->ev1) == cudaSuccess) { p->prof_ms += ms; p->prof_n += 1; }
+    p->ev_pending = false;
+  }
+  if (out_ms_sum) *out_ms_sum = p->prof_ms;
+  if (out_count) *out_count = p->prof_n;
+  if (enable && !p->profile) { p->prof_ms = 0.0; p->prof_n = 0; }
+  p->profile = enable != 0;
   return 0;
 }

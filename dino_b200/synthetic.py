@@ -182,6 +182,14 @@ def flops_per_sample(arch: Arch) -> float:
     return (s + 1) * 2.0 * (S + (S - sizes[0]) + S_t)
 
 
+def chain_flops_per_sample(arch: Arch) -> float:
+    """Algorithmic FLOPs of the Jacobian chain alone (forward chain + data-gradient chain):
+    s * 2 * (S + S_minus_first), the first two terms of SURVEY.md 8d's F_chain."""
+    sizes = [k * n for _, k, n, *_ in layer_table(arch)]
+    S = sum(sizes)
+    return min(arch.d_in, arch.d_out) * 2.0 * (S + (S - sizes[0]))
+
+
 def bytes_per_sample(arch: Arch) -> float:
     """Compulsory HBM bytes of one sample: read m, q and the target J once (fp32)."""
     return 4.0 * (arch.d_in + arch.d_out + arch.d_out * arch.d_in)
