@@ -4,3 +4,4 @@ gives what ``from dino import *`` gives in the reference (dino/__init__.py:18)."
 from .model import Adam, SGD, DinoModel, NetCore
 from .construction import *
 from . import evaluation
+from . import inference
