@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--no-fp32-leg", action="store_true", help="skip the secondary fp32-exact measurement")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--random-data", action="store_true",
+                    help="N(0,1) m/q/J instead of teacher data (wide configs: the host-side teacher Jacobian is slow)")
     return ap.parse_args()
 
 
@@ -209,7 +211,14 @@ def main():
 
     # ---- synthetic teacher data (same on every rank), student initial weights ------------------------
     n = args.n
-    data, tw = S.make_dataset(arch, n, 1234 + 1)
+    if args.random_data:
+        rng = np.random.default_rng(1234)
+        data = {"m": rng.standard_normal((n, arch.d_in), dtype=np.float32),
+                "q": rng.standard_normal((n, arch.d_out), dtype=np.float32),
+                "J": rng.standard_normal((n, arch.d_out, arch.d_in), dtype=np.float32)}
+        tw = S.random_weights(arch, rng, teacher=True)
+    else:
+        data, tw = S.make_dataset(arch, n, 1234 + 1)
     w = H.student_weights(arch, 1234 + 2, tw)
     model = S.build_model(arch, w, precision=args.precision)
     model.compile(optimizer=Adam(1e-3), loss=[normalized_mse, normalized_mse_matrix], loss_weights=[1.0, 1.0],

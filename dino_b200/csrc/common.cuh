@@ -117,6 +117,8 @@ cudaError_t launch_sketch_open(const float* dS, const float* V, const int* idx, 
 cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long n, float lr_t,
                         float b1, float b2, float eps, cudaStream_t st);
 cudaError_t launch_sgd(float* p, const float* g, long long n, float lr, cudaStream_t st);
+cudaError_t launch_transpose(const float* src, long long ld_src, float* dst, long long ld_dst, int rows, int cols,
+                             cudaStream_t st);
 cudaError_t launch_stage_batch(const int* idx_all, const int* pos, int* idx_stage, int B, cudaStream_t st);
 cudaError_t launch_roll_stats(float* stage, float* hist, int* pos, int advance, int* step, long long* t, cudaStream_t st);
 cudaError_t launch_adam_dev(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,

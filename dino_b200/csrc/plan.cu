@@ -87,6 +87,8 @@ struct DinoPlan {
   ChainMaps chain_maps;
   ChainSteps chain_steps;
   bool chain_fused;
+  bool tc_wgrad;             // layer-by-layer tf32 path: transposed chain states kept for the tensor-core weight gradient
+  long long ldT, r0t_off;
   // optional per-kernel timing (dino_plan_profile): CUDA events around the Jacobian-chain stage of each step
   bool profile;
   cudaEvent_t ev0, ev1;
@@ -260,6 +262,20 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
         c.layer[l].qt_off = lp.qt_off; c.layer[l].drt_off = lp.drt_off;
       }
       chain_fused_build_steps(&p->chain_steps, c);
+    }
+  }
+  p->tc_wgrad = false;
+  p->ldT = p->chain_fused ? p->chain.ldT : 0;
+  p->r0t_off = p->chain_fused ? p->chain.r0t_off : -1;
+  if (!p->chain_fused && p->precision == DINO_PREC_TF32 &&
+      (p->jac_mode == DINO_JAC_FULL || p->jac_mode == DINO_JAC_OUT_REDUCED)) {
+    p->tc_wgrad = true;
+    p->ldT = r4(Ms);
+    p->r0t_off = take((long long)p->d_in * p->ldT);
+    for (int l = 0; l < p->L; ++l) {
+      LayerPlan& lp = p->layers[l];
+      lp.qt_off = take((long long)lp.n_out * p->ldT);
+      lp.drt_off = l < p->L - 1 ? take((long long)lp.n_out * p->ldT) : -1;
     }
   }
   p->ws_floats = off;
@@ -454,11 +470,11 @@ static int push_chain_wgrads(DinoPlan* p, int B, float* grad, const TopQ& top, G
     const LayerPlan& lp = p->layers[l];
     if (!lp.trainable) continue;
     GemmOp op = gemm_op_zero();
-    if (p->chain_fused && lp.n_in <= 128 && lp.n_out <= 128) {
-      // dW_l += dRT_l QT_l^T : both factors transposed by the fused kernel -> K-major tensor-core contraction
-      op.A = l == 0 ? ws + p->chain.r0t_off : ws + p->layers[l - 1].drt_off;
-      op.a_sm = p->chain.ldT; op.a_sk = 1;
-      op.B = ws + lp.qt_off; op.b_sk = 1; op.b_sn = p->chain.ldT;
+    if (p->chain_fused || p->tc_wgrad) {
+      // dW_l += dRT_l QT_l^T : both factors transposed -> K-major tensor-core contraction
+      op.A = l == 0 ? ws + p->r0t_off : ws + p->layers[l - 1].drt_off;
+      op.a_sm = p->ldT; op.a_sk = 1;
+      op.B = ws + lp.qt_off; op.b_sk = 1; op.b_sn = p->ldT;
     } else {
       op.A = l == 0 ? ws + p->off_r0 : ws + p->layers[l - 1].dr_off;
       op.a_sm = 1; op.a_sk = l == 0 ? p->ld_in : p->layers[l - 1].ld_out;
@@ -534,7 +550,7 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
     const float* q; long long ldq; int qmod;
     if (l == L - 1) { q = top.ptr; ldq = top.ld; qmod = top.mod; }
     else { q = ws + lp.q_off; ldq = lp.ld_out; qmod = 0; }
-    if (lp.trainable) {     // dW_l += dR_l^T Q_l   (reduction over all B*s chain rows, split-K)
+    if (lp.trainable && !p->tc_wgrad) {     // dW_l += dR_l^T Q_l   (reduction over all B*s chain rows, split-K)
       GemmOp op = gemm_op_zero();
       op.A = dr_ptr(l); op.a_sm = 1; op.a_sk = dr_ld(l);
       op.B = q; op.b_sk = ldq; op.b_sn = 1; op.b_kmod = qmod;
@@ -688,6 +704,18 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
     if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
     if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st)) return 1;
     if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, wg, st)) return 1;
+    if (p->tc_wgrad) {
+      // transposes of every chain state, then all chain weight gradients in one tensor-core launch
+      float* ws = p->ws;
+      const int M = B * p->s;
+      DINO_LAUNCH(launch_transpose(ws + p->off_r0, p->ld_in, ws + p->r0t_off, p->ldT, M, p->d_in, st));
+      for (int l = 0; l < p->L; ++l) {
+        const LayerPlan& lp = p->layers[l];
+        DINO_LAUNCH(launch_transpose(ws + lp.q_off, lp.ld_out, ws + lp.qt_off, p->ldT, M, lp.n_out, st));
+        if (l < p->L - 1) DINO_LAUNCH(launch_transpose(ws + lp.dr_off, lp.ld_out, ws + lp.drt_off, p->ldT, M, lp.n_out, st));
+      }
+      if (push_chain_wgrads(p, B, grad, top, wg, st)) return 1;
+    }
   }
   if (run_mlp_backward(p, params, B, grad, wg, st)) return 1;
   return flush_wgrad(p, wg, st);

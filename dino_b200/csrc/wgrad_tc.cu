@@ -6,7 +6,7 @@
 // is the standard TMA -> tcgen05.mma.kind::tf32 -> TMEM pipeline of gemm_tc.cu with a red.global.add
 // epilogue.  (Feeding the row-major states as MN-major UMMA operands would avoid the copies, but TF32
 // MN-major tiles need the 32-byte-base swizzle variant, which could not be validated offline.)
-// Requires n_in, n_out <= 128; other layers use the SIMT split-K path.
+// Output tiles of 128 x 128; wide layers are covered by several tiles (blockIdx.x enumerates op, tile, split).
 #include <cuda.h>
 
 #include <mutex>
@@ -26,6 +26,7 @@ struct WgOp {
   int n_in, n_out, rows;    // rows = reduction length
   int z_start;              // first blockIdx.x of this op
   int chunks_per_cta;       // reduction chunks (of WG_BK rows) per CTA
+  int n_tiles, splits;      // CTAs of this op: m_tiles * n_tiles * splits, split fastest
 };
 struct WgGroup {
   int n;
@@ -62,7 +63,10 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
   while (oi + 1 < g.n && (int)blockIdx.x >= g.op[oi + 1].z_start) ++oi;
   const WgOp& op = g.op[oi];
   const int total_chunks = (op.rows + WG_BK - 1) / WG_BK;
-  const int c_begin = (blockIdx.x - op.z_start) * op.chunks_per_cta;
+  const int local = blockIdx.x - op.z_start;
+  const int split = local % op.splits, tile = local / op.splits;
+  const int m0 = (tile / op.n_tiles) * 128, n0 = (tile % op.n_tiles) * 128;
+  const int c_begin = split * op.chunks_per_cta;
   const int nchunks = min(total_chunks - c_begin, op.chunks_per_cta);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -97,14 +101,14 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
           uint8_t* sx = smem + st * WG_STAGE_BYTES;
           const int k0 = (c_begin + c) * WG_BK;
           asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                       ::"r"(wg_u32(sx)), "l"(mx), "r"(wg_u32(full_bar + st)), "r"(k0), "r"(0) : "memory");
+                       ::"r"(wg_u32(sx)), "l"(mx), "r"(wg_u32(full_bar + st)), "r"(k0), "r"(m0) : "memory");
           asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                       ::"r"(wg_u32(sx + WG_OPER_BYTES)), "l"(my), "r"(wg_u32(full_bar + st)), "r"(k0), "r"(0) : "memory");
+                       ::"r"(wg_u32(sx + WG_OPER_BYTES)), "l"(my), "r"(wg_u32(full_bar + st)), "r"(k0), "r"(n0) : "memory");
         }
       }
     } else if (warp == 1) {
       if (lane == 0) {
-        const uint32_t n16 = (uint32_t)((op.n_out + 15) & ~15);
+        const uint32_t n16 = (uint32_t)((min(128, op.n_out - n0) + 15) & ~15);
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((n16 >> 3) << 17) | ((128u >> 4) << 24);
         for (int c = 0; c < nchunks; ++c) {
           const int st = c % WG_STAGES;
@@ -131,8 +135,9 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
       wg_wait(done_bar, 0);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const int q = warp & 3;
-      const int m = q * 32 + lane;
-      for (int c0 = 0; c0 < op.n_out; c0 += 32) {
+      const int m = m0 + q * 32 + lane;
+      const int ncols = min(128, op.n_out - n0);
+      for (int c0 = 0; c0 < ncols; c0 += 32) {
         uint32_t r[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
         asm volatile(
@@ -146,10 +151,10 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
             : "r"(taddr));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         if (m < op.n_in) {
-          float* crow = op.C + (long long)m * op.n_out + c0;
+          float* crow = op.C + (long long)m * op.n_out + n0 + c0;
 #pragma unroll
           for (int j = 0; j < 32; ++j)
-            if (c0 + j < op.n_out) atomicAdd(crow + j, __uint_as_float(r[j]));
+            if (c0 + j < ncols) atomicAdd(crow + j, __uint_as_float(r[j]));
         }
       }
     }
@@ -192,7 +197,7 @@ static bool wg_map(CUtensorMap* m, const float* base, int n, int rows, long long
 // A = XT (pitch a_sm), B = YT (pitch b_sn).
 bool wgrad_tc_supported(const GemmOp& op) {
   if (!op.atomic_c || op.a_sk != 1 || op.b_sk != 1 || op.b_kmod > 0 || op.a_mod > 0) return false;
-  if (op.M > 128 || op.N > 128 || op.M < 1 || op.N < 1 || op.K < 1) return false;
+  if (op.M < 1 || op.N < 1 || op.K < 1) return false;
   if ((op.a_sm & 3) || (op.b_sn & 3)) return false;
   if ((reinterpret_cast<uintptr_t>(op.A) & 15) || (reinterpret_cast<uintptr_t>(op.B) & 15)) return false;
   return op.ldc == op.N;
@@ -202,21 +207,27 @@ cudaError_t launch_wgrad_tc(const GemmGroup& gg, int num_sms, cudaStream_t st) {
   if (gg.n <= 0) return cudaSuccess;
   static WgGroup g;                      // about 7 KB: keep it off the stack; plans are single-threaded
   g.n = gg.n;
-  long long total_rows = 0;
-  for (int i = 0; i < gg.n; ++i) total_rows += gg.ops[i].K;
-  const long long target_ctas = 2LL * num_sms;
+  // work of an op ~ tiles * rows; share about 2 waves of CTAs between the ops in that proportion
+  double total_work = 0.0;
+  for (int i = 0; i < gg.n; ++i)
+    total_work += (double)gg.ops[i].K * ((gg.ops[i].M + 127) / 128) * ((gg.ops[i].N + 127) / 128);
+  const double target_ctas = 2.0 * num_sms;
   int z = 0;
   for (int i = 0; i < gg.n; ++i) {
     const GemmOp& o = gg.ops[i];
     WgOp& w = g.op[i];
     w.C = o.C; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
     const int chunks = (o.K + WG_BK - 1) / WG_BK;
-    long long splits = (target_ctas * o.K + total_rows - 1) / total_rows;
+    const int m_tiles = (o.M + 127) / 128;
+    w.n_tiles = (o.N + 127) / 128;
+    const int tiles = m_tiles * w.n_tiles;
+    long long splits = (long long)(target_ctas * ((double)o.K * tiles / total_work) / tiles + 0.999);
     if (splits > chunks) splits = chunks;
     if (splits < 1) splits = 1;
     w.chunks_per_cta = (int)((chunks + splits - 1) / splits);
+    w.splits = (chunks + w.chunks_per_cta - 1) / w.chunks_per_cta;
     w.z_start = z;
-    z += (chunks + w.chunks_per_cta - 1) / w.chunks_per_cta;
+    z += tiles * w.splits;
     if (!wg_map(&g.mx[i], o.A, o.M, o.K, o.a_sm) || !wg_map(&g.my[i], o.B, o.N, o.K, o.b_sn)) return cudaErrorInvalidValue;
   }
   constexpr int SMEM = WG_STAGES * WG_STAGE_BYTES + 128 + 1024;

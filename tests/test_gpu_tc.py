@@ -49,7 +49,7 @@ def test_tf32_gemm_matches_fp64(cuda_device, M, N, K):
 
 
 @pytest.mark.parametrize("rows,n_in,n_out", [(64, 32, 32), (240, 13, 8), (1000, 50, 50), (12800, 100, 50), (300, 128, 128),
-                                             (77, 5, 100)])
+                                             (77, 5, 100), (520, 300, 200), (1000, 130, 257)])
 def test_tf32_weight_gradient_contraction(cuda_device, rows, n_in, n_out):
     """C += XT YT^T (split over the reduction, red.global.add epilogue) vs fp64, onto a non-zero C."""
     lib = _lib.load()
@@ -115,3 +115,26 @@ def test_tf32_mode_cfg2_widths(cuda_device):
     e0 = m32.evaluate([data["m"]], [data["q"], data["J"]], batch_size=64)
     e1 = mtf.evaluate([data["m"]], [data["q"], data["J"]], batch_size=64)
     assert np.allclose(e0, e1, rtol=5e-3, atol=1e-5)
+
+
+def test_tf32_mode_wide_network_layerwise_path(cuda_device):
+    """Widths > 128 take the layer-by-layer tensor-core path (gemm_tc + transposes + tiled wgrad_tc)."""
+    arch = S.Arch("rb_dense", 40, 20, hidden=[150, 200, 20], frozen_output=True, r_out=20)
+    data, tw = S.make_dataset(arch, 16, 9)
+    w = H.student_weights(arch, 10, tw, bias_noise=0.1)
+    from dino_b200 import SGD
+    net = H.oracle_net(arch, w)
+    (lt, l2, h1), grads = O.h1_step_grads(net, H.oracle_batch(data), (1.0, 1.0), vectorised=True)
+    model = S.build_model(arch, w, precision="tf32")
+    _compile(model)
+    model.optimizer = SGD(1.0)
+    before = {l.name: l.get_weights() for l in model.layers}
+    hist = model.fit([data["m"]], [data["q"], data["J"]], epochs=1, batch_size=16, perms=[np.arange(16)])
+    assert abs(hist.history["loss"][0] - lt) < 5e-3 * abs(lt)
+    gi = 0
+    for l, lname in enumerate(model.core.names):
+        if not model.core.trainable[l]:
+            continue
+        for a, b in zip(before[lname], model.get_layer(lname).get_weights()):
+            assert H.rel_err(a - b, grads[gi].numpy()) < 1e-2, lname
+            gi += 1
