@@ -292,6 +292,8 @@ def main():
         lib = _lib.load()
         ms_sum, cnt = C.c_double(0.0), C.c_int64(0)
         for i in range(5):
+            if prof_eng.remaining() < Bg:
+                prof_eng.rewind()
             prof_eng.step(Bg)
         _lib.check(lib.dino_plan_profile(prof_eng.plan.handle, 1, C.byref(ms_sum), C.byref(cnt)), "dino_plan_profile")
         for i in range(min(args.steps, 200)):
@@ -313,6 +315,8 @@ def main():
         e32.set_order(order)
         k32 = max(20, args.steps // 4)
         for i in range(max(3, args.warmup // 2)):
+            if e32.remaining() < Bg:
+                e32.rewind()
             e32.step(Bg)
         torch.cuda.synchronize(); dp.barrier(); torch.cuda.synchronize()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

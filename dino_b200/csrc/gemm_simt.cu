@@ -244,7 +244,12 @@ cudaError_t launch_gemm_simt(const GemmOp& op_in, int num_sms, cudaStream_t st) 
   GemmOp op = op_in;
   if (op.M <= 0 || op.N <= 0) return cudaSuccess;
   if (op.sdim <= 0) op.sdim = 1;
-  const int BM = op.M <= 32 ? 32 : (op.M <= 64 ? 64 : 128);
+  // largest row tile that still gives every SM a CTA (small-M contractions: the MLP of a wide network)
+  const int ntile_n = (op.N + 63) / 64;
+  int BM = 128;
+  if (op.M <= 32 || ((op.M + 127) / 128) * ntile_n < num_sms) BM = 64;
+  if (op.M <= 32 || (BM == 64 && ((op.M + 63) / 64) * ntile_n < num_sms)) BM = 32;
+  if (op.M > 32 && op.M <= 64 && BM == 128) BM = 64;
   int splits = 1;
   if (op.atomic_c && op.k_per_split == 0) {
     const int tiles = ((op.M + BM - 1) / BM) * ((op.N + 63) / 64);
