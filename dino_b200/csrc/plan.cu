@@ -90,6 +90,9 @@ struct DinoPlan {
   bool tc_wgrad;             // layer-by-layer tf32 path: transposed chain states kept for the tensor-core weight gradient
   long long ldT, r0t_off;
   // optional per-kernel timing (dino_plan_profile): CUDA events around the Jacobian-chain stage of each step
+  // side stream: the chain's weight gradients run concurrently with the MLP backward (fork/join by events)
+  cudaStream_t side;
+  cudaEvent_t ev_fork, ev_join;
   bool profile;
   cudaEvent_t ev0, ev1;
   double prof_ms; long long prof_n; bool ev_pending;
@@ -123,6 +126,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   p->max_batch = spec->max_batch;
   p->precision = spec->precision;
   p->ws = nullptr;
+  p->side = nullptr; p->ev_fork = p->ev_join = nullptr;
   p->profile = false; p->prof_ms = 0.0; p->prof_n = 0; p->ev_pending = false; p->ev0 = p->ev1 = nullptr;
   long long poff = 0;
   int n_in = spec->d_in;
@@ -279,12 +283,19 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     }
   }
   p->ws_floats = off;
+  if (p->chain_fused && getenv("DINO_B200_NO_SIDE_STREAM") == nullptr) {
+    DINO_CUDA(cudaSetDevice(device));
+    DINO_CUDA(cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking));
+    DINO_CUDA(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+    DINO_CUDA(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+  }
   *out = p;
   return 0;
 }
 
 extern "C" void dino_plan_destroy(DinoPlan* plan) {
   if (plan && plan->ev0) { cudaEventDestroy(plan->ev0); cudaEventDestroy(plan->ev1); }
+  if (plan && plan->side) { cudaEventDestroy(plan->ev_fork); cudaEventDestroy(plan->ev_join); cudaStreamDestroy(plan->side); }
   delete plan;
 }
 
@@ -699,6 +710,21 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
   if (p->chain_fused) {
     if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st, true)) return 1;
     if (run_chain_fused(p, params, b, B, 2.f * w_h1 * inv_gb, 1, 1, stats, st, &top)) return 1;
+    if (p->side != nullptr) {
+      // fork: the chain's weight gradients (tensor cores, side stream) overlap the MLP backward (main stream);
+      // both only ADD into the gradient, which was cleared before the fork
+      GemmGroup cw;
+      cw.n = 0;
+      DINO_CUDA(cudaEventRecord(p->ev_fork, st));
+      DINO_CUDA(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+      if (push_chain_wgrads(p, B, grad, top, cw, p->side)) return 1;
+      if (flush_wgrad(p, cw, p->side)) return 1;
+      DINO_CUDA(cudaEventRecord(p->ev_join, p->side));
+      if (run_mlp_backward(p, params, B, grad, wg, st)) return 1;
+      if (flush_wgrad(p, wg, st)) return 1;
+      DINO_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
+      return 0;
+    }
     if (push_chain_wgrads(p, B, grad, top, wg, st)) return 1;
   } else {
     if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;

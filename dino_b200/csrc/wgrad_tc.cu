@@ -16,7 +16,7 @@
 namespace dino {
 
 constexpr int WG_BK = 32;                       // reduction rows per stage (one 128-byte swizzle row)
-constexpr int WG_STAGES = 6;
+constexpr int WG_STAGES = 3;   // 96 KB: leaves room for a fused-MLP CTA on the same SM (the two overlap on separate streams)
 constexpr int WG_OPER_BYTES = 128 * WG_BK * 4;  // 16 KB: up to 128 operand rows x 32 reduction elements
 constexpr int WG_STAGE_BYTES = 2 * WG_OPER_BYTES;
 constexpr int WG_THREADS = 192;

@@ -133,3 +133,47 @@ def test_jacobian_error_metrics_from_arrays(cuda_device, tmp_path):
     mh, qh = np.ones(40), np.ones(10)
     assert H.rel_err(io.Jvp(m0, mh), Jo[0].numpy() @ mh) < 1e-5
     assert H.rel_err(io.Jtvp(m0, qh), Jo[0].numpy().T @ qh) < 1e-5
+
+
+def test_sketched_driver_with_column_reshuffle(cuda_device, tmp_path):
+    """train_full_jacobian = 0: flatten_data -> equip_model_with_sketched_jacobian -> train_h1_network on
+    [m, U, V] -> [q, diag sigma], with shuffle_every_epoch re-drawing the sketch columns (jacobianTrainingDriver.py:227-246)."""
+    data_dir, _ = _make_data_dir(tmp_path)
+    settings = _settings(data_dir, tmp_path, architecture="generic_dense", train_full_jacobian=0, target_rank=10,
+                         batch_rank=5, truncation_dimension=12, depth=2, reduced_input_training=False,
+                         shuffle_every_epoch=True, outer_epochs=2, inner_epochs=1)
+    settings["opt_parameters"].update(train_full_jacobian=0, keras_epochs=1, keras_batch_size=16)
+    np.random.seed(3)
+    regressor = D.jacobian_training_driver(settings)
+    assert len(regressor.inputs) == 3 and regressor.outputs[1].shape == (None, 5, 5)
+    # one more evaluation against the oracle's sketched Jacobian on flattened data
+    dd = D.get_the_data(settings)
+    tr = dd["train_dict"]
+    assert tr["U_data"].shape == (64 * 2, 10, 5) and tr["sigma_data"].shape == (128, 5, 5)
+    regressor.compile(optimizer=D.Adam(1e-3), loss=[D.normalized_mse, D.normalized_mse_matrix], loss_weights=[1.0, 1.0],
+                      metrics=[D.l2_accuracy, D.f_accuracy_matrix])
+    ev = regressor.evaluate([tr["m_data"], tr["U_data"], tr["V_data"]], [tr["q_data"], tr["sigma_data"]])
+    net = O.ONet(regressor.core.d_in)
+    core = regressor.core
+    for l, name in enumerate(core.names):
+        w = core.layer_weights(l)
+        net.layers.append(O.OLayer(name, torch.tensor(w[0], dtype=torch.float64),
+                                   torch.tensor(w[1], dtype=torch.float64) if len(w) == 2 else None,
+                                   core.act[l], core.trainable[l], core.skip_from[l]))
+    t = lambda a: torch.tensor(np.asarray(a, dtype=np.float32).astype(np.float64))
+    ob = O.Batch(t(tr["m_data"]), t(tr["q_data"]), t(tr["sigma_data"]), t(tr["U_data"]), t(tr["V_data"]))
+    ref = O.evaluate(net, ob, batch_size=32, jac_mode="sketched")
+    assert np.allclose(ev, ref, rtol=1e-3, atol=1e-5)
+
+
+def test_observable_training_driver_l2_only(cuda_device, tmp_path):
+    """observable_training_driver (observableConstruction.py:81-116): plain L2 training of m -> q."""
+    data_dir, _ = _make_data_dir(tmp_path)
+    settings = D.observable_network_settings({})
+    settings.update(data_dir=data_dir, architecture="rb_dense", depth=2, fixed_input_rank=12, fixed_output_rank=6,
+                    train_data_size=64, test_data_size=32, reduced_input_dim=None, reduced_output_dim=None)
+    settings["opt_parameters"].update(keras_epochs=2, keras_batch_size=16)
+    net = D.observable_training_driver(settings)
+    assert len(net.outputs) == 1
+    ev = net.evaluate(np.zeros((4, 40)) + 0.1, np.ones((4, 10)))
+    assert len(ev) == 2 and np.isfinite(ev).all()
