@@ -36,6 +36,7 @@ constexpr int CF_EPI = 128 * CF_PARTS;                                          
 constexpr int CF_EPI_WARPS = CF_EPI / 32;
 constexpr int CF_THREADS = CF_EPI + 32;                                            // + 1 control warp
 constexpr int CF_CW = 16;                                                          // columns per TMEM load / work item
+constexpr int CF_TILE_LD = 36;                                                     // floats per column of a warp's row-sum transposition tile
 
 __device__ __forceinline__ uint32_t cf_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void cf_mbar_init(uint64_t* bar, uint32_t count) {
@@ -73,6 +74,16 @@ __device__ __forceinline__ void cf_mma(uint32_t tmem_d, uint64_t adesc, uint64_t
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
       "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ bool cf_elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}" : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ uint64_t cf_desc(uint32_t saddr) {
   return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
@@ -128,11 +139,20 @@ __device__ __forceinline__ void cf_load16(float (&d)[CF_CW], const float* row, i
   }
 }
 
-// 16 consecutive columns of chain row `grow` from a TRANSPOSED array (element n at base[n * ldT]): lanes =
-// consecutive rows, so every load instruction is one coalesced 128-byte request
-__device__ __forceinline__ void cf_load16T(float (&d)[CF_CW], const float* base, int c0, int N, bool ok, long long ldT) {
+// 16 consecutive columns of one chain row from a TRANSPOSED array (column n at p[n * ldT]): lanes = consecutive
+// rows, so every load is one coalesced 128-byte request.  The arrays are padded to whole 16-column blocks.
+__device__ __forceinline__ void cf_loadT(float (&d)[CF_CW], const float* p, long long ldT, bool ok) {
 #pragma unroll
-  for (int j = 0; j < CF_CW; ++j) d[j] = (ok && c0 + j < N) ? base[(long long)(c0 + j) * ldT] : 0.f;
+  for (int j = 0; j < CF_CW; ++j) { d[j] = ok ? *p : 0.f; p += ldT; }
+}
+// 16 consecutive floats of a per-sample vector (zero at and beyond `len`; `len` and the row pitch are multiples of 4)
+__device__ __forceinline__ void cf_load_vec16(float (&d)[CF_CW], const float* row, int c0, int len) {
+#pragma unroll
+  for (int j = 0; j < CF_CW; j += 4) {
+    float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c0 + j < len) q4 = *reinterpret_cast<const float4*>(row + c0 + j);
+    d[j] = q4.x; d[j + 1] = q4.y; d[j + 2] = q4.z; d[j + 3] = q4.w;
+  }
 }
 
 __global__ void __launch_bounds__(CF_THREADS, 1)
@@ -148,19 +168,18 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   uint64_t* mma_done = w_full + 2;
   uint64_t* x_ready = w_full + 3;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 4);
-  float* rs_acc = reinterpret_cast<float*>(w_full + 6);                       // [G <= 16][128] row-sum staging
-  float* sc_s = rs_acc + 16 * 128;                                            // [G <= 16][128] per-sample scale vectors of the step
-  float* ex_s = sc_s + 16 * 128;                                              // [CF_PARTS][128][2] loss partials of the row parts
-  ChainStep* st_s = reinterpret_cast<ChainStep*>(ex_s + CF_PARTS * 128 * 2);   // step table (constant-bank indexed loads are slow)
+  float* rs_acc = reinterpret_cast<float*>(w_full + 6);                       // [16][128] row sums: per sample (packed rows) or per warp quarter
+  float* ex_s = rs_acc + 16 * 128;                                            // [CF_PARTS][128][2] loss partials of the row parts
+  float* tiles = ex_s + CF_PARTS * 128 * 2;                                   // [CF_EPI_WARPS][8][CF_TILE_LD] row-sum transposition tiles
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int s = net.s, G = net.G, L = net.L;
   const int b0 = blockIdx.x * G;
   const int nsamp = min(G, B - b0);
-  const int R = nsamp * s;                       // valid chain rows of this CTA
+  const int srow = net.srow;                     // tile rows reserved per sample (>= s)
   const long long row0 = (long long)b0 * s;      // first global chain row
 #ifdef DINO_CF_TRACE
-  const int dbg = do_backward >> 8;      // experiment knobs: 1 skip transposed stores, 2 skip X writes, 4 skip TMEM loads, 8 skip rounding
+  const int dbg = do_backward >> 8;      // experiment knobs: 1 skip transposed stores, 2 skip X writes, 8 skip rounding
   do_backward &= 0xff;
 #else
   const int dbg = 0;
@@ -170,11 +189,6 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   // ---- set-up --------------------------------------------------------------------------------------
   for (int e = tid; e < CF_X_BYTES / 16; e += CF_THREADS) reinterpret_cast<float4*>(X)[e] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int e = tid; e < 16 * 128; e += CF_THREADS) rs_acc[e] = 0.f;
-  {
-    const int words = (int)(sizeof(ChainStep) / 4) * steps.n_all;
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(&steps.st[0]);
-    for (int e = tid; e < words; e += CF_THREADS) reinterpret_cast<uint32_t*>(st_s)[e] = src[e];
-  }
   if (warp == CF_EPI_WARPS) {
     if (lane == 0) {
       cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(x_ready, CF_EPI_WARPS);
@@ -190,32 +204,40 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == CF_EPI_WARPS) {
-    // ===== control thread: weight TMA (one step ahead) and MMA issue =====
-    if (lane == 0) {
+  const int warp_u = __shfl_sync(0xffffffffu, warp, 0);   // tells the compiler that everything derived from it is warp-uniform
+  if (warp_u == CF_EPI_WARPS) {
+    // ===== control warp: one elected lane issues the weight TMA (one step ahead) and the MMAs =====
+    // (elect.sync, not `lane == 0`: the compiler then knows a single lane is active and feeds the uniform
+    //  datapath directly instead of looping over possibly-divergent lanes)
+    if (cf_elect_one()) {
       auto load_w = [&](int t) {
-        const int nch = (st_s[t].K + 31) >> 5, buf = t & 1;
+        const int nch = (steps.st[t].K + 31) >> 5, buf = t & 1;
         const CUtensorMap* map = t < L ? &maps.fwd[L - 1 - t] : &maps.bwd[t - L];
         cf_mbar_expect_tx(w_full + buf, (uint32_t)nch * CF_CHUNK_BYTES);
         for (int c = 0; c < nch; ++c) cf_tma_load(Wb[buf] + c * CF_CHUNK_BYTES, map, c * 32, 0, w_full + buf);
       };
       load_w(0);
-      const uint32_t xa = cf_smem_u32(X);
+      const uint64_t xd = cf_desc(cf_smem_u32(X));
+      const uint64_t wd0 = cf_desc(cf_smem_u32(Wb[0])), wd1 = cf_desc(cf_smem_u32(Wb[1]));
+#pragma unroll 1
       for (int t = 0; t < n_steps; ++t) {
         const int buf = t & 1;
-        const int K = st_s[t].K, N = st_s[t].N;
+        const int K = steps.st[t].K, N = steps.st[t].N;
         const uint32_t n16 = (uint32_t)((N + 15) & ~15);
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((n16 >> 3) << 17) | ((128u >> 4) << 24);
-        const uint32_t wa = cf_smem_u32(Wb[buf]);
+        const uint64_t bd = buf ? wd1 : wd0;
         const int ksteps = (K + 7) >> 3;
         cf_mbar_wait(x_ready, t & 1);                       // operand X written by the epilogue threads
         CF_STAMP(t, 0);
         cf_mbar_wait(w_full + buf, (t >> 1) & 1);           // weight tile landed
         CF_STAMP(t, 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // descriptor start addresses advance by 32 bytes per 8-wide K step, 16 KB per 32-column chunk (no carry out
+        // of the 14-bit address field: the tiles sit below 256 KB)
+#pragma unroll 1
         for (int k = 0; k < ksteps; ++k) {
-          const uint32_t off = (uint32_t)((k >> 2) * CF_CHUNK_BYTES + (k & 3) * 32);
-          cf_mma(tmem_base, cf_desc(xa + off), cf_desc(wa + off), idesc, k > 0 ? 1u : 0u);
+          const uint64_t o16 = (uint64_t)(((k >> 2) * CF_CHUNK_BYTES + (k & 3) * 32) >> 4);
+          cf_mma(tmem_base, xd + o16, bd + o16, idesc, k > 0 ? 1u : 0u);
         }
         cf_commit(mma_done);
         CF_STAMP(t, 2);
@@ -223,26 +245,32 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         CF_STAMP(t, 3);
       }
     }
+    __syncwarp();
   } else {
     // ===== epilogue threads: CF_PARTS threads per chain row (= TMEM lane), alternating 16-column blocks =====
-    const int r = tid & 127;
-    const int part = tid >> 7;
-    const int qw = warp & 3;                                // TMEM lane quarter of this warp
-    const bool row_ok = r < R;
-    const int g = row_ok ? r / s : 0;                       // local sample
-    const int i_seed = r - g * s;                           // seed row within the sample
+    const int qw = warp_u & 3;                              // TMEM lane quarter of this warp
+    const int part = warp_u >> 2;
+    const int r = qw * 32 + lane;
+    const int g_raw = r / srow;                             // local sample
+    const int i_seed = r - g_raw * srow;                    // seed row within the sample
+    const bool row_ok = g_raw < nsamp && i_seed < s;
+    const int g = row_ok ? g_raw : 0;
     const long long b = b0 + g;                             // batch sample
-    const long long grow = row0 + r;                        // global chain row
+    const long long grow = row0 + (long long)g * s + i_seed;   // global chain row
     const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16);
-    const int g_lo = min(32 * qw, R > 0 ? R - 1 : 0) / s, g_hi = min(32 * qw + 31, R > 0 ? R - 1 : 0) / s;
+    const int g_lo = (32 * qw) / srow, g_hi = min((32 * qw + 31) / srow, nsamp - 1);   // samples under this warp's rows
+    const bool aligned = (srow & 31) == 0;                  // a warp never straddles two samples
+    const int nq = srow >> 5;                               // warp quarters per sample (aligned layout)
     const long long ldT = net.ldT;
-    const uint32_t xrow = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
+    uint8_t* const xrow = X + (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
     const int xsw = r & 7;
+    float* const tile = tiles + warp_u * (8 * CF_TILE_LD);
 
     // X_0 = Q_{L-1} = seed (* sg_{L-1})
     {
       const ChainLayerDev& top = net.layer[L - 1];
-      for (int k = part * 4; k < top.n_out; k += 4 * CF_PARTS) {
+      const int n16 = (top.n_out + 15) & ~15;
+      for (int k = part * 4; k < n16; k += 4 * CF_PARTS) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (row_ok) {
           float t4[4];
@@ -259,8 +287,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
           v = make_float4(t4[0], t4[1], t4[2], t4[3]);
           if (net.top_materialised && (do_backward || net.has_skip)) {
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-              if (k + u < top.n_out) ws[top.qt_off + (long long)(k + u) * ldT + grow] = t4[u];
+            for (int u = 0; u < 4; ++u) ws[top.qt_off + (long long)(k + u) * ldT + grow] = t4[u];     // (padded to 16 columns)
           }
         }
         *reinterpret_cast<float4*>(X + cf_xoff(r, k)) = v;
@@ -273,29 +300,32 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     float st_h1 = 0.f, st_rr = 0.f, st_rows = 0.f;
 #pragma unroll 1
     for (int t = 0; t < n_steps; ++t) {
-      // ---- this step's descriptor (from the shared-memory copy) ----
-      const ChainStep sd = st_s[t];
+      // ---- this step's descriptor: kernel parameter, uniform index -> uniform registers ----
+      const ChainStep& sd = steps.st[t];
       const int N = sd.N;
       int mode = sd.mode;
-      const bool add_first = sd.add_first != 0;
       bool write_x = sd.write_x != 0;
-      const long long sc_off = sd.sc_off;
-      const int sc_ld = sd.sc_ld;
-      // row-major output only for the Jacobian itself when it is the product asked for (no loss, no backward);
-      // the training path keeps nothing but the transposed copies, whose stores and loads are coalesced
-      float* out = (sd.mode == 1 && !do_loss) ? ws + sd.out_off + grow * sd.out_ld : nullptr;
-      // (a residual network re-reads earlier chain states, so it needs the transposed copies even without a backward pass)
-      float* outT = ((do_backward || net.has_skip) && sd.outT_off >= 0) ? ws + sd.outT_off + grow : nullptr;
-      const float* addT = sd.add_off >= 0 ? ws + sd.add_off + grow : nullptr;   // transposed residual
-      const long long rs_off = sd.rs_off;
-      const int rs_ld = sd.rs_ld;
-      const float* prow = nullptr;                  // per-row operand: Q_l row (row-sum) or target-Jacobian row (loss)
-      float gscale = 0.f, inv_nj = 0.f;
       if (mode == 1) {
         if (!do_loss) mode = 0;                     // Jacobian only: plain row-major output
         if (!do_backward) write_x = false;
       }
-      const float* qT = mode == 2 ? ws + sd.q_off + grow : nullptr;    // transposed Q_l (row-sum operand)
+      // row-major output only for the Jacobian itself when it is the product asked for (no loss, no backward);
+      // the training path keeps nothing but the transposed copies, whose stores and loads are coalesced
+      const bool out_on = sd.mode == 1 && !do_loss;
+      // (a residual network re-reads earlier chain states, so it needs the transposed copies even without a backward pass)
+      const bool outT_on = (do_backward || net.has_skip) && sd.outT_off >= 0 && !(dbg & 1);
+      const bool add_on = sd.add_off >= 0;
+      const bool add_first = sd.add_first != 0;
+      const bool sc_on = sd.sc_off >= 0;
+      const bool do_round = (write_x || outT_on) && !(dbg & 8);     // only what feeds a later TF32 contraction is rounded
+      float* const out_p = ws + sd.out_off + grow * sd.out_ld;
+      float* const outT_p = ws + sd.outT_off + grow;
+      const float* const addT_p = ws + sd.add_off + grow;           // transposed residual
+      const float* const qT_p = ws + sd.q_off + grow;               // transposed Q_l (row-sum operand)
+      const float* const sc_p = ws + sd.sc_off + b * sd.sc_ld;      // this row's sample: per-sample scale vector
+      const int sc_len = (sd.sc_ld < ((N + 3) & ~3)) ? sd.sc_ld : ((N + 3) & ~3);
+      const float* prow = nullptr;                  // target-Jacobian row (loss)
+      float gscale = 0.f, inv_nj = 0.f;
       if (mode == 1 && row_ok) {
         const long long sb = idx ? idx[b] : b;
         prow = jt + (sb * s + i_seed) * (long long)net.d_in;
@@ -303,168 +333,160 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         gscale = coef * inv_nj;
       }
       const bool vec_ok = prow != nullptr && ((reinterpret_cast<uintptr_t>(prow) & 15) == 0);
-      const bool do_round = (write_x || outT != nullptr) && !(dbg & 8);     // only what feeds a later TF32 contraction is rounded
-      // ---- while the MMA runs: stage the per-sample scale vectors, prefetch the first operand block ----
-      if (sc_off >= 0) {
-        for (int e = tid; e < nsamp * 128; e += CF_EPI) {
-          const int gg = e >> 7, n = e & 127;
-          sc_s[e] = n < N ? ws[sc_off + (long long)(b0 + gg) * sc_ld + n] : 0.f;
-        }
-      }
-      float opnd[CF_CW];
+      // ---- while the MMA runs: request the first block's operands ----
+      const int c_first = part * CF_CW;
+      float opnd[CF_CW], scl[CF_CW];
 #pragma unroll
-      for (int j = 0; j < CF_CW; ++j) opnd[j] = 0.f;
-      if (part * CF_CW < N) {
-        if (qT != nullptr) cf_load16T(opnd, qT, part * CF_CW, N, row_ok, ldT);
-        else if (prow != nullptr) cf_load16(opnd, prow, part * CF_CW, N, row_ok, vec_ok);
+      for (int j = 0; j < CF_CW; ++j) { opnd[j] = 0.f; scl[j] = 1.f; }
+      if (c_first < N) {
+        if (mode == 2) cf_loadT(opnd, qT_p + (long long)c_first * ldT, ldT, row_ok);
+        else if (mode == 1) cf_load16(opnd, prow, c_first, N, row_ok, vec_ok);
+        if (sc_on) cf_load_vec16(scl, sc_p, c_first, sc_len);
       }
-      asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");       // scale vectors staged
+      if (tid == 0) CF_STAMP(32 + t, 3);
       cf_mbar_wait(mma_done, t & 1);
       if (tid == 0) CF_STAMP(t, 4);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const float* scale = sc_off >= 0 ? sc_s + g * 128 : nullptr;
       float e_row = 0.f, n_row = 0.f;
 #pragma unroll 1
-      for (int c0 = part * CF_CW; c0 < N; c0 += CF_CW * CF_PARTS) {
+      for (int c0 = c_first; c0 < N; c0 += CF_CW * CF_PARTS) {
         float v[CF_CW];
-        if (dbg & 4) {
+        cf_tmem_ld16(taddr + (uint32_t)c0, v);
+        // this block's operands were requested one block ago; request the next block's before working on this one
+        float cur[CF_CW], sc[CF_CW];
 #pragma unroll
-          for (int j = 0; j < CF_CW; ++j) v[j] = 1.f;
-        } else cf_tmem_ld16(taddr + (uint32_t)c0, v);
-        if (c0 != part * CF_CW) {
-          if (qT != nullptr) cf_load16T(opnd, qT, c0, N, row_ok, ldT);
-          else if (prow != nullptr) cf_load16(opnd, prow, c0, N, row_ok, vec_ok);
+        for (int j = 0; j < CF_CW; ++j) { cur[j] = opnd[j]; sc[j] = scl[j]; }
+        {
+          const int c1 = c0 + CF_CW * CF_PARTS;
+          if (c1 < N) {
+            if (mode == 2) cf_loadT(opnd, qT_p + (long long)c1 * ldT, ldT, row_ok);
+            else if (mode == 1) cf_load16(opnd, prow, c1, N, row_ok, vec_ok);
+            if (sc_on) cf_load_vec16(scl, sc_p, c1, sc_len);
+          }
         }
         if (mode == 2) {
-          // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l  (segmented over the samples of this warp's rows)
-          for (int gg = g_lo; gg <= g_hi; ++gg) {
-            float m[CF_CW];
+          // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l   (rows beyond the sample carry zeros in dQ_l)
+          if (aligned) {
+            // the warp's 32 rows belong to one sample: transpose 8 columns at a time through the warp's tile,
+            // lane (c, q) adds rows 8q..8q+7 of column c, two shuffles finish; one writer per (quarter, column)
 #pragma unroll
-            for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[j] * opnd[j] : 0.f;
-            const float tot = cf_colsum16(m, lane);
-            if (lane < 16 && c0 + lane < N) atomicAdd(&rs_acc[gg * 128 + c0 + lane], tot);
-          }
-        }
-        if (row_ok && addT == nullptr && c0 + CF_CW <= N) {
-          // ---- fast path: a full 16-column block of a valid row, no residual: no per-element guards ----
-          float x[CF_CW];
-          if (scale != nullptr) {
+            for (int h = 0; h < 2; ++h) {
 #pragma unroll
-            for (int j = 0; j < CF_CW; j += 4) {
-              const float4 a = *reinterpret_cast<const float4*>(scale + c0 + j);
-              x[j] = v[j] * a.x; x[j + 1] = v[j + 1] * a.y; x[j + 2] = v[j + 2] * a.z; x[j + 3] = v[j + 3] * a.w;
+              for (int j = 0; j < 8; ++j) tile[j * CF_TILE_LD + lane] = v[8 * h + j] * cur[8 * h + j];
+              __syncwarp();
+              const float* tp = tile + (lane & 7) * CF_TILE_LD + (lane >> 3) * 8;
+              const float4 a = *reinterpret_cast<const float4*>(tp), c = *reinterpret_cast<const float4*>(tp + 4);
+              float sum = ((a.x + a.y) + (a.z + a.w)) + ((c.x + c.y) + (c.z + c.w));
+              sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+              sum += __shfl_xor_sync(0xffffffffu, sum, 16);
+              if (lane < 8) rs_acc[qw * 128 + c0 + 8 * h + lane] = sum;
+              __syncwarp();
             }
           } else {
+            for (int gg = g_lo; gg <= g_hi; ++gg) {           // segmented over the samples under this warp's rows
+              float m[CF_CW];
 #pragma unroll
-            for (int j = 0; j < CF_CW; ++j) x[j] = v[j];
-          }
-          if (mode == 1) {
-#pragma unroll
-            for (int j = 0; j < CF_CW; ++j) {
-              const float tv = opnd[j];
-              const float d = x[j] - tv;
-              e_row = fmaf(d, d, e_row);
-              n_row = fmaf(tv, tv, n_row);
-              x[j] = gscale * d;
+              for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[j] * cur[j] : 0.f;
+              const float tot = cf_colsum16(m, lane);
+              if (lane < 16 && c0 + lane < N) atomicAdd(&rs_acc[gg * 128 + c0 + lane], tot);
             }
           }
-          if (do_round) {
+        }
+        // ---- value of the block: residual, per-sample scaling, loss ----
+        float x[CF_CW];
 #pragma unroll
-            for (int j = 0; j < CF_CW; ++j) x[j] = round_tf32_f(x[j]);
+        for (int j = 0; j < CF_CW; ++j) x[j] = v[j];
+        if (add_on) {
+          float ad[CF_CW];
+          cf_loadT(ad, addT_p + (long long)c0 * ldT, ldT, row_ok);
+          if (add_first) {
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) x[j] = (x[j] + ad[j]) * sc[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) x[j] = fmaf(x[j], sc[j], ad[j]);
           }
-          if (outT != nullptr) {                     // transposed copy: one coalesced 128-byte store per column
-            float* pT = outT + (long long)c0 * ldT;
+        } else if (sc_on) {
+#pragma unroll
+          for (int j = 0; j < CF_CW; ++j) x[j] *= sc[j];
+        }
+        if (mode == 1) {
+#pragma unroll
+          for (int j = 0; j < CF_CW; ++j) {
+            const float tv = cur[j];
+            const float d = x[j] - tv;
+            e_row = fmaf(d, d, e_row);
+            n_row = fmaf(tv, tv, n_row);
+            x[j] = gscale * d;
+          }
+        }
+        if (do_round) {
+#pragma unroll
+          for (int j = 0; j < CF_CW; ++j) x[j] = round_tf32_f(x[j]);
+        }
+        // ---- stores: whole 16-column blocks (the transposed arrays and X are padded; padded columns are exact zeros) ----
+        if (row_ok) {
+          if (outT_on) {                             // transposed copy: one coalesced 128-byte store per column
+            float* pT = outT_p + (long long)c0 * ldT;
 #pragma unroll
             for (int j = 0; j < CF_CW; ++j) { *pT = x[j]; pT += ldT; }
           }
-          if (out != nullptr) {
+          if (out_on) {
 #pragma unroll
-            for (int j = 0; j < CF_CW; j += 4) *reinterpret_cast<float4*>(out + c0 + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+            for (int j = 0; j < CF_CW; j += 4)
+              if (c0 + j < sd.out_ld) *reinterpret_cast<float4*>(out_p + c0 + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
           }
-          if (write_x) {
-            uint8_t* xb = X + (uint32_t)((c0 >> 5) * CF_CHUNK_BYTES) + xrow;
+          if (write_x && !(dbg & 2)) {
+            uint8_t* xb = xrow + (uint32_t)((c0 >> 5) * CF_CHUNK_BYTES);
             const int j0 = (c0 & 31) >> 2;
 #pragma unroll
             for (int j = 0; j < CF_CW; j += 4)
               *reinterpret_cast<float4*>(xb + (((j0 + (j >> 2)) ^ xsw) << 4)) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
           }
-        } else if (row_ok) {
-          // ---- generic path: tail block of a row and/or residual add ----
-#pragma unroll
-        for (int j = 0; j < CF_CW; j += 4) {
-          const int n = c0 + j;
-          float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (row_ok && n < N) {
-            float x[4] = {v[j], v[j + 1], v[j + 2], v[j + 3]};
-            if (addT != nullptr && add_first) {
-#pragma unroll
-              for (int u = 0; u < 4; ++u) if (n + u < N) x[u] += addT[(long long)(n + u) * ldT];
-            }
-            if (scale != nullptr) { const float4 a = *reinterpret_cast<const float4*>(scale + n); x[0] *= a.x; x[1] *= a.y; x[2] *= a.z; x[3] *= a.w; }
-            if (addT != nullptr && !add_first) {
-#pragma unroll
-              for (int u = 0; u < 4; ++u) if (n + u < N) x[u] += addT[(long long)(n + u) * ldT];
-            }
-            if (mode == 1) {
-#pragma unroll
-              for (int u = 0; u < 4; ++u) {
-                if (n + u < N) {
-                  const float tv = opnd[j + u];
-                  const float d = x[u] - tv;
-                  e_row = fmaf(d, d, e_row);
-                  n_row = fmaf(tv, tv, n_row);
-                  x[u] = gscale * d;
-                }
-              }
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) x[u] = (n + u < N) ? (do_round ? round_tf32_f(x[u]) : x[u]) : 0.f;
-            o = make_float4(x[0], x[1], x[2], x[3]);
-            if (out != nullptr) *reinterpret_cast<float4*>(out + n) = o;
-            if (outT != nullptr && !(dbg & 1)) {                 // transposed copy: consecutive threads = consecutive rows
-#pragma unroll
-              for (int u = 0; u < 4; ++u)
-                if (n + u < N) outT[(long long)(n + u) * ldT] = x[u];
-            }
-          }
-          if (write_x && !(dbg & 2)) *reinterpret_cast<float4*>(X + (uint32_t)((n >> 5) * CF_CHUNK_BYTES) + xrow + ((((n & 31) >> 2) ^ xsw) << 4)) = o;
         }
-              }
-      }
-      // the next contraction reads X up to the next multiple of 8 columns: clear [round4(N), round8(N))
-      if (write_x) {
-        const int n4 = (N + 3) & ~3;
-        if (n4 < ((N + 7) & ~7) && ((n4 >> 4) & (CF_PARTS - 1)) == part)
-          *reinterpret_cast<float4*>(X + cf_xoff(r, n4)) = make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-      if (mode == 1) {
-        if (row_ok) st_h1 += e_row * inv_nj;
-        ex_s[(part * 128 + r) * 2 + 0] = e_row;               // the per-row metric needs the FULL row sums
-        ex_s[(part * 128 + r) * 2 + 1] = n_row;
       }
       if (tid == 0) CF_STAMP(t, 5);
-      asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");       // end of step: sc_s / rs_acc / ex_s are consistent
-      if (tid == 0) CF_STAMP(t, 6);
-      if (mode == 1 && part == 0 && row_ok) {
-        float e_all = 0.f, n_all = 0.f;
-#pragma unroll
-        for (int pp = 0; pp < CF_PARTS; ++pp) { e_all += ex_s[(pp * 128 + r) * 2 + 0]; n_all += ex_s[(pp * 128 + r) * 2 + 1]; }
-        st_rr += e_all / n_all;
-        st_rows += 1.f;
-      }
-      if (mode == 2) {                                          // publish the row sums of this layer
-        for (int e = tid; e < nsamp * 128; e += CF_EPI) {
-          const int gg = e >> 7, n = e & 127;
-          if (n < N) ws[rs_off + (long long)(b0 + gg) * rs_ld + n] = rs_acc[e];
-          rs_acc[e] = 0.f;
-        }
-      }
+      // ---- hand X to the tensor core as soon as this warp's blocks are in place ----
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       if (t + 1 < n_steps) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) cf_mbar_arrive(x_ready);
       }
+      // ---- cross-warp leftovers of the step (off the critical path of the next contraction) ----
+      if (mode != 0) {
+        if (mode == 1) {
+          if (row_ok) st_h1 += e_row * inv_nj;
+          ex_s[(part * 128 + r) * 2 + 0] = e_row;               // the per-row metric needs the FULL row sums
+          ex_s[(part * 128 + r) * 2 + 1] = n_row;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");
+        if (mode == 1 && part == 0 && row_ok) {
+          float e_all = 0.f, n_all = 0.f;
+#pragma unroll
+          for (int pp = 0; pp < CF_PARTS; ++pp) { e_all += ex_s[(pp * 128 + r) * 2 + 0]; n_all += ex_s[(pp * 128 + r) * 2 + 1]; }
+          st_rr += e_all / n_all;
+          st_rows += 1.f;
+        }
+        if (mode == 2) {                                          // publish the row sums of this layer
+          float* const rs_p = ws + sd.rs_off + (long long)b0 * sd.rs_ld;
+          for (int e = tid; e < nsamp * 128; e += CF_EPI) {
+            const int gg = e >> 7, n = e & 127;
+            if (aligned) {
+              if (n < N) {
+                float sum = 0.f;
+                for (int q = 0; q < nq; ++q) sum += rs_acc[(gg * nq + q) * 128 + n];
+                rs_p[(long long)gg * sd.rs_ld + n] = sum;
+              }
+            } else {
+              if (n < N) rs_p[(long long)gg * sd.rs_ld + n] = rs_acc[e];
+              rs_acc[e] = 0.f;
+            }
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");     // rs_acc is free again before the next row-sum step writes it
+        }
+      }
+      if (tid == 0) CF_STAMP(t, 6);
     }
     if (do_loss) {
 #pragma unroll
@@ -481,7 +503,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == CF_EPI_WARPS)
+  if (warp_u == CF_EPI_WARPS)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
 }
 
@@ -581,7 +603,7 @@ cudaError_t chain_fused_read_trace(unsigned long long* out) {
 cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, const ChainSteps& steps, float* ws, const float* jt, const float* jn2,
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
                                float* stats, cudaStream_t st) {
-  constexpr int SMEM = 3 * CF_X_BYTES + 64 + 2 * 16 * 128 * 4 + CF_PARTS * 128 * 2 * 4 + (int)sizeof(ChainSteps) + 1024;
+  constexpr int SMEM = 3 * CF_X_BYTES + 64 + 16 * 128 * 4 + CF_PARTS * 128 * 2 * 4 + CF_EPI_WARPS * 8 * CF_TILE_LD * 4 + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(chain_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);

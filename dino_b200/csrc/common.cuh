@@ -141,7 +141,8 @@ namespace dino {
 constexpr int CHAIN_FUSED_MAX_LAYERS = 16;
 // qt_off / drt_off: TRANSPOSED copies [n_out, ldT] of Q_l and dR_{l+1} (operands of the tensor-core weight gradient)
 struct ChainLayerDev { long long q_off, sg_off, rs_off, dr_off, qt_off, drt_off; int n_in, n_out, ld_out, act, skip_from, lands_skip; };
-struct ChainNetDev { int L, s, G, d_in, ld_in, top_materialised, has_skip; long long r0_off, r0t_off, ldT; ChainLayerDev layer[CHAIN_FUSED_MAX_LAYERS]; };
+// srow: chain rows reserved per sample inside a CTA tile (s rounded up to a warp when the tile has room, so a warp never straddles two samples)
+struct ChainNetDev { int L, s, G, srow, d_in, ld_in, top_materialised, has_skip; long long r0_off, r0t_off, ldT; ChainLayerDev layer[CHAIN_FUSED_MAX_LAYERS]; };
 // One contraction + epilogue of the fused kernel, in execution order (built on the host: the device code
 // carries no layer logic).  Offsets are into the workspace, -1 = absent.
 struct ChainStep {

@@ -246,6 +246,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     ChainNetDev& c = p->chain;
     memset(&c, 0, sizeof(c));
     c.L = p->L; c.s = p->s; c.G = p->s <= 128 ? 128 / p->s : 0; if (c.G > 16) c.G = 16;
+    c.srow = (c.G * ((p->s + 31) & ~31) <= 128) ? ((p->s + 31) & ~31) : p->s;
     c.d_in = p->d_in; c.ld_in = (int)p->ld_in; c.top_materialised = p->top_materialised ? 1 : 0; c.r0_off = p->off_r0;
     for (int l = 0; l < p->L; ++l) {
       const LayerPlan& lp = p->layers[l];
@@ -258,11 +259,13 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     p->chain_fused = chain_fused_supported(c);
     if (p->chain_fused) {
       c.ldT = r4(Ms);
-      c.r0t_off = take((long long)p->d_in * c.ldT);
+      // the fused kernel moves whole 16-column blocks: the transposed arrays carry (zero) columns up to the next multiple of 16
+      auto r16 = [](int n) { return (long long)((n + 15) & ~15); };
+      c.r0t_off = take(r16(p->d_in) * c.ldT);
       for (int l = 0; l < p->L; ++l) {
         LayerPlan& lp = p->layers[l];
-        lp.qt_off = take((long long)lp.n_out * c.ldT);
-        lp.drt_off = l < p->L - 1 ? take((long long)lp.n_out * c.ldT) : -1;
+        lp.qt_off = take(r16(lp.n_out) * c.ldT);
+        lp.drt_off = l < p->L - 1 ? take(r16(lp.n_out) * c.ldT) : -1;
         c.layer[l].qt_off = lp.qt_off; c.layer[l].drt_off = lp.drt_off;
       }
       chain_fused_build_steps(&p->chain_steps, c);

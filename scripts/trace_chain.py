@@ -27,3 +27,9 @@ names = ["x_ready", "w_full", "commit", "w_issued", "mma_done", "epi_end", "bar_
 print("step  " + "  ".join(f"{n:>9s}" for n in names) + "   (ns since first stamp)")
 for s in range(17):
     print(f"{s:4d}  " + "  ".join(f"{int(v - t0):9d}" for v in t[s, :7]))
+
+print("epilogue detail (tid 0): pre_bar | it0: start, tmem_ld, rowsum | it1: start, tmem_ld, rowsum | loop_end   (ns since mma_done)")
+for s in range(17):
+    base = t[s, 4]
+    e = t[32 + s]
+    print(f"{s:4d}  pre_bar {int(e[3]-base):6d} | " + "  ".join(f"{int(e[k]-base):6d}" for k in (0, 1, 2)) + " | " + "  ".join(f"{int(e[k]-base):6d}" for k in (4, 5, 6)) + f" | {int(e[7]-base):6d}")
