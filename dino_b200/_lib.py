@@ -68,6 +68,8 @@ SIGNATURES = {
                                C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "dino_gemm_nt_acc": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32,
                                    C.c_int32, C.c_int32, C.c_void_p]),
+    "dino_gemm_tn_acc": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32,
+                                   C.c_int32, C.c_int32, C.c_void_p]),
     "dino_plan_profile": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "dino_debug_chain_trace": (C.c_int, [C.c_void_p]),
     "dino_launch_count": (C.c_int64, []),

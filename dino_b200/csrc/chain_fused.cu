@@ -36,6 +36,7 @@ constexpr int CF_EPI = 128 * CF_PARTS;                                          
 constexpr int CF_EPI_WARPS = CF_EPI / 32;
 constexpr int CF_THREADS = CF_EPI + 32;                                            // + 1 control warp
 constexpr int CF_CW = 16;                                                          // columns per TMEM load / work item
+constexpr int CF_ACC_COLS = 128;                                                   // TMEM columns per accumulator (two of them: steps alternate)
 constexpr int CF_TILE_LD = 36;                                                     // floats per column of a warp's row-sum transposition tile
 
 __device__ __forceinline__ uint32_t cf_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -74,6 +75,22 @@ __device__ __forceinline__ void cf_mma(uint32_t tmem_d, uint64_t adesc, uint64_t
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
       "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void cf_sts128(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void cf_sts32(uint32_t addr, float a) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(a) : "memory");
+}
+__device__ __forceinline__ float4 cf_lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+// round-to-nearest (ties away) to the 10-bit TF32 mantissa: what cvt.rna.tf32.f32 does for finite values, without its
+// Inf/NaN guard (a non-finite chain state has already lost the step)
+__device__ __forceinline__ float cf_round_tf32(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
 }
 __device__ __forceinline__ bool cf_elect_one() {
   uint32_t pred;
@@ -139,20 +156,19 @@ __device__ __forceinline__ void cf_load16(float (&d)[CF_CW], const float* row, i
   }
 }
 
-// 16 consecutive columns of one chain row from a TRANSPOSED array (column n at p[n * ldT]): lanes = consecutive
-// rows, so every load is one coalesced 128-byte request.  The arrays are padded to whole 16-column blocks.
-__device__ __forceinline__ void cf_loadT(float (&d)[CF_CW], const float* p, long long ldT, bool ok) {
-#pragma unroll
-  for (int j = 0; j < CF_CW; ++j) { d[j] = ok ? *p : 0.f; p += ldT; }
-}
-// 16 consecutive floats of a per-sample vector (zero at and beyond `len`; `len` and the row pitch are multiples of 4)
-__device__ __forceinline__ void cf_load_vec16(float (&d)[CF_CW], const float* row, int c0, int len) {
+// 16 consecutive floats of a row (zero at and beyond `len`; `len`, the row pitch and c0 are multiples of 4)
+__device__ __forceinline__ void cf_load_vec16(float (&d)[CF_CW], const float* row, int c0, int len, bool ok = true) {
 #pragma unroll
   for (int j = 0; j < CF_CW; j += 4) {
     float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (c0 + j < len) q4 = *reinterpret_cast<const float4*>(row + c0 + j);
+    if (ok && c0 + j < len) q4 = *reinterpret_cast<const float4*>(row + c0 + j);
     d[j] = q4.x; d[j + 1] = q4.y; d[j + 2] = q4.z; d[j + 3] = q4.w;
   }
+}
+__device__ __forceinline__ void cf_store_vec16(float* row, int c0, int len, const float (&x)[CF_CW]) {
+#pragma unroll
+  for (int j = 0; j < CF_CW; j += 4)
+    if (c0 + j < len) *reinterpret_cast<float4*>(row + c0 + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
 }
 
 __global__ void __launch_bounds__(CF_THREADS, 1)
@@ -195,7 +211,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(cf_smem_u32(tmem_slot)), "r"(128u) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(cf_smem_u32(tmem_slot)), "r"(2u * CF_ACC_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the zero fill of X must be visible to the tensor core
@@ -237,7 +253,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
 #pragma unroll 1
         for (int k = 0; k < ksteps; ++k) {
           const uint64_t o16 = (uint64_t)(((k >> 2) * CF_CHUNK_BYTES + (k & 3) * 32) >> 4);
-          cf_mma(tmem_base, xd + o16, bd + o16, idesc, k > 0 ? 1u : 0u);
+          cf_mma(tmem_base + (uint32_t)(buf * CF_ACC_COLS), xd + o16, bd + o16, idesc, k > 0 ? 1u : 0u);
         }
         cf_commit(mma_done);
         CF_STAMP(t, 2);
@@ -248,6 +264,10 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     __syncwarp();
   } else {
     // ===== epilogue threads: CF_PARTS threads per chain row (= TMEM lane), alternating 16-column blocks =====
+    // Every step has two phases over the thread's column blocks.  Phase A is the critical path: accumulator ->
+    // next operand X, then X is handed to the tensor core.  Phase B re-reads the same accumulator (the next
+    // contraction writes the OTHER TMEM buffer) and does everything nobody waits for: transposed copies to
+    // global memory, row sums, loss statistics.  Phase B of step t overlaps the contraction of step t+1.
     const int qw = warp_u & 3;                              // TMEM lane quarter of this warp
     const int part = warp_u >> 2;
     const int r = qw * 32 + lane;
@@ -261,19 +281,20 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     const int g_lo = (32 * qw) / srow, g_hi = min((32 * qw + 31) / srow, nsamp - 1);   // samples under this warp's rows
     const bool aligned = (srow & 31) == 0;                  // a warp never straddles two samples
     const int nq = srow >> 5;                               // warp quarters per sample (aligned layout)
-    const long long ldT = net.ldT;
-    uint8_t* const xrow = X + (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
+    const uint32_t xrow = cf_smem_u32(X) + (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
     const int xsw = r & 7;
-    float* const tile = tiles + warp_u * (8 * CF_TILE_LD);
+    const uint32_t tile_u = cf_smem_u32(tiles) + (uint32_t)(warp_u * (8 * CF_TILE_LD) * 4);
+    const uint32_t rs_u = cf_smem_u32(rs_acc);
+    constexpr int STRIDE = CF_CW * CF_PARTS;
+    const int c_first = part * CF_CW;
 
     // X_0 = Q_{L-1} = seed (* sg_{L-1})
     {
       const ChainLayerDev& top = net.layer[L - 1];
       const int n16 = (top.n_out + 15) & ~15;
       for (int k = part * 4; k < n16; k += 4 * CF_PARTS) {
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        float t4[4] = {0.f, 0.f, 0.f, 0.f};
         if (row_ok) {
-          float t4[4];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int kk = k + u;
@@ -284,13 +305,10 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             }
             t4[u] = x;
           }
-          v = make_float4(t4[0], t4[1], t4[2], t4[3]);
-          if (net.top_materialised && (do_backward || net.has_skip)) {
-#pragma unroll
-            for (int u = 0; u < 4; ++u) ws[top.qt_off + (long long)(k + u) * ldT + grow] = t4[u];     // (padded to 16 columns)
-          }
+          if (net.top_materialised && (do_backward || net.has_skip) && k < top.ld_out)
+            *reinterpret_cast<float4*>(ws + top.q_off + grow * top.ld_out + k) = make_float4(t4[0], t4[1], t4[2], t4[3]);
         }
-        *reinterpret_cast<float4*>(X + cf_xoff(r, k)) = v;
+        cf_sts128(cf_smem_u32(X) + cf_xoff(r, k), t4[0], t4[1], t4[2], t4[3]);
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
@@ -304,24 +322,21 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       const ChainStep& sd = steps.st[t];
       const int N = sd.N;
       int mode = sd.mode;
-      bool write_x = sd.write_x != 0;
+      bool write_x = sd.write_x != 0 && !(dbg & 2);
       if (mode == 1) {
         if (!do_loss) mode = 0;                     // Jacobian only: plain row-major output
         if (!do_backward) write_x = false;
       }
-      // row-major output only for the Jacobian itself when it is the product asked for (no loss, no backward);
-      // the training path keeps nothing but the transposed copies, whose stores and loads are coalesced
-      const bool out_on = sd.mode == 1 && !do_loss;
-      // (a residual network re-reads earlier chain states, so it needs the transposed copies even without a backward pass)
-      const bool outT_on = (do_backward || net.has_skip) && sd.outT_off >= 0 && !(dbg & 1);
+      // the result goes to global memory (row-major, each thread 64 contiguous bytes of its row) when somebody reads it
+      // later: the weight-gradient launch after a training step, a residual connection, or the caller (the Jacobian)
+      const bool out_on = sd.out_off >= 0 && (do_backward || net.has_skip || (sd.mode == 1 && !do_loss)) && !(dbg & 1);
       const bool add_on = sd.add_off >= 0;
       const bool add_first = sd.add_first != 0;
-      const bool sc_on = sd.sc_off >= 0;
-      const bool do_round = (write_x || outT_on) && !(dbg & 8);     // only what feeds a later TF32 contraction is rounded
+      const bool sc_on = sd.sc_off >= 0 && !(dbg & 64);
+      const bool do_round = (write_x || do_backward) && !(dbg & 8);  // only what feeds a later TF32 contraction is rounded
       float* const out_p = ws + sd.out_off + grow * sd.out_ld;
-      float* const outT_p = ws + sd.outT_off + grow;
-      const float* const addT_p = ws + sd.add_off + grow;           // transposed residual
-      const float* const qT_p = ws + sd.q_off + grow;               // transposed Q_l (row-sum operand)
+      const float* const add_p = ws + sd.add_off + grow * sd.add_ld;   // residual rows
+      const float* const q_p = ws + sd.q_off + grow * sd.q_ld;         // Q_l rows (row-sum operand)
       const float* const sc_p = ws + sd.sc_off + b * sd.sc_ld;      // this row's sample: per-sample scale vector
       const int sc_len = (sd.sc_ld < ((N + 3) & ~3)) ? sd.sc_ld : ((N + 3) & ~3);
       const float* prow = nullptr;                  // target-Jacobian row (loss)
@@ -333,72 +348,15 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         gscale = coef * inv_nj;
       }
       const bool vec_ok = prow != nullptr && ((reinterpret_cast<uintptr_t>(prow) & 15) == 0);
-      // ---- while the MMA runs: request the first block's operands ----
-      const int c_first = part * CF_CW;
-      float opnd[CF_CW], scl[CF_CW];
-#pragma unroll
-      for (int j = 0; j < CF_CW; ++j) { opnd[j] = 0.f; scl[j] = 1.f; }
-      if (c_first < N) {
-        if (mode == 2) cf_loadT(opnd, qT_p + (long long)c_first * ldT, ldT, row_ok);
-        else if (mode == 1) cf_load16(opnd, prow, c_first, N, row_ok, vec_ok);
-        if (sc_on) cf_load_vec16(scl, sc_p, c_first, sc_len);
-      }
-      if (tid == 0) CF_STAMP(32 + t, 3);
-      cf_mbar_wait(mma_done, t & 1);
-      if (tid == 0) CF_STAMP(t, 4);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      float e_row = 0.f, n_row = 0.f;
-#pragma unroll 1
-      for (int c0 = c_first; c0 < N; c0 += CF_CW * CF_PARTS) {
-        float v[CF_CW];
-        cf_tmem_ld16(taddr + (uint32_t)c0, v);
-        // this block's operands were requested one block ago; request the next block's before working on this one
-        float cur[CF_CW], sc[CF_CW];
-#pragma unroll
-        for (int j = 0; j < CF_CW; ++j) { cur[j] = opnd[j]; sc[j] = scl[j]; }
-        {
-          const int c1 = c0 + CF_CW * CF_PARTS;
-          if (c1 < N) {
-            if (mode == 2) cf_loadT(opnd, qT_p + (long long)c1 * ldT, ldT, row_ok);
-            else if (mode == 1) cf_load16(opnd, prow, c1, N, row_ok, vec_ok);
-            if (sc_on) cf_load_vec16(scl, sc_p, c1, sc_len);
-          }
-        }
-        if (mode == 2) {
-          // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l   (rows beyond the sample carry zeros in dQ_l)
-          if (aligned) {
-            // the warp's 32 rows belong to one sample: transpose 8 columns at a time through the warp's tile,
-            // lane (c, q) adds rows 8q..8q+7 of column c, two shuffles finish; one writer per (quarter, column)
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) tile[j * CF_TILE_LD + lane] = v[8 * h + j] * cur[8 * h + j];
-              __syncwarp();
-              const float* tp = tile + (lane & 7) * CF_TILE_LD + (lane >> 3) * 8;
-              const float4 a = *reinterpret_cast<const float4*>(tp), c = *reinterpret_cast<const float4*>(tp + 4);
-              float sum = ((a.x + a.y) + (a.z + a.w)) + ((c.x + c.y) + (c.z + c.w));
-              sum += __shfl_xor_sync(0xffffffffu, sum, 8);
-              sum += __shfl_xor_sync(0xffffffffu, sum, 16);
-              if (lane < 8) rs_acc[qw * 128 + c0 + 8 * h + lane] = sum;
-              __syncwarp();
-            }
-          } else {
-            for (int gg = g_lo; gg <= g_hi; ++gg) {           // segmented over the samples under this warp's rows
-              float m[CF_CW];
-#pragma unroll
-              for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[j] * cur[j] : 0.f;
-              const float tot = cf_colsum16(m, lane);
-              if (lane < 16 && c0 + lane < N) atomicAdd(&rs_acc[gg * 128 + c0 + lane], tot);
-            }
-          }
-        }
-        // ---- value of the block: residual, per-sample scaling, loss ----
-        float x[CF_CW];
+      const uint32_t acc = taddr + (uint32_t)((t & 1) * CF_ACC_COLS);
+
+      // value of a 16-column block (identical in both phases): residual and per-sample scaling ...
+      auto block_pre = [&](float (&x)[CF_CW], const float (&v)[CF_CW], const float (&sc)[CF_CW], int c0) {
 #pragma unroll
         for (int j = 0; j < CF_CW; ++j) x[j] = v[j];
         if (add_on) {
           float ad[CF_CW];
-          cf_loadT(ad, addT_p + (long long)c0 * ldT, ldT, row_ok);
+          cf_load_vec16(ad, add_p, c0, sd.add_ld, row_ok);
           if (add_first) {
 #pragma unroll
             for (int j = 0; j < CF_CW; ++j) x[j] = (x[j] + ad[j]) * sc[j];
@@ -410,50 +368,120 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
 #pragma unroll
           for (int j = 0; j < CF_CW; ++j) x[j] *= sc[j];
         }
+      };
+      // ... then the loss gradient (last forward step) and the TF32 rounding of whatever feeds a later contraction
+      auto block_post = [&](float (&x)[CF_CW], const float (&tg)[CF_CW]) {
         if (mode == 1) {
 #pragma unroll
-          for (int j = 0; j < CF_CW; ++j) {
-            const float tv = cur[j];
-            const float d = x[j] - tv;
-            e_row = fmaf(d, d, e_row);
-            n_row = fmaf(tv, tv, n_row);
-            x[j] = gscale * d;
-          }
+          for (int j = 0; j < CF_CW; ++j) x[j] = gscale * (x[j] - tg[j]);
         }
         if (do_round) {
 #pragma unroll
-          for (int j = 0; j < CF_CW; ++j) x[j] = round_tf32_f(x[j]);
+          for (int j = 0; j < CF_CW; ++j) x[j] = cf_round_tf32(x[j]);
         }
-        // ---- stores: whole 16-column blocks (the transposed arrays and X are padded; padded columns are exact zeros) ----
-        if (row_ok) {
-          if (outT_on) {                             // transposed copy: one coalesced 128-byte store per column
-            float* pT = outT_p + (long long)c0 * ldT;
+      };
+      // per-block operands: scale vector block, target-Jacobian block
+      auto load_sc_tg = [&](float (&sc)[CF_CW], float (&tg)[CF_CW], int c0) {
+        if (sc_on) cf_load_vec16(sc, sc_p, c0, sc_len);
+        if (mode == 1) cf_load16(tg, prow, c0, N, row_ok, vec_ok);
+      };
+
+      // ---- while the MMA runs: request the first block's operands ----
+      float sc0[CF_CW], tg0[CF_CW], q0[CF_CW];
 #pragma unroll
-            for (int j = 0; j < CF_CW; ++j) { *pT = x[j]; pT += ldT; }
-          }
-          if (out_on) {
+      for (int j = 0; j < CF_CW; ++j) { sc0[j] = 1.f; tg0[j] = 0.f; q0[j] = 0.f; }
+      if (c_first < N) {
+        load_sc_tg(sc0, tg0, c_first);
+        if (mode == 2) cf_load_vec16(q0, q_p, c_first, sd.q_ld, row_ok);
+      }
+      cf_mbar_wait(mma_done, t & 1);
+      if (tid == 0) CF_STAMP(t, 4);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+      // ---- phase A: accumulator -> next operand X (and its row-major copy in global memory), hand X over ----
+      if (write_x || out_on) {
+#pragma unroll 1
+        for (int c0 = c_first; c0 < N; c0 += STRIDE) {
+          float v[CF_CW], sc[CF_CW], tg[CF_CW], x[CF_CW];
+          cf_tmem_ld16(acc + (uint32_t)c0, v);
 #pragma unroll
-            for (int j = 0; j < CF_CW; j += 4)
-              if (c0 + j < sd.out_ld) *reinterpret_cast<float4*>(out_p + c0 + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
-          }
-          if (write_x && !(dbg & 2)) {
-            uint8_t* xb = xrow + (uint32_t)((c0 >> 5) * CF_CHUNK_BYTES);
+          for (int j = 0; j < CF_CW; ++j) { sc[j] = sc0[j]; tg[j] = tg0[j]; }
+          if (c0 != c_first) load_sc_tg(sc, tg, c0);
+          block_pre(x, v, sc, c0);
+          block_post(x, tg);
+          if (write_x) {
+            const uint32_t xb = xrow + (uint32_t)((c0 >> 5) * CF_CHUNK_BYTES);
             const int j0 = (c0 & 31) >> 2;
 #pragma unroll
             for (int j = 0; j < CF_CW; j += 4)
-              *reinterpret_cast<float4*>(xb + (((j0 + (j >> 2)) ^ xsw) << 4)) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+              cf_sts128(xb + (uint32_t)(((j0 + (j >> 2)) ^ xsw) << 4), x[j], x[j + 1], x[j + 2], x[j + 3]);
           }
+          if (out_on && row_ok) cf_store_vec16(out_p, c0, sd.out_ld, x);     // padded columns are exact zeros
         }
       }
-      if (tid == 0) CF_STAMP(t, 5);
-      // ---- hand X to the tensor core as soon as this warp's blocks are in place ----
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       if (t + 1 < n_steps) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) cf_mbar_arrive(x_ready);
       }
-      // ---- cross-warp leftovers of the step (off the critical path of the next contraction) ----
+      if (tid == 0) CF_STAMP(t, 5);
+
+      // ---- phase B: everything nobody waits for (overlaps the next contraction) ----
+      float e_row = 0.f, n_row = 0.f;
+      if (mode != 0 && !(dbg & 16)) {
+#pragma unroll 1
+        for (int c0 = c_first; c0 < N; c0 += STRIDE) {
+          float v[CF_CW];
+          cf_tmem_ld16(acc + (uint32_t)c0, v);
+          if (mode == 2 && !(dbg & 32)) {
+            // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l   (rows beyond the sample carry zeros in dQ_l)
+            float q[CF_CW];
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) q[j] = q0[j];
+            if (c0 != c_first) cf_load_vec16(q, q_p, c0, sd.q_ld, row_ok);
+            if (aligned) {
+              // the warp's 32 rows belong to one sample: transpose 8 columns at a time through the warp's tile,
+              // lane (c, q) adds rows 8q..8q+7 of column c, two shuffles finish; one writer per (quarter, column)
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) cf_sts32(tile_u + (uint32_t)((j * CF_TILE_LD + lane) * 4), v[8 * h + j] * q[8 * h + j]);
+                __syncwarp();
+                const uint32_t tp = tile_u + (uint32_t)(((lane & 7) * CF_TILE_LD + (lane >> 3) * 8) * 4);
+                const float4 a = cf_lds128(tp), c = cf_lds128(tp + 16);
+                float sum = ((a.x + a.y) + (a.z + a.w)) + ((c.x + c.y) + (c.z + c.w));
+                sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+                sum += __shfl_xor_sync(0xffffffffu, sum, 16);
+                if (lane < 8) cf_sts32(rs_u + (uint32_t)((qw * 128 + c0 + 8 * h + lane) * 4), sum);
+                __syncwarp();
+              }
+            } else {
+              for (int gg = g_lo; gg <= g_hi; ++gg) {           // segmented over the samples under this warp's rows
+                float m[CF_CW];
+#pragma unroll
+                for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[j] * q[j] : 0.f;
+                const float tot = cf_colsum16(m, lane);
+                if (lane < 16 && c0 + lane < N) atomicAdd(&rs_acc[gg * 128 + c0 + lane], tot);
+              }
+            }
+          }
+          if (mode == 1) {                           // loss statistics of the row: squared error and target norm
+            float sc[CF_CW], tg[CF_CW], x[CF_CW];
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) { sc[j] = sc0[j]; tg[j] = tg0[j]; }
+            if (c0 != c_first) load_sc_tg(sc, tg, c0);
+            block_pre(x, v, sc, c0);
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) {
+              const float d = x[j] - tg[j];
+              e_row = fmaf(d, d, e_row);
+              n_row = fmaf(tg[j], tg[j], n_row);
+            }
+          }
+        }
+      }
+      // ---- cross-warp leftovers of the step ----
       if (mode != 0) {
         if (mode == 1) {
           if (row_ok) st_h1 += e_row * inv_nj;
@@ -504,7 +532,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp_u == CF_EPI_WARPS)
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2u * CF_ACC_COLS) : "memory");
 }
 
 // ---- host ---------------------------------------------------------------------------------------------
@@ -552,12 +580,12 @@ void chain_fused_build_steps(ChainSteps* steps, const ChainNetDev& net) {
     if (l > 0) {
       const ChainLayerDev& below = net.layer[l - 1];
       if (below.act) { st.sc_off = below.sg_off; st.sc_ld = below.ld_out; }
-      st.out_off = below.q_off; st.out_ld = below.ld_out; st.outT_off = below.qt_off;
+      st.out_off = below.q_off; st.out_ld = below.ld_out;
     } else {
       st.mode = 1;
-      st.out_off = net.r0_off; st.out_ld = net.ld_in; st.outT_off = net.r0t_off;
+      st.out_off = net.r0_off; st.out_ld = net.ld_in;
     }
-    if (ly.lands_skip >= 0) { st.add_off = net.layer[ly.lands_skip].qt_off; st.add_first = 1; }   // transposed Q of the skip layer
+    if (ly.lands_skip >= 0) { st.add_off = net.layer[ly.lands_skip].q_off; st.add_ld = net.layer[ly.lands_skip].ld_out; st.add_first = 1; }   // Q of the skip layer
     steps->st[t] = st;
   }
   steps->n_fwd = t;
@@ -570,14 +598,15 @@ void chain_fused_build_steps(ChainSteps* steps, const ChainNetDev& net) {
     if (ly.act) {
       st.mode = 2;
       st.sc_off = ly.sg_off; st.sc_ld = ly.ld_out;
-      st.q_off = ly.qt_off;                                     // transposed Q_l
+      st.q_off = ly.q_off; st.q_ld = ly.ld_out;                 // Q_l
       st.rs_off = ly.rs_off; st.rs_ld = ly.ld_out;
     }
     if (l < L - 1) {
-      st.out_off = ly.dr_off; st.out_ld = ly.ld_out; st.outT_off = ly.drt_off;
+      st.out_off = ly.dr_off; st.out_ld = ly.ld_out;
       if (ly.skip_from >= 0) {
         const int j = ly.skip_from;
-        st.add_off = j == 0 ? net.r0t_off : net.layer[j - 1].drt_off;      // transposed dR_j
+        st.add_off = j == 0 ? net.r0_off : net.layer[j - 1].dr_off;        // dR_j
+        st.add_ld = j == 0 ? net.ld_in : net.layer[j - 1].ld_out;
       }
     } else {
       st.write_x = 0;

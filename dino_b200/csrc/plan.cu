@@ -257,34 +257,11 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
       if (lp.skip_from >= 0) c.has_skip = 1;
     }
     p->chain_fused = chain_fused_supported(c);
-    if (p->chain_fused) {
-      c.ldT = r4(Ms);
-      // the fused kernel moves whole 16-column blocks: the transposed arrays carry (zero) columns up to the next multiple of 16
-      auto r16 = [](int n) { return (long long)((n + 15) & ~15); };
-      c.r0t_off = take(r16(p->d_in) * c.ldT);
-      for (int l = 0; l < p->L; ++l) {
-        LayerPlan& lp = p->layers[l];
-        lp.qt_off = take(r16(lp.n_out) * c.ldT);
-        lp.drt_off = l < p->L - 1 ? take(r16(lp.n_out) * c.ldT) : -1;
-        c.layer[l].qt_off = lp.qt_off; c.layer[l].drt_off = lp.drt_off;
-      }
-      chain_fused_build_steps(&p->chain_steps, c);
-    }
+    if (p->chain_fused) chain_fused_build_steps(&p->chain_steps, c);
   }
   p->tc_wgrad = false;
-  p->ldT = p->chain_fused ? p->chain.ldT : 0;
-  p->r0t_off = p->chain_fused ? p->chain.r0t_off : -1;
-  if (!p->chain_fused && p->precision == DINO_PREC_TF32 &&
-      (p->jac_mode == DINO_JAC_FULL || p->jac_mode == DINO_JAC_OUT_REDUCED)) {
-    p->tc_wgrad = true;
-    p->ldT = r4(Ms);
-    p->r0t_off = take((long long)p->d_in * p->ldT);
-    for (int l = 0; l < p->L; ++l) {
-      LayerPlan& lp = p->layers[l];
-      lp.qt_off = take((long long)lp.n_out * p->ldT);
-      lp.drt_off = l < p->L - 1 ? take((long long)lp.n_out * p->ldT) : -1;
-    }
-  }
+  p->ldT = 0;
+  p->r0t_off = -1;
   p->ws_floats = off;
   if (p->chain_fused && getenv("DINO_B200_NO_SIDE_STREAM") == nullptr) {
     DINO_CUDA(cudaSetDevice(device));
@@ -484,18 +461,13 @@ static int push_chain_wgrads(DinoPlan* p, int B, float* grad, const TopQ& top, G
     const LayerPlan& lp = p->layers[l];
     if (!lp.trainable) continue;
     GemmOp op = gemm_op_zero();
-    if (p->chain_fused || p->tc_wgrad) {
-      // dW_l += dRT_l QT_l^T : both factors transposed -> K-major tensor-core contraction
-      op.A = l == 0 ? ws + p->r0t_off : ws + p->layers[l - 1].drt_off;
-      op.a_sm = p->ldT; op.a_sk = 1;
-      op.B = ws + lp.qt_off; op.b_sk = 1; op.b_sn = p->ldT;
-    } else {
-      op.A = l == 0 ? ws + p->off_r0 : ws + p->layers[l - 1].dr_off;
-      op.a_sm = 1; op.a_sk = l == 0 ? p->ld_in : p->layers[l - 1].ld_out;
-      if (l == L - 1) { op.B = top.ptr; op.b_sk = top.ld; op.b_kmod = top.mod; }
-      else { op.B = ws + lp.q_off; op.b_sk = lp.ld_out; }
-      op.b_sn = 1;
-    }
+    // dW_l += dR_l^T Q_l with both factors row-major [rows, n]: MN-major operands for the tensor-core engine,
+    // plain strides for the SIMT engine
+    op.A = l == 0 ? ws + p->off_r0 : ws + p->layers[l - 1].dr_off;
+    op.a_sm = 1; op.a_sk = l == 0 ? p->ld_in : p->layers[l - 1].ld_out;
+    if (l == L - 1) { op.B = top.ptr; op.b_sk = top.ld; op.b_kmod = top.mod; }
+    else { op.B = ws + lp.q_off; op.b_sk = lp.ld_out; }
+    op.b_sn = 1;
     op.M = lp.n_in; op.N = lp.n_out; op.K = M;
     op.C = grad + lp.koff; op.ldc = lp.n_out; op.atomic_c = 1;
     if (push_wgrad(p, wg, op, st)) return 1;
@@ -564,7 +536,7 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
     const float* q; long long ldq; int qmod;
     if (l == L - 1) { q = top.ptr; ldq = top.ld; qmod = top.mod; }
     else { q = ws + lp.q_off; ldq = lp.ld_out; qmod = 0; }
-    if (lp.trainable && !p->tc_wgrad) {     // dW_l += dR_l^T Q_l   (reduction over all B*s chain rows, split-K)
+    if (lp.trainable) {     // dW_l += dR_l^T Q_l   (reduction over all B*s chain rows, split-K)
       GemmOp op = gemm_op_zero();
       op.A = dr_ptr(l); op.a_sm = 1; op.a_sk = dr_ld(l);
       op.B = q; op.b_sk = ldq; op.b_sn = 1; op.b_kmod = qmod;
@@ -733,18 +705,6 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
     if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
     if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st)) return 1;
     if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, wg, st)) return 1;
-    if (p->tc_wgrad) {
-      // transposes of every chain state, then all chain weight gradients in one tensor-core launch
-      float* ws = p->ws;
-      const int M = B * p->s;
-      DINO_LAUNCH(launch_transpose(ws + p->off_r0, p->ld_in, ws + p->r0t_off, p->ldT, M, p->d_in, st));
-      for (int l = 0; l < p->L; ++l) {
-        const LayerPlan& lp = p->layers[l];
-        DINO_LAUNCH(launch_transpose(ws + lp.q_off, lp.ld_out, ws + lp.qt_off, p->ldT, M, lp.n_out, st));
-        if (l < p->L - 1) DINO_LAUNCH(launch_transpose(ws + lp.dr_off, lp.ld_out, ws + lp.drt_off, p->ldT, M, lp.n_out, st));
-      }
-      if (push_chain_wgrads(p, B, grad, top, wg, st)) return 1;
-    }
   }
   if (run_mlp_backward(p, params, B, grad, wg, st)) return 1;
   return flush_wgrad(p, wg, st);
@@ -844,6 +804,29 @@ extern "C" int dino_gemm_nt_acc(int engine, const float* XT, int64_t ldx, const 
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (engine == DINO_PREC_TF32) {
     if (!wgrad_tc_supported(op)) return fail("dino_gemm_nt_acc: operands do not meet the tensor-core weight-gradient rules");
+    DINO_LAUNCH(launch_wgrad_tc(g, sms, S(stream)));
+  } else {
+    DINO_LAUNCH(launch_gemm_simt(op, sms, S(stream)));
+  }
+  return 0;
+}
+
+extern "C" int dino_gemm_tn_acc(int engine, const float* X, int64_t ldx, const float* Y, int64_t ldy, float* C,
+                                int32_t rows, int32_t n_in, int32_t n_out, dino_stream_t stream) {
+  if (!X || !Y || !C) return fail("dino_gemm_tn_acc: null argument");
+  static GemmGroup g;
+  g.n = 1;
+  GemmOp& op = g.ops[0];
+  op = gemm_op_zero();
+  op.A = X; op.a_sm = 1; op.a_sk = ldx;
+  op.B = Y; op.b_sk = ldy; op.b_sn = 1;
+  op.M = n_in; op.N = n_out; op.K = rows;
+  op.C = C; op.ldc = n_out; op.atomic_c = 1;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (engine == DINO_PREC_TF32) {
+    if (!wgrad_tc_supported(op)) return fail("dino_gemm_tn_acc: operands do not meet the tensor-core weight-gradient rules");
     DINO_LAUNCH(launch_wgrad_tc(g, sms, S(stream)));
   } else {
     DINO_LAUNCH(launch_gemm_simt(op, sms, S(stream)));

@@ -27,6 +27,7 @@ struct WgOp {
   int z_start;              // first blockIdx.x of this op
   int chunks_per_cta;       // reduction chunks (of WG_BK rows) per CTA
   int n_tiles, splits;      // CTAs of this op: m_tiles * n_tiles * splits, split fastest
+  int mn;                   // 1: operands are the ROW-major chain states [rows, n] (MN-major UMMA operands), 0: transposed copies
 };
 struct WgGroup {
   int n;
@@ -49,6 +50,12 @@ __device__ __forceinline__ void wg_wait(uint64_t* bar, uint32_t parity) {
 }
 __device__ __forceinline__ uint64_t wg_desc(uint32_t saddr) {    // K-major, SWIZZLE_128B (as gemm_tc.cu)
   return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// MN-major TF32 operand tile as TMA (SWIZZLE_128B_ATOM_32B) lays it down: per 32-column group WG_BK reduction rows of
+// 128 bytes; canonical UMMA layout ((8,n),(4,k)):((1,LBO),(8,SBO)) in 16-byte units: LBO = group pitch, SBO = 4-row atom
+__device__ __forceinline__ uint64_t wg_desc_mn(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)((WG_BK * 128) >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) | (1ull << 46) | (1ull << 61);
 }
 
 __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_constant__ WgGroup g) {
@@ -96,10 +103,23 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
         for (int c = 0; c < nchunks; ++c) {
           const int st = c % WG_STAGES;
           wg_wait(empty_bar + st, ((c / WG_STAGES) & 1) ^ 1);
-          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(wg_u32(full_bar + st)),
-                       "r"((uint32_t)WG_STAGE_BYTES) : "memory");
           uint8_t* sx = smem + st * WG_STAGE_BYTES;
           const int k0 = (c_begin + c) * WG_BK;
+          if (op.mn) {
+            // row-major states: one box of 32 columns x WG_BK rows per column group that holds data
+            const int ga = (min(128, op.n_in - m0) + 31) >> 5, gb = (min(128, op.n_out - n0) + 31) >> 5;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(wg_u32(full_bar + st)),
+                         "r"((uint32_t)((ga + gb) * WG_BK * 128)) : "memory");
+            for (int gI = 0; gI < ga; ++gI)
+              asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                           ::"r"(wg_u32(sx + gI * WG_BK * 128)), "l"(mx), "r"(wg_u32(full_bar + st)), "r"(m0 + 32 * gI), "r"(k0) : "memory");
+            for (int gI = 0; gI < gb; ++gI)
+              asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                           ::"r"(wg_u32(sx + WG_OPER_BYTES + gI * WG_BK * 128)), "l"(my), "r"(wg_u32(full_bar + st)), "r"(n0 + 32 * gI), "r"(k0) : "memory");
+            continue;
+          }
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(wg_u32(full_bar + st)),
+                       "r"((uint32_t)WG_STAGE_BYTES) : "memory");
           asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                        ::"r"(wg_u32(sx)), "l"(mx), "r"(wg_u32(full_bar + st)), "r"(k0), "r"(m0) : "memory");
           asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -109,13 +129,16 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
     } else if (warp == 1) {
       if (lane == 0) {
         const uint32_t n16 = (uint32_t)((min(128, op.n_out - n0) + 15) & ~15);
-        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((n16 >> 3) << 17) | ((128u >> 4) << 24);
+        // (bits 15 / 16: A / B are MN-major when the operands are the row-major states)
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((n16 >> 3) << 17) | ((128u >> 4) << 24) |
+                               (op.mn ? ((1u << 15) | (1u << 16)) : 0u);
+        const uint64_t kstep = op.mn ? 64 : 2;      // descriptor start-address advance per 8 reduction rows (16-byte units)
         for (int c = 0; c < nchunks; ++c) {
           const int st = c % WG_STAGES;
           wg_wait(full_bar + st, (c / WG_STAGES) & 1);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t sx = wg_u32(smem + st * WG_STAGE_BYTES), sy = sx + WG_OPER_BYTES;
-          const uint64_t ad = wg_desc(sx), bd = wg_desc(sy);
+          const uint64_t ad = op.mn ? wg_desc_mn(sx) : wg_desc(sx), bd = op.mn ? wg_desc_mn(sy) : wg_desc(sy);
 #pragma unroll
           for (int k = 0; k < WG_BK / 8; ++k) {
             const uint32_t acc = (c > 0 || k > 0) ? 1u : 0u;
@@ -124,7 +147,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
                 ".reg .pred p;\n\t"
                 "setp.ne.b32 p, %4, 0;\n\t"
                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-                "}" ::"r"(tmem_base), "l"(ad + 2 * k), "l"(bd + 2 * k), "r"(idesc), "r"(acc) : "memory");
+                "}" ::"r"(tmem_base), "l"(ad + kstep * k), "l"(bd + kstep * k), "r"(idesc), "r"(acc) : "memory");
           }
           asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(wg_u32(empty_bar + st)) : "memory");
         }
@@ -193,12 +216,29 @@ static bool wg_map(CUtensorMap* m, const float* base, int n, int rows, long long
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// operand stored ROW-major [rows, n] with pitch ld floats: box = 32 columns x WG_BK reduction rows, 32-byte-atom swizzle
+static bool wg_map_mn(CUtensorMap* m, const float* base, int n, int rows, long long ld) {
+  PFN_wgEncode enc = wg_encoder();
+  if (!enc) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)n, (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)ld * sizeof(float)};
+  cuuint32_t box[2] = {32, (cuuint32_t)WG_BK};
+  cuuint32_t es[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, es,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // The ops passed here describe C[M,N] += A[M,K] * Bt[N,K]^T with BOTH operands K-major (a_sk == b_sk == 1):
 // A = XT (pitch a_sm), B = YT (pitch b_sn).
 bool wgrad_tc_supported(const GemmOp& op) {
-  if (!op.atomic_c || op.a_sk != 1 || op.b_sk != 1 || op.b_kmod > 0 || op.a_mod > 0) return false;
+  if (!op.atomic_c || op.b_kmod > 0 || op.a_mod > 0) return false;
   if (op.M < 1 || op.N < 1 || op.K < 1) return false;
-  if ((op.a_sm & 3) || (op.b_sn & 3)) return false;
+  const bool kmaj = op.a_sk == 1 && op.b_sk == 1;                      // transposed copies [n, rows]
+  const bool mnmaj = op.a_sm == 1 && op.b_sn == 1;                     // row-major states [rows, n], pitches a_sk / b_sk
+  if (!kmaj && !mnmaj) return false;
+  if (kmaj && ((op.a_sm & 3) || (op.b_sn & 3))) return false;
+  if (!kmaj && ((op.a_sk & 3) || (op.b_sk & 3))) return false;
   if ((reinterpret_cast<uintptr_t>(op.A) & 15) || (reinterpret_cast<uintptr_t>(op.B) & 15)) return false;
   return op.ldc == op.N;
 }
@@ -228,7 +268,10 @@ cudaError_t launch_wgrad_tc(const GemmGroup& gg, int num_sms, cudaStream_t st) {
     w.splits = (chunks + w.chunks_per_cta - 1) / w.chunks_per_cta;
     w.z_start = z;
     z += tiles * w.splits;
-    if (!wg_map(&g.mx[i], o.A, o.M, o.K, o.a_sm) || !wg_map(&g.my[i], o.B, o.N, o.K, o.b_sn)) return cudaErrorInvalidValue;
+    w.mn = (o.a_sk == 1 && o.b_sk == 1) ? 0 : 1;
+    if (w.mn) {
+      if (!wg_map_mn(&g.mx[i], o.A, o.M, o.K, o.a_sk) || !wg_map_mn(&g.my[i], o.B, o.N, o.K, o.b_sk)) return cudaErrorInvalidValue;
+    } else if (!wg_map(&g.mx[i], o.A, o.M, o.K, o.a_sm) || !wg_map(&g.my[i], o.B, o.N, o.K, o.b_sn)) return cudaErrorInvalidValue;
   }
   constexpr int SMEM = WG_STAGES * WG_STAGE_BYTES + 128 + 1024;
   static bool configured = false;

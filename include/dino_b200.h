@@ -183,6 +183,12 @@ int dino_gemm_nt(int engine, const float* d_A, int64_t lda, const float* d_Bt, i
 int dino_gemm_nt_acc(int engine, const float* d_XT, int64_t ldx, const float* d_YT, int64_t ldy, float* d_C,
                      int32_t rows, int32_t n_in, int32_t n_out, dino_stream_t stream);
 
+/* The same contraction with the factors given ROW-major, as the chain keeps them: C[n_in, n_out] += X[rows, n_in]^T
+ * Y[rows, n_out] (pitches ldx, ldy floats, multiples of 4).  The TF32 engine reads them as MN-major tensor-core
+ * operands (no transposed copies).  Same reference line as dino_gemm_nt_acc (trainingUtilities.py:135). */
+int dino_gemm_tn_acc(int engine, const float* d_X, int64_t ldx, const float* d_Y, int64_t ldy, float* d_C,
+                     int32_t rows, int32_t n_in, int32_t n_out, dino_stream_t stream);
+
 /* Measurement aid: time the dominant kernel of the step (the fused Jacobian-chain kernel) with CUDA events on the
  * launching stream.  enable = 1 starts (totals reset), enable = 0 stops; the running totals are returned.  Use with
  * eager steps only (events are not recorded inside a replayed graph).  No counterpart in the reference. */

@@ -28,7 +28,7 @@ print("step  " + "  ".join(f"{n:>9s}" for n in names) + "   (ns since first stam
 for s in range(17):
     print(f"{s:4d}  " + "  ".join(f"{int(v - t0):9d}" for v in t[s, :7]))
 
-print("epilogue detail (tid 0): pre_bar | it0: start, tmem_ld, rowsum | it1: start, tmem_ld, rowsum | loop_end   (ns since mma_done)")
+print("epilogue detail (tid 0): pre_bar | it0: start, tmem_ld, computed | it1: start, tmem_ld, computed | loop_end   (ns since mma_done)")
 for s in range(17):
     base = t[s, 4]
     e = t[32 + s]

@@ -69,6 +69,27 @@ def test_tf32_weight_gradient_contraction(cuda_device, rows, n_in, n_out):
         assert np.abs(got - want).max() < tol * np.sqrt(rows) * 4, (engine, np.abs(got - want).max())
 
 
+@pytest.mark.parametrize("rows,n_in,n_out", [(64, 32, 32), (240, 13, 8), (1000, 50, 50), (12800, 100, 50), (300, 128, 128),
+                                             (77, 5, 100), (520, 300, 200), (1000, 130, 257)])
+def test_tf32_weight_gradient_contraction_row_major(cuda_device, rows, n_in, n_out):
+    """C += X^T Y with the factors row-major (MN-major tensor-core operands) vs fp64, onto a non-zero C."""
+    lib = _lib.load()
+    rng = np.random.default_rng(rows + n_in + n_out + 1)
+    ldx, ldy = (n_in + 3) & ~3, (n_out + 7) & ~3
+    X = np.full((rows, ldx), 1e30, np.float32); X[:, :n_in] = rng.normal(size=(rows, n_in))
+    Y = np.full((rows, ldy), 1e30, np.float32); Y[:, :n_out] = rng.normal(size=(rows, n_out))
+    C0 = rng.normal(size=(n_in, n_out)).astype(np.float32)
+    want = C0 + X[:, :n_in].astype(np.float64).T @ Y[:, :n_out].astype(np.float64)
+    for engine, tol in ((_lib.PREC_FP32, 1e-5), (_lib.PREC_TF32, 2e-3)):
+        dX, dY, dC = torch.from_numpy(X).cuda(), torch.from_numpy(Y).cuda(), torch.from_numpy(C0.copy()).cuda()
+        _lib.check(lib.dino_gemm_tn_acc(engine, C.c_void_p(dX.data_ptr()), ldx, C.c_void_p(dY.data_ptr()), ldy,
+                                        C.c_void_p(dC.data_ptr()), rows, n_in, n_out, _stream()), "dino_gemm_tn_acc")
+        torch.cuda.synchronize()
+        got = dC.cpu().numpy()
+        assert np.isfinite(got).all()
+        assert np.abs(got - want).max() < tol * np.sqrt(rows) * 4, (engine, np.abs(got - want).max())
+
+
 def _compile(model):
     model.compile(optimizer=Adam(1e-3), loss=[normalized_mse, normalized_mse_matrix], loss_weights=[1.0, 1.0],
                   metrics=[l2_accuracy, f_accuracy_matrix])
