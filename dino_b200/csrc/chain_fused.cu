@@ -65,6 +65,10 @@ __device__ __forceinline__ void cf_tma_load(void* dst, const CUtensorMap* map, i
       "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(cf_smem_u32(dst)), "l"(map), "r"(cf_smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
 }
+__device__ __forceinline__ void cf_tma_store(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ void cf_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(cf_smem_u32(bar)) : "memory");
 }
@@ -171,6 +175,12 @@ __device__ __forceinline__ void cf_store_vec16(float* row, int c0, int len, cons
     if (c0 + j < len) *reinterpret_cast<float4*>(row + c0 + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
 }
 
+// the result of a step goes to global memory (row-major) when somebody reads it later: the weight-gradient launch
+// after a training step, a residual connection, or the caller (the Jacobian itself when no loss is asked for)
+__device__ __forceinline__ bool cf_out_needed(const ChainStep& sd, const ChainNetDev& net, int do_loss, int do_backward) {
+  return sd.out_off >= 0 && (do_backward || net.has_skip || (sd.mode == 1 && !do_loss));
+}
+
 __global__ void __launch_bounds__(CF_THREADS, 1)
 chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ ChainNetDev net,
                    const __grid_constant__ ChainSteps steps, float* __restrict__ ws, const float* __restrict__ jt,
@@ -201,6 +211,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   const int dbg = 0;
 #endif
   const int n_steps = do_backward ? steps.n_all : steps.n_fwd;
+  // residual networks re-read chain states inside the kernel right after they are produced: those keep per-thread stores
+  const bool tma_out = net.has_skip == 0;
 
   // ---- set-up --------------------------------------------------------------------------------------
   for (int e = tid; e < CF_X_BYTES / 16; e += CF_THREADS) reinterpret_cast<float4*>(X)[e] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -235,6 +247,19 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       load_w(0);
       const uint64_t xd = cf_desc(cf_smem_u32(X));
       const uint64_t wd0 = cf_desc(cf_smem_u32(Wb[0])), wd1 = cf_desc(cf_smem_u32(Wb[1]));
+      const uint32_t x_u = cf_smem_u32(X);
+      // Row-major copy of step t's result (it sits in X as the next operand): TMA stores straight from the tile, whole
+      // 128-byte lines, no thread touches it.  One box per 32-column chunk (and per sample when rows are warp-aligned).
+      auto store_out = [&](int t) {
+        const int nch = (steps.st[t].N + 31) >> 5;
+        for (int c = 0; c < nch; ++c) {
+          if (srow == s) cf_tma_store(&maps.out[t], x_u + (uint32_t)(c * CF_CHUNK_BYTES), c * 32, (int)row0);
+          else
+            for (int gI = 0; gI < nsamp; ++gI)
+              cf_tma_store(&maps.out[t], x_u + (uint32_t)(c * CF_CHUNK_BYTES + gI * srow * 128), c * 32, (int)(row0 + (long long)gI * s));
+        }
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      };
 #pragma unroll 1
       for (int t = 0; t < n_steps; ++t) {
         const int buf = t & 1;
@@ -245,6 +270,9 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         const int ksteps = (K + 7) >> 3;
         cf_mbar_wait(x_ready, t & 1);                       // operand X written by the epilogue threads
         CF_STAMP(t, 0);
+        if (tma_out && t > 0 && cf_out_needed(steps.st[t - 1], net, do_loss, do_backward)) store_out(t - 1);
+        // the backward steps re-read the forward chain states with ordinary loads: all of them must have landed
+        if (tma_out && t == steps.n_fwd) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
         cf_mbar_wait(w_full + buf, (t >> 1) & 1);           // weight tile landed
         CF_STAMP(t, 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -255,11 +283,18 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
           const uint64_t o16 = (uint64_t)(((k >> 2) * CF_CHUNK_BYTES + (k & 3) * 32) >> 4);
           cf_mma(tmem_base + (uint32_t)(buf * CF_ACC_COLS), xd + o16, bd + o16, idesc, k > 0 ? 1u : 0u);
         }
+        // X is rewritten once this contraction is reported done: the stores must have read it by then
+        if (tma_out) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         cf_commit(mma_done);
         CF_STAMP(t, 2);
         if (t + 1 < n_steps) load_w(t + 1);                 // the other buffer was released by step t-1
         CF_STAMP(t, 3);
       }
+      if (tma_out && cf_out_needed(steps.st[n_steps - 1], net, do_loss, do_backward)) {
+        cf_mbar_wait(x_ready, n_steps & 1);
+        store_out(n_steps - 1);
+      }
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // shared memory must outlive the stores
     }
     __syncwarp();
   } else {
@@ -322,18 +357,19 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       const ChainStep& sd = steps.st[t];
       const int N = sd.N;
       int mode = sd.mode;
-      bool write_x = sd.write_x != 0 && !(dbg & 2);
+      bool next_reads_x = sd.write_x != 0;          // the result is the next contraction's operand
       if (mode == 1) {
         if (!do_loss) mode = 0;                     // Jacobian only: plain row-major output
-        if (!do_backward) write_x = false;
+        if (!do_backward) next_reads_x = false;
       }
-      // the result goes to global memory (row-major, each thread 64 contiguous bytes of its row) when somebody reads it
-      // later: the weight-gradient launch after a training step, a residual connection, or the caller (the Jacobian)
-      const bool out_on = sd.out_off >= 0 && (do_backward || net.has_skip || (sd.mode == 1 && !do_loss)) && !(dbg & 1);
+      const bool out_on = cf_out_needed(sd, net, do_loss, do_backward) && !(dbg & 1);
+      // with TMA stores the global copy is taken from X, so X is written whenever the copy is needed
+      const bool write_x = (next_reads_x || (tma_out && out_on)) && !(dbg & 2);
+      const bool thread_out = out_on && !tma_out;
       const bool add_on = sd.add_off >= 0;
       const bool add_first = sd.add_first != 0;
       const bool sc_on = sd.sc_off >= 0 && !(dbg & 64);
-      const bool do_round = (write_x || do_backward) && !(dbg & 8);  // only what feeds a later TF32 contraction is rounded
+      const bool do_round = (next_reads_x || do_backward) && !(dbg & 8);  // only what feeds a later TF32 contraction is rounded
       float* const out_p = ws + sd.out_off + grow * sd.out_ld;
       const float* const add_p = ws + sd.add_off + grow * sd.add_ld;   // residual rows
       const float* const q_p = ws + sd.q_off + grow * sd.q_ld;         // Q_l rows (row-sum operand)
@@ -399,7 +435,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
       // ---- phase A: accumulator -> next operand X (and its row-major copy in global memory), hand X over ----
-      if (write_x || out_on) {
+      if (write_x || thread_out) {
 #pragma unroll 1
         for (int c0 = c_first; c0 < N; c0 += STRIDE) {
           float v[CF_CW], sc[CF_CW], tg[CF_CW], x[CF_CW];
@@ -416,11 +452,11 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             for (int j = 0; j < CF_CW; j += 4)
               cf_sts128(xb + (uint32_t)(((j0 + (j >> 2)) ^ xsw) << 4), x[j], x[j + 1], x[j + 2], x[j + 3]);
           }
-          if (out_on && row_ok) cf_store_vec16(out_p, c0, sd.out_ld, x);     // padded columns are exact zeros
+          if (thread_out && row_ok) cf_store_vec16(out_p, c0, sd.out_ld, x);     // padded columns are exact zeros
         }
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      if (t + 1 < n_steps) {
+      if (t + 1 < n_steps || (tma_out && out_on)) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) cf_mbar_arrive(x_ready);
@@ -540,8 +576,8 @@ typedef CUresult (*PFN_cfEncode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, 
                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const float* ws, const long long* wp_off,
-                             const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp) {
+bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const ChainSteps& steps, long long max_rows, const float* ws,
+                             const long long* wp_off, const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp) {
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult qres;
   if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
@@ -557,6 +593,21 @@ bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const floa
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   };
+  // row-major destinations of the step results [max_rows, pitch]: box = 32 columns x the rows of one sample (or of the
+  // whole tile when the samples are packed back to back); rows / columns beyond the array are clipped by the hardware
+  const cuuint32_t box_rows = (cuuint32_t)(net.srow == net.s ? (net.G * net.s < CF_ROWS ? net.G * net.s : CF_ROWS) : net.s);
+  for (int t = 0; t < steps.n_all; ++t) {
+    const ChainStep& st = steps.st[t];
+    if (st.out_off < 0) continue;
+    cuuint64_t gdim[2] = {(cuuint64_t)st.out_ld, (cuuint64_t)max_rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)st.out_ld * sizeof(float)};
+    cuuint32_t box[2] = {32, box_rows};
+    cuuint32_t es[2] = {1, 1};
+    if (enc(&maps->out[t], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ws + st.out_off), gdim, gstr, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return false;
+  }
   for (int l = 0; l < net.L; ++l) {
     const ChainLayerDev& ly = net.layer[l];
     // forward: B operand stored [N = n_in][K = n_out] = padded W_l ; backward: [N = n_out][K = n_in] = padded W_l^T

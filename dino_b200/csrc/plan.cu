@@ -305,7 +305,7 @@ extern "C" int dino_plan_bind_workspace(DinoPlan* plan, void* d_ws, size_t bytes
       wp[l] = plan->layers[l].wp_off; lwp[l] = plan->layers[l].ld_wp;
       wtp[l] = plan->layers[l].wtp_off; lwtp[l] = plan->layers[l].ld_wtp;
     }
-    if (!chain_fused_encode_maps(&plan->chain_maps, plan->chain, plan->ws, wp, lwp, wtp, lwtp))
+    if (!chain_fused_encode_maps(&plan->chain_maps, plan->chain, plan->chain_steps, (long long)plan->max_batch * plan->s, plan->ws, wp, lwp, wtp, lwtp))
       return fail("dino_plan_bind_workspace: cuTensorMapEncodeTiled failed for the fused chain kernel");
   }
   if (plan->off_ident >= 0)
