@@ -34,7 +34,7 @@ constexpr int CF_X_BYTES = (CF_MAXW / 32) * CF_CHUNK_BYTES;                     
 constexpr int CF_PARTS = 2;                                                        // threads per chain row (column split)
 constexpr int CF_EPI = 128 * CF_PARTS;                                             // 8 epilogue warps: 2 per TMEM lane quarter
 constexpr int CF_EPI_WARPS = CF_EPI / 32;
-constexpr int CF_THREADS = CF_EPI + 32;                                            // + 1 control warp
+constexpr int CF_THREADS = CF_EPI + 64;                                            // + control warp (weight TMA, MMA issue) + store warp (TMA stores of the results)
 constexpr int CF_CW = 16;                                                          // columns per TMEM load / work item
 constexpr int CF_ACC_COLS = 128;                                                   // TMEM columns per accumulator (two of them: steps alternate)
 constexpr int CF_TILE_LD = 36;                                                     // floats per column of a warp's row-sum transposition tile
@@ -177,8 +177,8 @@ __device__ __forceinline__ void cf_store_vec16(float* row, int c0, int len, cons
 
 // the result of a step goes to global memory (row-major) when somebody reads it later: the weight-gradient launch
 // after a training step, a residual connection, or the caller (the Jacobian itself when no loss is asked for)
-__device__ __forceinline__ bool cf_out_needed(const ChainStep& sd, const ChainNetDev& net, int do_loss, int do_backward) {
-  return sd.out_off >= 0 && (do_backward || net.has_skip || (sd.mode == 1 && !do_loss));
+__device__ __forceinline__ bool cf_out_needed(const ChainStep& sd, const ChainNetDev& net, int do_loss, int do_backward, int dbg) {
+  return sd.out_off >= 0 && (do_backward || net.has_skip || (sd.mode == 1 && !do_loss)) && !(dbg & 1);
 }
 
 __global__ void __launch_bounds__(CF_THREADS, 1)
@@ -193,8 +193,10 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + 3 * CF_X_BYTES);     // [2]
   uint64_t* mma_done = w_full + 2;
   uint64_t* x_ready = w_full + 3;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 4);
-  float* rs_acc = reinterpret_cast<float*>(w_full + 6);                       // [16][128] row sums: per sample (packed rows) or per warp quarter
+  uint64_t* x_free = w_full + 4;                                             // the stores of the previous result have read X
+  uint64_t* fwd_stored = w_full + 5;                                         // every forward chain state has landed in global memory
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 6);
+  float* rs_acc = reinterpret_cast<float*>(w_full + 8);                       // [16][128] row sums: per sample (packed rows) or per warp quarter
   float* ex_s = rs_acc + 16 * 128;                                            // [CF_PARTS][128][2] loss partials of the row parts
   float* tiles = ex_s + CF_PARTS * 128 * 2;                                   // [CF_EPI_WARPS][8][CF_TILE_LD] row-sum transposition tiles
 
@@ -220,6 +222,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   if (warp == CF_EPI_WARPS) {
     if (lane == 0) {
       cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(x_ready, CF_EPI_WARPS);
+      cf_mbar_init(x_free, 1); cf_mbar_init(fwd_stored, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -247,19 +250,6 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       load_w(0);
       const uint64_t xd = cf_desc(cf_smem_u32(X));
       const uint64_t wd0 = cf_desc(cf_smem_u32(Wb[0])), wd1 = cf_desc(cf_smem_u32(Wb[1]));
-      const uint32_t x_u = cf_smem_u32(X);
-      // Row-major copy of step t's result (it sits in X as the next operand): TMA stores straight from the tile, whole
-      // 128-byte lines, no thread touches it.  One box per 32-column chunk (and per sample when rows are warp-aligned).
-      auto store_out = [&](int t) {
-        const int nch = (steps.st[t].N + 31) >> 5;
-        for (int c = 0; c < nch; ++c) {
-          if (srow == s) cf_tma_store(&maps.out[t], x_u + (uint32_t)(c * CF_CHUNK_BYTES), c * 32, (int)row0);
-          else
-            for (int gI = 0; gI < nsamp; ++gI)
-              cf_tma_store(&maps.out[t], x_u + (uint32_t)(c * CF_CHUNK_BYTES + gI * srow * 128), c * 32, (int)(row0 + (long long)gI * s));
-        }
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      };
 #pragma unroll 1
       for (int t = 0; t < n_steps; ++t) {
         const int buf = t & 1;
@@ -270,9 +260,6 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         const int ksteps = (K + 7) >> 3;
         cf_mbar_wait(x_ready, t & 1);                       // operand X written by the epilogue threads
         CF_STAMP(t, 0);
-        if (tma_out && t > 0 && cf_out_needed(steps.st[t - 1], net, do_loss, do_backward)) store_out(t - 1);
-        // the backward steps re-read the forward chain states with ordinary loads: all of them must have landed
-        if (tma_out && t == steps.n_fwd) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
         cf_mbar_wait(w_full + buf, (t >> 1) & 1);           // weight tile landed
         CF_STAMP(t, 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -283,16 +270,44 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
           const uint64_t o16 = (uint64_t)(((k >> 2) * CF_CHUNK_BYTES + (k & 3) * 32) >> 4);
           cf_mma(tmem_base + (uint32_t)(buf * CF_ACC_COLS), xd + o16, bd + o16, idesc, k > 0 ? 1u : 0u);
         }
-        // X is rewritten once this contraction is reported done: the stores must have read it by then
-        if (tma_out) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         cf_commit(mma_done);
         CF_STAMP(t, 2);
         if (t + 1 < n_steps) load_w(t + 1);                 // the other buffer was released by step t-1
         CF_STAMP(t, 3);
       }
-      if (tma_out && cf_out_needed(steps.st[n_steps - 1], net, do_loss, do_backward)) {
-        cf_mbar_wait(x_ready, n_steps & 1);
-        store_out(n_steps - 1);
+    }
+    __syncwarp();
+  } else if (warp_u == CF_EPI_WARPS + 1) {
+    // ===== store warp: row-major copy of every step result that somebody reads later =====
+    // The result of step t sits in X as the operand of step t+1: one elected lane TMA-stores it from there (whole
+    // 128-byte lines, no thread touches the data), one box per 32-column chunk (and per sample when rows are warp-aligned).
+    if (tma_out && cf_elect_one()) {
+      const uint32_t x_u = cf_smem_u32(X);
+      cf_mbar_wait(x_ready, 0);                             // (a parity wait only works on the phase in flight: follow every phase)
+#pragma unroll 1
+      for (int t = 1; t <= n_steps; ++t) {
+        const bool last = t == n_steps;
+        const bool need = cf_out_needed(steps.st[t - 1], net, do_loss, do_backward, dbg);
+        if (last && !need) break;
+        cf_mbar_wait(x_ready, t & 1);                       // X holds the result of step t-1
+        if (need) {
+          const int nch = (steps.st[t - 1].N + 31) >> 5;
+          for (int c = 0; c < nch; ++c) {
+            if (srow == s) cf_tma_store(&maps.out[t - 1], x_u + (uint32_t)(c * CF_CHUNK_BYTES), c * 32, (int)row0);
+            else
+              for (int gI = 0; gI < nsamp; ++gI)
+                cf_tma_store(&maps.out[t - 1], x_u + (uint32_t)(c * CF_CHUNK_BYTES + gI * srow * 128), c * 32, (int)(row0 + (long long)gI * s));
+          }
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        if (do_backward && t == steps.n_fwd) {
+          // the backward steps re-read the forward chain states with ordinary loads: all of them must have landed
+          asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+          cf_mbar_arrive(fwd_stored);
+        } else if (need) {
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
+        if (!last) cf_mbar_arrive(x_free);                  // X may be rewritten
       }
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // shared memory must outlive the stores
     }
@@ -362,7 +377,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         if (!do_loss) mode = 0;                     // Jacobian only: plain row-major output
         if (!do_backward) next_reads_x = false;
       }
-      const bool out_on = cf_out_needed(sd, net, do_loss, do_backward) && !(dbg & 1);
+      const bool out_on = cf_out_needed(sd, net, do_loss, do_backward, dbg);
       // with TMA stores the global copy is taken from X, so X is written whenever the copy is needed
       const bool write_x = (next_reads_x || (tma_out && out_on)) && !(dbg & 2);
       const bool thread_out = out_on && !tma_out;
@@ -422,6 +437,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         if (mode == 1) cf_load16(tg, prow, c0, N, row_ok, vec_ok);
       };
 
+      if (tma_out && do_backward && t == steps.n_fwd) cf_mbar_wait(fwd_stored, 0);   // Q_l are read from global memory from here on
       // ---- while the MMA runs: request the first block's operands ----
       float sc0[CF_CW], tg0[CF_CW], q0[CF_CW];
 #pragma unroll
@@ -433,6 +449,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       cf_mbar_wait(mma_done, t & 1);
       if (tid == 0) CF_STAMP(t, 4);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (tma_out && t > 0) cf_mbar_wait(x_free, (t - 1) & 1);     // the copy of the previous result has left X
 
       // ---- phase A: accumulator -> next operand X (and its row-major copy in global memory), hand X over ----
       if (write_x || thread_out) {
