@@ -196,8 +196,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   uint64_t* x_free = w_full + 4;                                             // the stores of the previous result have read X
   uint64_t* fwd_stored = w_full + 5;                                         // every forward chain state has landed in global memory
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 6);
-  float* rs_acc = reinterpret_cast<float*>(w_full + 8);                       // [16][128] row sums: per sample (packed rows) or per warp quarter
-  float* ex_s = rs_acc + 16 * 128;                                            // [CF_PARTS][128][2] loss partials of the row parts
+  float* ex_s = reinterpret_cast<float*>(w_full + 8);                                            // [CF_PARTS][128][2] loss partials of the row parts
   float* tiles = ex_s + CF_PARTS * 128 * 2;                                   // [CF_EPI_WARPS][8][CF_TILE_LD] row-sum transposition tiles
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -217,8 +216,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   const bool tma_out = net.has_skip == 0;
 
   // ---- set-up --------------------------------------------------------------------------------------
+  if (tid == 0) CF_STAMP(0, 7);
   for (int e = tid; e < CF_X_BYTES / 16; e += CF_THREADS) reinterpret_cast<float4*>(X)[e] = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int e = tid; e < 16 * 128; e += CF_THREADS) rs_acc[e] = 0.f;
   if (warp == CF_EPI_WARPS) {
     if (lane == 0) {
       cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(x_ready, CF_EPI_WARPS);
@@ -234,6 +233,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
+  if (tid == 0) CF_STAMP(1, 7);
 
   const int warp_u = __shfl_sync(0xffffffffu, warp, 0);   // tells the compiler that everything derived from it is warp-uniform
   if (warp_u == CF_EPI_WARPS) {
@@ -265,10 +265,13 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         // descriptor start addresses advance by 32 bytes per 8-wide K step, 16 KB per 32-column chunk (no carry out
         // of the 14-bit address field: the tiles sit below 256 KB)
+        const uint32_t dcol = tmem_base + (uint32_t)(buf * CF_ACC_COLS);
 #pragma unroll 1
-        for (int k = 0; k < ksteps; ++k) {
-          const uint64_t o16 = (uint64_t)(((k >> 2) * CF_CHUNK_BYTES + (k & 3) * 32) >> 4);
-          cf_mma(tmem_base + (uint32_t)(buf * CF_ACC_COLS), xd + o16, bd + o16, idesc, k > 0 ? 1u : 0u);
+        for (int c = 0; c * 4 < ksteps; ++c) {              // one 32-column chunk of X / the weight tile = four K steps
+          const uint64_t oc = (uint64_t)(c * (CF_CHUNK_BYTES >> 4));
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (c * 4 + j < ksteps) cf_mma(dcol, xd + oc + 2 * j, bd + oc + 2 * j, idesc, (c | j) ? 1u : 0u);
         }
         cf_commit(mma_done);
         CF_STAMP(t, 2);
@@ -283,23 +286,30 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     // 128-byte lines, no thread touches the data), one box per 32-column chunk (and per sample when rows are warp-aligned).
     if (tma_out && cf_elect_one()) {
       const uint32_t x_u = cf_smem_u32(X);
-      cf_mbar_wait(x_ready, 0);                             // (a parity wait only works on the phase in flight: follow every phase)
+      auto store_x = [&](const CUtensorMap* map, int N) {
+        const int nch = (N + 31) >> 5;
+        for (int c = 0; c < nch; ++c) {
+          if (srow == s) cf_tma_store(map, x_u + (uint32_t)(c * CF_CHUNK_BYTES), c * 32, (int)row0);
+          else
+            for (int gI = 0; gI < nsamp; ++gI)
+              cf_tma_store(map, x_u + (uint32_t)(c * CF_CHUNK_BYTES + gI * srow * 128), c * 32, (int)(row0 + (long long)gI * s));
+        }
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      };
+      // X version 0 = the top chain state Q_{L-1} (operand of the top layer's weight gradient)
+      cf_mbar_wait(x_ready, 0);
+      if (net.top_materialised && do_backward) {
+        store_x(&maps.top, net.layer[L - 1].n_out);
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      }
+      cf_mbar_arrive(x_free);
 #pragma unroll 1
       for (int t = 1; t <= n_steps; ++t) {
         const bool last = t == n_steps;
         const bool need = cf_out_needed(steps.st[t - 1], net, do_loss, do_backward, dbg);
         if (last && !need) break;
         cf_mbar_wait(x_ready, t & 1);                       // X holds the result of step t-1
-        if (need) {
-          const int nch = (steps.st[t - 1].N + 31) >> 5;
-          for (int c = 0; c < nch; ++c) {
-            if (srow == s) cf_tma_store(&maps.out[t - 1], x_u + (uint32_t)(c * CF_CHUNK_BYTES), c * 32, (int)row0);
-            else
-              for (int gI = 0; gI < nsamp; ++gI)
-                cf_tma_store(&maps.out[t - 1], x_u + (uint32_t)(c * CF_CHUNK_BYTES + gI * srow * 128), c * 32, (int)(row0 + (long long)gI * s));
-          }
-          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        }
+        if (need) store_x(&maps.out[t - 1], steps.st[t - 1].N);
         if (do_backward && t == steps.n_fwd) {
           // the backward steps re-read the forward chain states with ordinary loads: all of them must have landed
           asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
@@ -330,11 +340,9 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16);
     const int g_lo = (32 * qw) / srow, g_hi = min((32 * qw + 31) / srow, nsamp - 1);   // samples under this warp's rows
     const bool aligned = (srow & 31) == 0;                  // a warp never straddles two samples
-    const int nq = srow >> 5;                               // warp quarters per sample (aligned layout)
     const uint32_t xrow = cf_smem_u32(X) + (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
     const int xsw = r & 7;
     const uint32_t tile_u = cf_smem_u32(tiles) + (uint32_t)(warp_u * (8 * CF_TILE_LD) * 4);
-    const uint32_t rs_u = cf_smem_u32(rs_acc);
     constexpr int STRIDE = CF_CW * CF_PARTS;
     const int c_first = part * CF_CW;
 
@@ -355,7 +363,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             }
             t4[u] = x;
           }
-          if (net.top_materialised && (do_backward || net.has_skip) && k < top.ld_out)
+          if (!tma_out && net.top_materialised && (do_backward || net.has_skip) && k < top.ld_out)
             *reinterpret_cast<float4*>(ws + top.q_off + grow * top.ld_out + k) = make_float4(t4[0], t4[1], t4[2], t4[3]);
         }
         cf_sts128(cf_smem_u32(X) + cf_xoff(r, k), t4[0], t4[1], t4[2], t4[3]);
@@ -400,6 +408,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       }
       const bool vec_ok = prow != nullptr && ((reinterpret_cast<uintptr_t>(prow) & 15) == 0);
       const uint32_t acc = taddr + (uint32_t)((t & 1) * CF_ACC_COLS);
+      float* const rs_p = ws + sd.rs_off + (long long)b0 * sd.rs_ld;   // row sums of the layer [B, rs_ld] (zeroed by the caller; added to)
 
       // value of a 16-column block (identical in both phases): residual and per-sample scaling ...
       auto block_pre = [&](float (&x)[CF_CW], const float (&v)[CF_CW], const float (&sc)[CF_CW], int c0) {
@@ -449,19 +458,21 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       cf_mbar_wait(mma_done, t & 1);
       if (tid == 0) CF_STAMP(t, 4);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      if (tma_out && t > 0) cf_mbar_wait(x_free, (t - 1) & 1);     // the copy of the previous result has left X
 
       // ---- phase A: accumulator -> next operand X (and its row-major copy in global memory), hand X over ----
+      // Blocks go in pairs: both values are computed first, then X is written.  X still feeds the TMA store of the
+      // PREVIOUS result when the contraction completes; computing before waiting for that store hides its latency.
       if (write_x || thread_out) {
-#pragma unroll 1
-        for (int c0 = c_first; c0 < N; c0 += STRIDE) {
-          float v[CF_CW], sc[CF_CW], tg[CF_CW], x[CF_CW];
+        auto compute_block = [&](float (&x)[CF_CW], int c0) {
+          float v[CF_CW], sc[CF_CW], tg[CF_CW];
           cf_tmem_ld16(acc + (uint32_t)c0, v);
 #pragma unroll
           for (int j = 0; j < CF_CW; ++j) { sc[j] = sc0[j]; tg[j] = tg0[j]; }
           if (c0 != c_first) load_sc_tg(sc, tg, c0);
           block_pre(x, v, sc, c0);
           block_post(x, tg);
+        };
+        auto write_block = [&](const float (&x)[CF_CW], int c0) {
           if (write_x) {
             const uint32_t xb = xrow + (uint32_t)((c0 >> 5) * CF_CHUNK_BYTES);
             const int j0 = (c0 & 31) >> 2;
@@ -470,7 +481,21 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
               cf_sts128(xb + (uint32_t)(((j0 + (j >> 2)) ^ xsw) << 4), x[j], x[j + 1], x[j + 2], x[j + 3]);
           }
           if (thread_out && row_ok) cf_store_vec16(out_p, c0, sd.out_ld, x);     // padded columns are exact zeros
+        };
+        bool x_is_free = !tma_out;
+#pragma unroll 1
+        for (int c0 = c_first; c0 < N; c0 += 2 * STRIDE) {
+          float xa[CF_CW], xb[CF_CW];
+          const bool two = c0 + STRIDE < N;
+          compute_block(xa, c0);
+          if (two) compute_block(xb, c0 + STRIDE);
+          if (!x_is_free) { cf_mbar_wait(x_free, t & 1); x_is_free = true; }   // the copy of the previous result has left X
+          write_block(xa, c0);
+          if (two) write_block(xb, c0 + STRIDE);
         }
+        if (!x_is_free) cf_mbar_wait(x_free, t & 1);          // (a thread without blocks still follows every phase)
+      } else if (tma_out) {
+        cf_mbar_wait(x_free, t & 1);
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       if (t + 1 < n_steps || (tma_out && out_on)) {
@@ -506,7 +531,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                 float sum = ((a.x + a.y) + (a.z + a.w)) + ((c.x + c.y) + (c.z + c.w));
                 sum += __shfl_xor_sync(0xffffffffu, sum, 8);
                 sum += __shfl_xor_sync(0xffffffffu, sum, 16);
-                if (lane < 8) cf_sts32(rs_u + (uint32_t)((qw * 128 + c0 + 8 * h + lane) * 4), sum);
+                if (lane < 8 && g_lo < nsamp && c0 + 8 * h + lane < N) atomicAdd(rs_p + (long long)g_lo * sd.rs_ld + c0 + 8 * h + lane, sum);
                 __syncwarp();
               }
             } else {
@@ -515,7 +540,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
 #pragma unroll
                 for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[j] * q[j] : 0.f;
                 const float tot = cf_colsum16(m, lane);
-                if (lane < 16 && c0 + lane < N) atomicAdd(&rs_acc[gg * 128 + c0 + lane], tot);
+                if (lane < 16 && c0 + lane < N) atomicAdd(rs_p + (long long)gg * sd.rs_ld + c0 + lane, tot);
               }
             }
           }
@@ -535,8 +560,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         }
       }
       // ---- cross-warp leftovers of the step ----
-      if (mode != 0) {
-        if (mode == 1) {
+      if (mode == 1) {
+        {
           if (row_ok) st_h1 += e_row * inv_nj;
           ex_s[(part * 128 + r) * 2 + 0] = e_row;               // the per-row metric needs the FULL row sums
           ex_s[(part * 128 + r) * 2 + 1] = n_row;
@@ -549,26 +574,10 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
           st_rr += e_all / n_all;
           st_rows += 1.f;
         }
-        if (mode == 2) {                                          // publish the row sums of this layer
-          float* const rs_p = ws + sd.rs_off + (long long)b0 * sd.rs_ld;
-          for (int e = tid; e < nsamp * 128; e += CF_EPI) {
-            const int gg = e >> 7, n = e & 127;
-            if (aligned) {
-              if (n < N) {
-                float sum = 0.f;
-                for (int q = 0; q < nq; ++q) sum += rs_acc[(gg * nq + q) * 128 + n];
-                rs_p[(long long)gg * sd.rs_ld + n] = sum;
-              }
-            } else {
-              if (n < N) rs_p[(long long)gg * sd.rs_ld + n] = rs_acc[e];
-              rs_acc[e] = 0.f;
-            }
-          }
-          asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");     // rs_acc is free again before the next row-sum step writes it
-        }
       }
       if (tid == 0) CF_STAMP(t, 6);
     }
+    if (tid == 0) CF_STAMP(2, 7);
     if (do_loss) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
@@ -584,6 +593,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  if (tid == 0) CF_STAMP(3, 7);
   if (warp_u == CF_EPI_WARPS)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2u * CF_ACC_COLS) : "memory");
 }
@@ -621,6 +631,17 @@ bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const Chai
     cuuint32_t box[2] = {32, box_rows};
     cuuint32_t es[2] = {1, 1};
     if (enc(&maps->out[t], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ws + st.out_off), gdim, gstr, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return false;
+  }
+  if (net.top_materialised && net.layer[net.L - 1].q_off >= 0) {
+    const ChainLayerDev& top = net.layer[net.L - 1];
+    cuuint64_t gdim[2] = {(cuuint64_t)top.ld_out, (cuuint64_t)max_rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)top.ld_out * sizeof(float)};
+    cuuint32_t box[2] = {32, box_rows};
+    cuuint32_t es[2] = {1, 1};
+    if (enc(&maps->top, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ws + top.q_off), gdim, gstr, box, es,
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return false;
@@ -700,7 +721,7 @@ cudaError_t chain_fused_read_trace(unsigned long long* out) {
 cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, const ChainSteps& steps, float* ws, const float* jt, const float* jn2,
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
                                float* stats, cudaStream_t st) {
-  constexpr int SMEM = 3 * CF_X_BYTES + 64 + 16 * 128 * 4 + CF_PARTS * 128 * 2 * 4 + CF_EPI_WARPS * 8 * CF_TILE_LD * 4 + 1024;
+  constexpr int SMEM = 3 * CF_X_BYTES + 64 + CF_PARTS * 128 * 2 * 4 + CF_EPI_WARPS * 8 * CF_TILE_LD * 4 + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(chain_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);

@@ -160,7 +160,7 @@ struct ChainStep {
 };
 struct ChainSteps { int n_fwd, n_all; ChainStep st[2 * CHAIN_FUSED_MAX_LAYERS]; };
 // fwd / bwd: weight tiles per layer; out[t]: row-major destination of step t's result (TMA store from the operand tile)
-struct ChainMaps { CUtensorMap fwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap bwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap out[2 * CHAIN_FUSED_MAX_LAYERS]; };
+struct ChainMaps { CUtensorMap fwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap bwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap out[2 * CHAIN_FUSED_MAX_LAYERS]; CUtensorMap top; };
 bool chain_fused_supported(const ChainNetDev& net);
 bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const ChainSteps& steps, long long max_rows, const float* ws,
                              const long long* wp_off, const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp);

@@ -28,8 +28,4 @@ print("step  " + "  ".join(f"{n:>9s}" for n in names) + "   (ns since first stam
 for s in range(17):
     print(f"{s:4d}  " + "  ".join(f"{int(v - t0):9d}" for v in t[s, :7]))
 
-print("epilogue detail (tid 0): pre_bar | it0: start, tmem_ld, computed | it1: start, tmem_ld, computed | loop_end   (ns since mma_done)")
-for s in range(17):
-    base = t[s, 4]
-    e = t[32 + s]
-    print(f"{s:4d}  pre_bar {int(e[3]-base):6d} | " + "  ".join(f"{int(e[k]-base):6d}" for k in (0, 1, 2)) + " | " + "  ".join(f"{int(e[k]-base):6d}" for k in (4, 5, 6)) + f" | {int(e[7]-base):6d}")
+print("kernel entry -> set-up done -> first x_ready -> loop end -> exit (ns):", [int(t[k, 7] - t[0, 7]) for k in range(4)], "first x_ready", int(t[0, 0] - t[0, 7]))
