@@ -284,6 +284,16 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     // ===== store warp: row-major copy of every step result that somebody reads later =====
     // The result of step t sits in X as the operand of step t+1: one elected lane TMA-stores it from there (whole
     // 128-byte lines, no thread touches the data), one box per 32-column chunk (and per sample when rows are warp-aligned).
+    if (do_loss) {
+      // the target Jacobians of this tile are first needed ~15 us from now (last forward step): pull them into L2
+      for (int gI = 0; gI < nsamp; ++gI) {
+        const long long sb = idx ? idx[b0 + gI] : b0 + gI;
+        const char* base = reinterpret_cast<const char*>(jt + sb * (long long)s * net.d_in);
+        const long long bytes = (long long)s * net.d_in * 4;
+        for (long long o = (long long)lane * 128; o < bytes; o += 32 * 128)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(base + o));
+      }
+    }
     if (tma_out && cf_elect_one()) {
       const uint32_t x_u = cf_smem_u32(X);
       auto store_x = [&](const CUtensorMap* map, int N) {
@@ -462,7 +472,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       // ---- phase A: accumulator -> next operand X (and its row-major copy in global memory), hand X over ----
       // Blocks go in pairs: both values are computed first, then X is written.  X still feeds the TMA store of the
       // PREVIOUS result when the contraction completes; computing before waiting for that store hides its latency.
-      if (write_x || thread_out) {
+      float e_row = 0.f, n_row = 0.f;
+      if (write_x || thread_out || mode == 1) {
         auto compute_block = [&](float (&x)[CF_CW], int c0) {
           float v[CF_CW], sc[CF_CW], tg[CF_CW];
           cf_tmem_ld16(acc + (uint32_t)c0, v);
@@ -470,6 +481,14 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
           for (int j = 0; j < CF_CW; ++j) { sc[j] = sc0[j]; tg[j] = tg0[j]; }
           if (c0 != c_first) load_sc_tg(sc, tg, c0);
           block_pre(x, v, sc, c0);
+          if (mode == 1) {                           // loss statistics of the row: squared error and target norm
+#pragma unroll
+            for (int j = 0; j < CF_CW; ++j) {
+              const float d = x[j] - tg[j];
+              e_row = fmaf(d, d, e_row);
+              n_row = fmaf(tg[j], tg[j], n_row);
+            }
+          }
           block_post(x, tg);
         };
         auto write_block = [&](const float (&x)[CF_CW], int c0) {
@@ -505,14 +524,13 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       }
       if (tid == 0) CF_STAMP(t, 5);
 
-      // ---- phase B: everything nobody waits for (overlaps the next contraction) ----
-      float e_row = 0.f, n_row = 0.f;
-      if (mode != 0 && !(dbg & 16)) {
+      // ---- phase B: the row sums, which nobody waits for (overlaps the next contraction) ----
+      if (mode == 2 && !(dbg & 16)) {
 #pragma unroll 1
         for (int c0 = c_first; c0 < N; c0 += STRIDE) {
           float v[CF_CW];
           cf_tmem_ld16(acc + (uint32_t)c0, v);
-          if (mode == 2 && !(dbg & 32)) {
+          if (!(dbg & 32)) {
             // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l   (rows beyond the sample carry zeros in dQ_l)
             float q[CF_CW];
 #pragma unroll
@@ -542,19 +560,6 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                 const float tot = cf_colsum16(m, lane);
                 if (lane < 16 && c0 + lane < N) atomicAdd(rs_p + (long long)gg * sd.rs_ld + c0 + lane, tot);
               }
-            }
-          }
-          if (mode == 1) {                           // loss statistics of the row: squared error and target norm
-            float sc[CF_CW], tg[CF_CW], x[CF_CW];
-#pragma unroll
-            for (int j = 0; j < CF_CW; ++j) { sc[j] = sc0[j]; tg[j] = tg0[j]; }
-            if (c0 != c_first) load_sc_tg(sc, tg, c0);
-            block_pre(x, v, sc, c0);
-#pragma unroll
-            for (int j = 0; j < CF_CW; ++j) {
-              const float d = x[j] - tg[j];
-              e_row = fmaf(d, d, e_row);
-              n_row = fmaf(tg[j], tg[j], n_row);
             }
           }
         }

@@ -92,7 +92,7 @@ struct DinoPlan {
   // optional per-kernel timing (dino_plan_profile): CUDA events around the Jacobian-chain stage of each step
   // side stream: the chain's weight gradients run concurrently with the MLP backward (fork/join by events)
   cudaStream_t side;
-  cudaEvent_t ev_fork, ev_join;
+  cudaEvent_t ev_fork, ev_join, ev_prep;
   bool profile;
   cudaEvent_t ev0, ev1;
   double prof_ms; long long prof_n; bool ev_pending;
@@ -126,7 +126,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   p->max_batch = spec->max_batch;
   p->precision = spec->precision;
   p->ws = nullptr;
-  p->side = nullptr; p->ev_fork = p->ev_join = nullptr;
+  p->side = nullptr; p->ev_fork = p->ev_join = p->ev_prep = nullptr;
   p->profile = false; p->prof_ms = 0.0; p->prof_n = 0; p->ev_pending = false; p->ev0 = p->ev1 = nullptr;
   long long poff = 0;
   int n_in = spec->d_in;
@@ -268,6 +268,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     DINO_CUDA(cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking));
     DINO_CUDA(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
     DINO_CUDA(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+    DINO_CUDA(cudaEventCreateWithFlags(&p->ev_prep, cudaEventDisableTiming));
   }
   *out = p;
   return 0;
@@ -275,7 +276,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
 
 extern "C" void dino_plan_destroy(DinoPlan* plan) {
   if (plan && plan->ev0) { cudaEventDestroy(plan->ev0); cudaEventDestroy(plan->ev1); }
-  if (plan && plan->side) { cudaEventDestroy(plan->ev_fork); cudaEventDestroy(plan->ev_join); cudaStreamDestroy(plan->side); }
+  if (plan && plan->side) { cudaEventDestroy(plan->ev_fork); cudaEventDestroy(plan->ev_join); cudaEventDestroy(plan->ev_prep); cudaStreamDestroy(plan->side); }
   delete plan;
 }
 
@@ -428,14 +429,14 @@ static int push_wgrad(DinoPlan* p, GemmGroup& g, const GemmOp& op, cudaStream_t 
 
 // Fused tcgen05 path: prep weights, then ONE kernel runs chain forward [+ H1 loss [+ chain backward]].
 static int run_chain_fused(DinoPlan* p, const float* params, const DinoBatch* b, int B, float coef, int do_loss,
-                           int do_backward, float* stats, cudaStream_t st, TopQ* top_out) {
+                           int do_backward, float* stats, cudaStream_t st, TopQ* top_out, bool weights_ready = false) {
   float* ws = p->ws;
   const LayerPlan& last = p->layers[p->L - 1];
   const float* seed = p->jac_mode == DINO_JAC_OUT_REDUCED ? b->seed : nullptr;
   if (p->top_materialised) *top_out = {ws + last.q_off, last.ld_out, 0};
   else if (p->jac_mode == DINO_JAC_FULL) *top_out = {ws + p->off_ident, p->ld_ident, p->s};
   else *top_out = {b->seed, (long long)p->d_out, p->s};
-  DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
+  if (!weights_ready) DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
   if (p->profile) {
     if (p->ev_pending && cudaEventSynchronize(p->ev1) == cudaSuccess) {
       float ms = 0.f;
@@ -678,13 +679,22 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
   DINO_CUDA(cudaMemsetAsync(grad, 0, (size_t)p->n_params * sizeof(float), st));
   if (p->rs_floats > 0)
     DINO_CUDA(cudaMemsetAsync(p->ws + p->off_rs_begin, 0, (size_t)p->rs_floats * sizeof(float), st));
+  const bool prep_aside = p->chain_fused && p->side != nullptr;
+  if (prep_aside) {
+    // the padded / rounded weight tiles of the chain only depend on the parameters: build them next to the MLP forward
+    DINO_CUDA(cudaEventRecord(p->ev_fork, st));
+    DINO_CUDA(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+    DINO_LAUNCH(launch_prep_weights(params, p->ws, p->prep, p->max_in, p->max_out, p->side));
+    DINO_CUDA(cudaEventRecord(p->ev_prep, p->side));
+  }
   if (run_mlp_forward(p, params, b, B, st)) return 1;
   TopQ top = {nullptr, 0, 0};
   GemmGroup wg;
   wg.n = 0;
   if (p->chain_fused) {
     if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st, true)) return 1;
-    if (run_chain_fused(p, params, b, B, 2.f * w_h1 * inv_gb, 1, 1, stats, st, &top)) return 1;
+    if (prep_aside) DINO_CUDA(cudaStreamWaitEvent(st, p->ev_prep, 0));
+    if (run_chain_fused(p, params, b, B, 2.f * w_h1 * inv_gb, 1, 1, stats, st, &top, prep_aside)) return 1;
     if (p->side != nullptr) {
       // fork: the chain's weight gradients (tensor cores, side stream) overlap the MLP backward (main stream);
       // both only ADD into the gradient, which was cleared before the fork
