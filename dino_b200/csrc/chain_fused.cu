@@ -185,7 +185,9 @@ __global__ void __launch_bounds__(CF_THREADS, 1)
 chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ ChainNetDev net,
                    const __grid_constant__ ChainSteps steps, float* __restrict__ ws, const float* __restrict__ jt,
                    const float* __restrict__ jn2, const int* __restrict__ idx, const float* __restrict__ seed, int B,
-                   float coef, int do_loss, int do_backward, float* __restrict__ stats) {
+                   float coef, int do_loss, int do_backward, float* __restrict__ stats,
+                   const __grid_constant__ MlpNetDev mlp, const float* __restrict__ params, const float* __restrict__ m_in,
+                   const float* __restrict__ q_tgt, const float* __restrict__ qn2, float coef_q, int mlp_mode) {
   extern __shared__ uint8_t cf_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cf_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* X = smem;
@@ -198,6 +200,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 6);
   float* ex_s = reinterpret_cast<float*>(w_full + 8);                                            // [CF_PARTS][128][2] loss partials of the row parts
   float* tiles = ex_s + CF_PARTS * 128 * 2;                                   // [CF_EPI_WARPS][8][CF_TILE_LD] row-sum transposition tiles
+  uint64_t* mlp_done = w_full + 7;                                           // the MLP forward no longer uses the weight-tile buffers
+  float* act_s = tiles + CF_EPI_WARPS * 8 * CF_TILE_LD;                       // [2][16][128] MLP activations of the tile's samples (ping-pong)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int s = net.s, G = net.G, L = net.L;
@@ -221,7 +225,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   if (warp == CF_EPI_WARPS) {
     if (lane == 0) {
       cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(x_ready, CF_EPI_WARPS);
-      cf_mbar_init(x_free, 1); cf_mbar_init(fwd_stored, 1);
+      cf_mbar_init(x_free, 1); cf_mbar_init(fwd_stored, 1); cf_mbar_init(mlp_done, CF_EPI_WARPS);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -247,6 +251,13 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         cf_mbar_expect_tx(w_full + buf, (uint32_t)nch * CF_CHUNK_BYTES);
         for (int c = 0; c < nch; ++c) cf_tma_load(Wb[buf] + c * CF_CHUNK_BYTES, map, c * 32, 0, w_full + buf);
       };
+      // the in-kernel MLP forward borrows the weight-tile buffers and their barriers first: wait until it is done with
+      // them, and count the barrier phases it has used up
+      const int used0 = mlp_mode > 0 ? (mlp.L + 1) / 2 : 0, used1 = mlp_mode > 0 ? mlp.L / 2 : 0;
+      if (mlp_mode > 0) {
+        cf_mbar_wait(mlp_done, 0);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      }
       load_w(0);
       const uint64_t xd = cf_desc(cf_smem_u32(X));
       const uint64_t wd0 = cf_desc(cf_smem_u32(Wb[0])), wd1 = cf_desc(cf_smem_u32(Wb[1]));
@@ -260,7 +271,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         const int ksteps = (K + 7) >> 3;
         cf_mbar_wait(x_ready, t & 1);                       // operand X written by the epilogue threads
         CF_STAMP(t, 0);
-        cf_mbar_wait(w_full + buf, (t >> 1) & 1);           // weight tile landed
+        cf_mbar_wait(w_full + buf, ((t >> 1) + (buf ? used1 : used0)) & 1);           // weight tile landed
         CF_STAMP(t, 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         // descriptor start addresses advance by 32 bytes per 8-wide K step, 16 KB per 32-column chunk (no carry out
@@ -355,6 +366,103 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     const uint32_t tile_u = cf_smem_u32(tiles) + (uint32_t)(warp_u * (8 * CF_TILE_LD) * 4);
     constexpr int STRIDE = CF_CW * CF_PARTS;
     const int c_first = part * CF_CW;
+
+    // ---- the network itself for the tile's samples: z_{l+1} = act(z_l W_l + b_l), plain fp32 FMAs ----
+    // (a few thousand multiply-adds per sample: not worth a launch of its own.  One thread per (sample, output column),
+    //  activations ping-pong in shared memory, the fp32 weights of layer l+1 / l+2 arrive by bulk copy in the two
+    //  weight-tile buffers -- idle until the chain starts -- while layer l is computed.)
+    if (mlp_mode > 0) {
+      float* a_cur = act_s;
+      float* a_nxt = act_s + 16 * 128;
+      auto fetch_w = [&](int l) {
+        const MlpLayerDev& ly = mlp.layer[l];
+        const uint32_t bytes = (uint32_t)(((ly.n_in * ly.n_out + 3) & ~3) * 4);
+        cf_mbar_expect_tx(w_full + (l & 1), bytes);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(cf_smem_u32(Wb[l & 1])), "l"(params + ly.koff), "r"(bytes), "r"(cf_smem_u32(w_full + (l & 1))) : "memory");
+      };
+      if (tid == 0) { fetch_w(0); if (mlp.L > 1) fetch_w(1); }
+      for (int e = tid; e < nsamp * 128; e += CF_EPI) {
+        const int gI = e >> 7, k = e & 127;
+        float v = 0.f;
+        if (k < mlp.d_in) {
+          const long long row = idx ? idx[b0 + gI] : (b0 + gI);
+          v = __ldg(m_in + row * mlp.d_in + k);
+          ws[mlp.z0_off + (long long)(b0 + gI) * mlp.ld_in + k] = v;
+        }
+        a_cur[e] = v;
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");
+      const int cl = tid & 63, u = tid >> 6;                 // 256 threads = 4 samples x 64 columns per pass
+#pragma unroll 1
+      for (int l = 0; l < mlp.L; ++l) {
+        const MlpLayerDev& ly = mlp.layer[l];
+        const float* W = reinterpret_cast<const float*>(Wb[l & 1]);
+        const int n_in = ly.n_in, n_out = ly.n_out;
+        cf_mbar_wait(w_full + (l & 1), (l >> 1) & 1);
+#pragma unroll 1
+        for (int c0 = 0; c0 < n_out; c0 += 64) {
+          const int c = c0 + cl;
+#pragma unroll 1
+          for (int g0 = 0; g0 < nsamp; g0 += 4) {
+            const int gI = g0 + u;
+            if (c < n_out && gI < nsamp) {
+              const float* a = a_cur + gI * 128;
+              float acc0 = ly.boff >= 0 ? __ldg(params + ly.boff + c) : 0.f, acc1 = 0.f;
+              int k = 0;
+#pragma unroll 4
+              for (; k + 1 < n_in; k += 2) {                  // (two chains: the FMA latency is the cost here)
+                acc0 = fmaf(a[k], W[k * n_out + c], acc0);
+                acc1 = fmaf(a[k + 1], W[(k + 1) * n_out + c], acc1);
+              }
+              if (k < n_in) acc0 = fmaf(a[k], W[k * n_out + c], acc0);
+              float v = acc0 + acc1;
+              if (ly.act) {
+                ws[ly.sg_off + (long long)(b0 + gI) * ly.ld_out + c] = sigmoid_f(v);
+                v = softplus_f(v);
+              }
+              a_nxt[gI * 128 + c] = v;
+              ws[ly.z_off + (long long)(b0 + gI) * ly.ld_out + c] = v;
+            }
+          }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");      // layer done: activations visible, weight buffer free
+        if (tid == 0 && l + 2 < mlp.L) fetch_w(l + 2);
+        float* sw = a_cur; a_cur = a_nxt; a_nxt = sw;
+      }
+      // output loss normalized_mse (trainingUtilities.py:25-29): one warp per sample
+      if (mlp_mode > 1) {
+        const int d_out = mlp.layer[mlp.L - 1].n_out;
+        for (int gI = warp_u; gI < nsamp; gI += CF_EPI_WARPS) {
+          const long long sb = idx ? idx[b0 + gI] : (b0 + gI);
+          const float* qt = q_tgt + sb * d_out;
+          float e = 0.f;
+          for (int cI = lane; cI < d_out; cI += 32) {
+            const float d = a_cur[gI * 128 + cI] - __ldg(qt + cI);
+            e = fmaf(d, d, e);
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
+          const float nq = __ldg(qn2 + sb);
+          if (mlp_mode > 2) {
+            const float gq = coef_q / nq;
+            for (int cI = lane; cI < d_out; cI += 32)
+              ws[mlp.dz_top_off + (long long)(b0 + gI) * mlp.ld_dz + cI] = gq * (a_cur[gI * 128 + cI] - __ldg(qt + cI));
+          }
+          if (lane == 0) {
+            atomicAdd(stats + ST_L2_SUM, e / nq);
+            atomicAdd(stats + ST_EQ_SUM, e);
+            atomicAdd(stats + ST_NQ_SUM, nq);
+            atomicAdd(stats + ST_COUNT, 1.f);
+          }
+        }
+      }
+      // the chain epilogue of OTHER threads reads these sigmoids from global memory; the weight-tile buffers and their
+      // barriers now belong to the chain (the control warp waits for this before its first TMA)
+      __threadfence_block();
+      asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");
+      if (lane == 0) cf_mbar_arrive(mlp_done);
+    }
 
     // X_0 = Q_{L-1} = seed (* sg_{L-1})
     {
@@ -725,8 +833,9 @@ cudaError_t chain_fused_read_trace(unsigned long long* out) {
 
 cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, const ChainSteps& steps, float* ws, const float* jt, const float* jn2,
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
-                               float* stats, cudaStream_t st) {
-  constexpr int SMEM = 3 * CF_X_BYTES + 64 + CF_PARTS * 128 * 2 * 4 + CF_EPI_WARPS * 8 * CF_TILE_LD * 4 + 1024;
+                               float* stats, const MlpNetDev& mlp, const float* params, const float* m_in, const float* q_tgt,
+                               const float* qn2, float coef_q, int mlp_mode, cudaStream_t st) {
+  constexpr int SMEM = 2 * 16 * 128 * 4 + 3 * CF_X_BYTES + 64 + CF_PARTS * 128 * 2 * 4 + CF_EPI_WARPS * 8 * CF_TILE_LD * 4 + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(chain_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
@@ -734,7 +843,8 @@ cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, co
     configured = true;
   }
   const int ctas = (B + net.G - 1) / net.G;
-  chain_fused_kernel<<<ctas, CF_THREADS, SMEM, st>>>(maps, net, steps, ws, jt, jn2, idx, seed, B, coef, do_loss, do_backward, stats);
+  chain_fused_kernel<<<ctas, CF_THREADS, SMEM, st>>>(maps, net, steps, ws, jt, jn2, idx, seed, B, coef, do_loss, do_backward, stats,
+                                                      mlp, params, m_in, q_tgt, qn2, coef_q, mlp_mode);
   return cudaGetLastError();
 }
 

@@ -167,7 +167,8 @@ bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const Chai
 void chain_fused_build_steps(ChainSteps* steps, const ChainNetDev& net);
 cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, const ChainSteps& steps, float* ws, const float* jt, const float* jn2,
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
-                               float* stats, cudaStream_t st);
+                               float* stats, const MlpNetDev& mlp, const float* params, const float* m_in, const float* q_tgt,
+                               const float* qn2, float coef_q, int mlp_mode, cudaStream_t st);
 
 cudaError_t chain_fused_read_trace(unsigned long long* out);
 

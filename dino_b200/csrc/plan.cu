@@ -86,6 +86,7 @@ struct DinoPlan {
   ChainNetDev chain;         // descriptor + weight tensor maps of the fused tcgen05 chain kernel
   ChainMaps chain_maps;
   ChainSteps chain_steps;
+  bool mlp_in_chain;         // the fused chain kernel also runs the MLP forward and the output loss of its samples
   bool chain_fused;
   bool tc_wgrad;             // layer-by-layer tf32 path: transposed chain states kept for the tensor-core weight gradient
   long long ldT, r0t_off;
@@ -241,6 +242,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     }
   }
   p->chain_fused = false;
+  p->mlp_in_chain = false;
   if (p->precision == DINO_PREC_TF32 && (p->jac_mode == DINO_JAC_FULL || p->jac_mode == DINO_JAC_OUT_REDUCED) &&
       p->L <= CHAIN_FUSED_MAX_LAYERS && getenv("DINO_B200_NO_FUSED_CHAIN") == nullptr) {
     ChainNetDev& c = p->chain;
@@ -258,6 +260,8 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     }
     p->chain_fused = chain_fused_supported(c);
     if (p->chain_fused) chain_fused_build_steps(&p->chain_steps, c);
+    p->mlp_in_chain = p->chain_fused && p->mlp_fused && !c.has_skip && p->L <= MLP_FUSED_MAX_LAYERS &&
+                      getenv("DINO_B200_NO_MLP_IN_CHAIN") == nullptr;
   }
   p->tc_wgrad = false;
   p->ldT = 0;
@@ -428,8 +432,11 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
 static int push_wgrad(DinoPlan* p, GemmGroup& g, const GemmOp& op, cudaStream_t st);
 
 // Fused tcgen05 path: prep weights, then ONE kernel runs chain forward [+ H1 loss [+ chain backward]].
+// mlp_mode: 0 = the MLP forward (and the output loss) ran in their own launches; 1 = run the forward inside the chain
+// kernel; 2 = forward + output-loss statistics; 3 = forward + statistics + d loss / d q_hat (coef_q = 2 w_l2 / B_global)
 static int run_chain_fused(DinoPlan* p, const float* params, const DinoBatch* b, int B, float coef, int do_loss,
-                           int do_backward, float* stats, cudaStream_t st, TopQ* top_out, bool weights_ready = false) {
+                           int do_backward, float* stats, cudaStream_t st, TopQ* top_out, bool weights_ready = false,
+                           int mlp_mode = 0, float coef_q = 0.f) {
   float* ws = p->ws;
   const LayerPlan& last = p->layers[p->L - 1];
   const float* seed = p->jac_mode == DINO_JAC_OUT_REDUCED ? b->seed : nullptr;
@@ -448,7 +455,8 @@ static int run_chain_fused(DinoPlan* p, const float* params, const DinoBatch* b,
     const char* dbg = getenv("DINO_CF_DBG");
     const int knobs = dbg ? atoi(dbg) << 8 : 0;
     DINO_LAUNCH(launch_chain_fused(p->chain_maps, p->chain, p->chain_steps, ws, b->J, b->J_sqnorm, b->idx, seed, B, coef, do_loss,
-                                   do_backward | (do_backward ? knobs : 0), stats, st));
+                                   do_backward | (do_backward ? knobs : 0), stats, p->mlp, params, b->m, b->q, b->q_sqnorm, coef_q,
+                                   mlp_mode, st));
   }
   if (p->profile) { DINO_CUDA(cudaEventRecord(p->ev1, st)); p->ev_pending = true; }
   return 0;
@@ -657,10 +665,10 @@ extern "C" int dino_jacobian(DinoPlan* p, const float* params, const DinoBatch* 
   if (check_call(p, params, b, B, false)) return 1;
   if (p->jac_mode == DINO_JAC_NONE) return fail("dino_jacobian: plan has no Jacobian output");
   cudaStream_t st = S(stream);
-  if (run_mlp_forward(p, params, b, B, st)) return 1;
+  if (!p->mlp_in_chain && run_mlp_forward(p, params, b, B, st)) return 1;
   TopQ top;
   if (p->chain_fused) {
-    if (run_chain_fused(p, params, b, B, 0.f, 0, 0, nullptr, st, &top)) return 1;
+    if (run_chain_fused(p, params, b, B, 0.f, 0, 0, nullptr, st, &top, false, p->mlp_in_chain ? 1 : 0)) return 1;
   } else if (run_chain_forward(p, params, b, B, st, &top)) return 1;
   const LayerPlan& last = p->layers[p->L - 1];
   if (q_out) DINO_LAUNCH(launch_copy2d(p->ws + last.z_off, last.ld_out, q_out, p->d_out, B, p->d_out, st));
@@ -687,14 +695,16 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
     DINO_LAUNCH(launch_prep_weights(params, p->ws, p->prep, p->max_in, p->max_out, p->side));
     DINO_CUDA(cudaEventRecord(p->ev_prep, p->side));
   }
-  if (run_mlp_forward(p, params, b, B, st)) return 1;
+  if (!p->mlp_in_chain && run_mlp_forward(p, params, b, B, st)) return 1;
   TopQ top = {nullptr, 0, 0};
   GemmGroup wg;
   wg.n = 0;
   if (p->chain_fused) {
-    if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st, true)) return 1;
+    if (!p->mlp_in_chain && run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st, true)) return 1;
     if (prep_aside) DINO_CUDA(cudaStreamWaitEvent(st, p->ev_prep, 0));
-    if (run_chain_fused(p, params, b, B, 2.f * w_h1 * inv_gb, 1, 1, stats, st, &top, prep_aside)) return 1;
+    if (run_chain_fused(p, params, b, B, 2.f * w_h1 * inv_gb, 1, 1, stats, st, &top, prep_aside, p->mlp_in_chain ? 3 : 0,
+                        2.f * w_l2 * inv_gb))
+      return 1;
     if (p->side != nullptr) {
       // fork: the chain's weight gradients (tensor cores, side stream) overlap the MLP backward (main stream);
       // both only ADD into the gradient, which was cleared before the fork
@@ -725,11 +735,11 @@ extern "C" int dino_h1_eval(DinoPlan* p, const float* params, const DinoBatch* b
   if (!stats) return fail("dino_h1_eval: null output");
   if (check_call(p, params, b, B, true)) return 1;
   cudaStream_t st = S(stream);
-  if (run_mlp_forward(p, params, b, B, st)) return 1;
+  if (!p->mlp_in_chain && run_mlp_forward(p, params, b, B, st)) return 1;
   TopQ top = {nullptr, 0, 0};
   if (p->chain_fused) {
-    if (run_losses(p, b, B, 1.f, 1.f, 1.f, false, stats, st, true)) return 1;
-    return run_chain_fused(p, params, b, B, 2.f, 1, 0, stats, st, &top);
+    if (!p->mlp_in_chain && run_losses(p, b, B, 1.f, 1.f, 1.f, false, stats, st, true)) return 1;
+    return run_chain_fused(p, params, b, B, 2.f, 1, 0, stats, st, &top, false, p->mlp_in_chain ? 2 : 0);
   }
   if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
   return run_losses(p, b, B, 1.f, 1.f, 1.f, false, stats, st);
