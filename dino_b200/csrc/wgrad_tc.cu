@@ -9,6 +9,7 @@
 // Output tiles of 128 x 128; wide layers are covered by several tiles (blockIdx.x enumerates op, tile, split).
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -251,7 +252,8 @@ cudaError_t launch_wgrad_tc(const GemmGroup& gg, int num_sms, cudaStream_t st) {
   double total_work = 0.0;
   for (int i = 0; i < gg.n; ++i)
     total_work += (double)gg.ops[i].K * ((gg.ops[i].M + 127) / 128) * ((gg.ops[i].N + 127) / 128);
-  const double target_ctas = 2.0 * num_sms;
+  static const double wg_waves = getenv("DINO_WG_WAVES") ? atof(getenv("DINO_WG_WAVES")) : 1.0;
+  const double target_ctas = wg_waves * num_sms;
   int z = 0;
   for (int i = 0; i < gg.n; ++i) {
     const GemmOp& o = gg.ops[i];
