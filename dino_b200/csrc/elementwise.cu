@@ -474,8 +474,14 @@ cudaError_t launch_roll_stats(float* stage, float* hist, int* pos, int advance, 
 __global__ void adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                 float* __restrict__ v, long long n, float lr, float b1, float b2, float eps,
                                 const long long* __restrict__ t_done) {
-  const double t = (double)(*t_done + 1);
-  const float lr_t = (float)((double)lr * sqrt(1.0 - pow((double)b2, t)) / (1.0 - pow((double)b1, t)));
+  // the bias-corrected step size needs two double-precision pow(): one thread per block, not every thread
+  __shared__ float lr_t_s;
+  if (threadIdx.x == 0) {
+    const double t = (double)(*t_done + 1);
+    lr_t_s = (float)((double)lr * sqrt(1.0 - pow((double)b2, t)) / (1.0 - pow((double)b1, t)));
+  }
+  __syncthreads();
+  const float lr_t = lr_t_s;
   const float ob1 = 1.f - b1, ob2 = 1.f - b2;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float G = g[i];

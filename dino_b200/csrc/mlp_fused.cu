@@ -10,7 +10,7 @@
 
 namespace dino {
 
-constexpr int TS = 4;            // samples per CTA
+constexpr int TS = 2;            // samples per CTA
 constexpr int MT = 256;          // threads per CTA
 
 static inline int cdiv_i(int a, int b) { return (a + b - 1) / b; }
