@@ -348,11 +348,12 @@ def main():
         if ent and ent.get("per_gpu_batch") == batch and ent.get("config") == args.config:
             traffic = ent["dram_bytes_per_launch"]
     if kern is not None:
-        Fk = S.chain_flops_per_sample(arch)               # forward chain + data-gradient chain, SURVEY 8d terms
+        # forward chain + data-gradient chain (SURVEY 8d terms) + the network forward pass the kernel also runs
+        Fk = S.chain_flops_per_sample(arch) + S.mlp_forward_flops_per_sample(arch)
         ach = Fk * batch / (kern["ms"] * 1e-3) / 1e12
         roof = {"bound": "tensor", "achieved": ach, "peak": peaks["tensor"], "unit": "TFLOP/s",
                 "frac": ach / peaks["tensor"], "traffic": traffic, "peak_source": peaks["src"],
-                "kernel": "chain_fused_kernel (tcgen05 Jacobian chain: forward + H1 loss + data-gradient backward)",
+                "kernel": "chain_fused_kernel (network forward + output loss, tcgen05 Jacobian chain: forward + H1 loss + data-gradient backward)",
                 "kernel_ms": kern["ms"], "launches_timed": kern["launches_timed"],
                 "algorithmic_flops_per_launch": Fk * batch,
                 "timing": "CUDA events on the launching stream around the kernel, eager steps after the timed region",

@@ -190,6 +190,11 @@ def chain_flops_per_sample(arch: Arch) -> float:
     return min(arch.d_in, arch.d_out) * 2.0 * (S + (S - sizes[0]))
 
 
+def mlp_forward_flops_per_sample(arch: Arch) -> float:
+    """Algorithmic FLOPs of the network forward pass of one sample: 2 * S."""
+    return 2.0 * sum(k * n for _, k, n, *_ in layer_table(arch))
+
+
 def bytes_per_sample(arch: Arch) -> float:
     """Compulsory HBM bytes of one sample: read m, q and the target J once (fp32)."""
     return 4.0 * (arch.d_in + arch.d_out + arch.d_out * arch.d_in)
