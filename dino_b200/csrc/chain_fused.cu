@@ -1,20 +1,24 @@
-// Fused Jacobian-chain kernel (tcgen05 + TMA): forward chain, H1 loss and backward chain for a tile
-// of samples in ONE CTA, for networks whose widths fit one UMMA tile (<= 128; every BASELINE
-// reduced-basis config with r <= 128).
+// Fused Jacobian-chain kernel (tcgen05 + TMA): network forward, forward chain, H1 loss and backward chain for a
+// tile of samples in ONE CTA, for networks whose widths fit one UMMA tile (<= 128; every BASELINE reduced-basis
+// config with r <= 128).
 //
-// A CTA owns G = floor(128/s) whole samples = G*s <= 128 chain rows (s seed rows per sample).  The
-// current chain state X [128 rows, K <= 128] lives in shared memory in the UMMA K-major SWIZZLE_128B
-// layout; it is the A operand of every contraction.  Per layer one elected thread waits for the
-// layer's weight tile (TMA, double-buffered, prefetched one layer ahead), issues tcgen05.mma
-// kind::tf32 into a TMEM accumulator and commits to an mbarrier; the 128 epilogue threads (thread =
-// chain row = TMEM lane) read the accumulator with tcgen05.ld, apply the per-sample sigmoid scaling /
-// residual adds / loss, write the result BACK INTO X as the next layer's operand and stream it to
-// global memory once (Q_l and dR_l are needed later by the weight-gradient launch).  No chain state
-// is ever re-read from global memory inside the kernel except Q_l in the backward epilogue.
+// A CTA owns G = floor(128/s) whole samples = up to 128 chain rows (s seed rows per sample; a sample's rows start at
+// a multiple of 32 when the tile has room, so a warp never straddles two samples).  The current chain state X
+// [128 rows, K <= 128] lives in shared memory in the UMMA K-major SWIZZLE_128B layout; it is the A operand of every
+// contraction.  Roles: 8 epilogue warps (thread = chain row = TMEM lane, two threads per row splitting the column
+// blocks), one control warp (an elected lane streams the TF32 weight tiles by TMA one step ahead and issues the
+// tcgen05.mma of each step into one of two TMEM accumulators), one store warp (an elected lane TMA-stores every
+// step result from X to its row-major array in global memory: the weight-gradient launch reads those arrays as
+// MN-major operands, and the backward steps re-read Q_l from them).
 //
+//   network  l = 0..L-1 :  z_{l+1} = act(z_l W_l + b_l), sg_l = sigmoid(.)    (fp32 FMAs, 1 thread per output; the fp32
+//                          weights arrive by bulk copy in the still idle weight-tile buffers) ; output loss
 //   forward  l = L-1..0 :  R_l = X W_l^T (+ Q_skip) ;  X <- Q_{l-1} = R_l * sg_{l-1}      (X_0 = seed)
 //   loss                :  X <- G = coef (R_0 - J) / ||J_b||^2 ; statistics
-//   backward l = 0..L-1 :  dQ_l = X W_l ; rs_l[b,:] = sum_rows dQ_l * Q_l ; X <- dR_{l+1} = dQ_l * sg_l (+ dR_skip)
+//   backward l = 0..L-1 :  dQ_l = X W_l ; rs_l[b,:] += sum_rows dQ_l * Q_l ; X <- dR_{l+1} = dQ_l * sg_l (+ dR_skip)
+//
+// Every step has a phase A (accumulator -> X, the only thing the next contraction waits for) and, for the backward
+// steps, a phase B (the row sums) that re-reads the accumulator while the next contraction fills the other one.
 #include <cuda.h>
 
 #include "common.cuh"

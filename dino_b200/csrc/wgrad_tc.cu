@@ -1,12 +1,13 @@
-// Weight gradients of the Jacobian chain on the tensor cores:
-//     dW_l[n_in, n_out] += dR_l^T Q_l = XT[n_in, rows] * YT[n_out, rows]^T        (rows = B*s, tens of thousands)
-// for every layer in ONE launch, split over the rows.  XT / YT are the TRANSPOSED chain states the fused
-// chain kernel streams out next to the row-major ones (its epilogue threads own consecutive rows, so the
-// transposed stores are perfectly coalesced); with them both operands are K-major and the contraction
-// is the standard TMA -> tcgen05.mma.kind::tf32 -> TMEM pipeline of gemm_tc.cu with a red.global.add
-// epilogue.  (Feeding the row-major states as MN-major UMMA operands would avoid the copies, but TF32
-// MN-major tiles need the 32-byte-base swizzle variant, which could not be validated offline.)
-// Output tiles of 128 x 128; wide layers are covered by several tiles (blockIdx.x enumerates op, tile, split).
+// Weight gradients on the tensor cores:
+//     dW_l[n_in, n_out] += dR_l^T Q_l = X[rows, n_in]^T * Y[rows, n_out]          (rows = B*s, tens of thousands)
+// for every layer in ONE launch, split over the rows.  X / Y are the chain states exactly as the chain kernel keeps
+// them: ROW-major.  The reduction index is then the strided one, i.e. both factors are MN-major UMMA operands; for
+// 4-byte elements that takes the 128-byte swizzle with 32-byte atoms on the TMA side (CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)
+// and shared-memory descriptor layout type 1 (SWIZZLE_128B_BASE32B: LBO = pitch between 32-column groups, SBO = 512 B
+// = 4 reduction rows) plus the two "major" bits of the instruction descriptor.  Transposed factors [n, rows] (K-major,
+// plain SWIZZLE_128B) are still accepted.  Pipeline: TMA 3-stage ring -> tcgen05.mma.kind::tf32 -> TMEM ->
+// red.global.add.  Output tiles of 128 x 128; wide layers are covered by several tiles (blockIdx.x enumerates op,
+// tile, split).  The launch is sized to ONE wave of CTAs: every extra split adds 128 x n_out atomics.
 #include <cuda.h>
 
 #include <cstdlib>
