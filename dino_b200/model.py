@@ -778,6 +778,144 @@ class DinoModel:
         self.last_d2h_bytes = int(stats.numel()) * 4
         return _combine_stats(host, self.loss_weights, self.jac_mode != _lib.JAC_NONE)
 
+    def fit_generator(self, generator, steps_per_epoch=None, **_ignored):
+        """Keras ``fit_generator`` for ONE pass over ``generator``: every item is ``(x, y)`` of HOST arrays
+        (pinned torch tensors are copied asynchronously), one optimiser step per item, like ``train_on_batch``.
+        The input pipeline is overlapped the way ``tf.data`` prefetching does it: the host->device copy of
+        minibatch k+1 runs on a copy stream while minibatch k is computed, and the [loss, ...] row of step k
+        is read back (device->host) after step k+1 has been queued.  Returns the list of per-step rows."""
+        import torch
+        if not self._compiled:
+            raise RuntimeError("You must compile your model before training/testing.")
+        lib = _lib.load()
+        dp = parallel.context()
+        dev = self.core.device_params().device
+        jac = self.jac_mode != _lib.JAC_NONE
+        compute = torch.cuda.current_stream()
+        pipe = getattr(self, "_pipe", None)
+        if pipe is None:
+            pipe = self._pipe = {"copy": torch.cuda.Stream(), "sets": [{}, {}], "grad": None}
+        copy_stream = pipe["copy"]
+        if pipe["grad"] is None:
+            pipe["grad"] = torch.zeros(self.core.n_params, dtype=torch.float32, device=dev)
+        self._ensure_opt_state()
+        st = _stream()
+        rows, pending, h2d = [], None, 0
+
+        def stage(S, key, a):
+            t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))
+            buf = S.get(key)
+            if buf is None or buf.shape != t.shape:
+                buf = S[key] = torch.empty(t.shape, dtype=torch.float32, device=dev)
+            buf.copy_(t, non_blocking=True)
+            return buf
+
+        for k, (x, y) in enumerate(generator):
+            if steps_per_epoch is not None and k >= steps_per_epoch:
+                break
+            x = list(x) if isinstance(x, (list, tuple)) else [x]
+            y = list(y) if isinstance(y, (list, tuple)) else [y]
+            S = pipe["sets"][k & 1]
+            # ---- copy stream: this minibatch's inputs, once the step that last used this buffer set is done ----
+            if "consumed" in S:
+                copy_stream.wait_event(S["consumed"])
+            with torch.cuda.stream(copy_stream):
+                ds = DeviceDataset.__new__(DeviceDataset)
+                ds.m = stage(S, "m", x[0]); ds.n = Bl = int(ds.m.shape[0])
+                ds.U = ds.V = ds.J = ds.jn2 = ds.seed = None
+                if self.jac_mode == _lib.JAC_SKETCHED:
+                    ds.U, ds.V = stage(S, "U", x[1]), stage(S, "V", x[2])
+                ds.q = stage(S, "q", y[0])
+                if jac:
+                    ds.J = stage(S, "J", y[1])
+                S.setdefault("copied", torch.cuda.Event()).record(copy_stream)
+            h2d = sum(int(t.numel()) * 4 for kk, t in S.items() if kk in ("m", "q", "J", "U", "V"))
+            if self.output_basis is not None:
+                if "seed" not in pipe:
+                    pipe["seed"] = torch.from_numpy(np.ascontiguousarray(self.output_basis.T, dtype=np.float32)).to(dev)
+                ds.seed = pipe["seed"]
+            # ---- compute stream: norms, the step, the result row into pinned host memory ----
+            compute.wait_event(S["copied"])
+            if "norms" not in S or S["norms"].shape[1] != Bl:
+                S["norms"] = torch.empty(2, Bl, dtype=torch.float32, device=dev)
+                S["stats"] = torch.zeros(_lib.STAT_SLOTS, dtype=torch.float32, device=dev)
+                S["host"] = torch.zeros(_lib.STAT_SLOTS, dtype=torch.float32).pin_memory()
+                S.pop("graph", None)
+            opt = self.optimizer
+            if getattr(opt, "_t_dev", None) is None or opt._t_dev.device != dev:
+                opt._t_dev = torch.tensor([opt.iterations], dtype=torch.int64, device=dev)
+            plan = self._plan(Bl)
+
+            def enqueue():
+                # everything of one step that does not depend on the host: capturable, replayable
+                ds.qn2 = S["norms"][0]
+                _lib.check(lib.dino_sample_sqnorms(C.c_void_p(ds.q.data_ptr()), Bl, ds.q[0].numel(),
+                                                   C.c_void_p(ds.qn2.data_ptr()), _stream()), "dino_sample_sqnorms")
+                if jac:
+                    ds.jn2 = S["norms"][1]
+                    _lib.check(lib.dino_sample_sqnorms(C.c_void_p(ds.J.data_ptr()), Bl, ds.J[0].numel(),
+                                                       C.c_void_p(ds.jn2.data_ptr()), _stream()), "dino_sample_sqnorms")
+                S["stats"].zero_()
+                params = self.core.device_params()
+                _lib.check(lib.dino_h1_fwd_bwd(plan.handle, C.c_void_p(params.data_ptr()), C.byref(ds.batch(None)), Bl,
+                                               self.loss_weights[0], self.loss_weights[1], 1.0 / (Bl * dp.world),
+                                               C.c_void_p(pipe["grad"].data_ptr()), C.c_void_p(S["stats"].data_ptr()),
+                                               _stream()), "dino_h1_fwd_bwd")
+                if dp.world > 1:
+                    dp.all_reduce_sum(pipe["grad"])
+                if opt.kind == "adam":
+                    _lib.check(lib.dino_adam_dev(C.c_void_p(params.data_ptr()), C.c_void_p(pipe["grad"].data_ptr()),
+                                                 C.c_void_p(opt._m.data_ptr()), C.c_void_p(opt._v.data_ptr()),
+                                                 self.core.n_params, opt.learning_rate, opt.beta_1, opt.beta_2, opt.epsilon,
+                                                 C.c_void_p(opt._t_dev.data_ptr()), _stream()), "dino_adam_dev")
+                else:
+                    _lib.check(lib.dino_sgd(C.c_void_p(params.data_ptr()), C.c_void_p(pipe["grad"].data_ptr()),
+                                            self.core.n_params, opt.learning_rate, _stream()), "dino_sgd")
+                opt._t_dev += 1
+                if dp.world > 1:
+                    dp.all_reduce_sum(S["stats"])
+                S["host"].copy_(S["stats"], non_blocking=True)      # device->host read of the step's result
+
+            gkey = (Bl, opt.kind, float(opt.learning_rate), tuple(self.loss_weights), self.core.device_params().data_ptr())
+            entry = S.get("graph")
+            if entry is not None and entry[1] != gkey:
+                entry = None
+            use_graph = os.environ.get("DINO_B200_NO_GRAPH", "0") != "1" and not pipe.get("no_graph", False)
+            if entry is not None:
+                entry[0].replay()
+            elif use_graph and S.get("seen") == gkey:
+                try:                                    # second use of this buffer set with this shape: capture the step
+                    g = torch.cuda.CUDAGraph()
+                    side = torch.cuda.Stream()
+                    side.wait_stream(compute)
+                    with torch.cuda.graph(g, stream=side):
+                        enqueue()
+                    compute.wait_stream(side)
+                    S["graph"] = (g, gkey)
+                    g.replay()
+                except Exception:
+                    pipe["no_graph"] = True
+                    torch.cuda.synchronize()
+                    enqueue()
+            else:
+                enqueue()
+                S["seen"] = gkey
+            opt.iterations += 1
+            self.core.mark_device_updated()
+            S.setdefault("consumed", torch.cuda.Event()).record(compute)
+            S.setdefault("done", torch.cuda.Event()).record(compute)
+            # ---- the previous step's row is on the host by now (or soon): collect it ----
+            if pending is not None:
+                pending["done"].synchronize()
+                rows.append(_combine_stats(pending["host"].numpy().copy()[None, :], self.loss_weights, jac))
+            pending = S
+        if pending is not None:
+            pending["done"].synchronize()
+            rows.append(_combine_stats(pending["host"].numpy().copy()[None, :], self.loss_weights, jac))
+        self.last_h2d_bytes = h2d
+        self.last_d2h_bytes = _lib.STAT_SLOTS * 4
+        return rows
+
     # ---- fit -----------------------------------------------------------------------------------------
     def fit(self, x, y, validation_data=None, epochs=1, batch_size=32, verbose=0, callbacks=None,
             shuffle=True, initial_epoch=0, perms=None, **_ignored):

@@ -177,3 +177,29 @@ def test_observable_training_driver_l2_only(cuda_device, tmp_path):
     assert len(net.outputs) == 1
     ev = net.evaluate(np.zeros((4, 40)) + 0.1, np.ones((4, 10)))
     assert len(ev) == 2 and np.isfinite(ev).all()
+
+
+def test_fit_generator_matches_train_on_batch(cuda_device):
+    """The pipelined streaming call takes the same steps as one train_on_batch per minibatch."""
+    import torch
+    arch = H.SMALL["dense"]
+    data, tw = S.make_dataset(arch, 48, 5)
+    w = H.student_weights(arch, 6, tw, bias_noise=0.1)
+    batches = [([data["m"][i:i + 12]], [data["q"][i:i + 12], data["J"][i:i + 12]]) for i in range(0, 48, 12)]
+
+    def build():
+        m = S.build_model(arch, w, precision="fp32")
+        m.compile(optimizer=Adam(1e-3), loss=[normalized_mse, normalized_mse_matrix], loss_weights=[1.0, 1.0],
+                  metrics=[l2_accuracy, f_accuracy_matrix])
+        return m
+
+    from dino_b200 import Adam
+    from dino_b200.construction import normalized_mse, normalized_mse_matrix, l2_accuracy, f_accuracy_matrix
+    a, b = build(), build()
+    rows_a = [a.train_on_batch(x, y) for x, y in batches]
+    rows_b = b.fit_generator(iter(batches))
+    assert len(rows_b) == len(rows_a)
+    np.testing.assert_allclose(np.array(rows_b), np.array(rows_a), rtol=1e-5, atol=1e-7)
+    for la, lb in zip(a.layers, b.layers):
+        for wa, wb in zip(la.get_weights(), lb.get_weights()):
+            np.testing.assert_allclose(wb, wa, rtol=1e-5, atol=1e-7)
