@@ -474,11 +474,12 @@ cudaError_t launch_roll_stats(float* stage, float* hist, int* pos, int advance, 
 __global__ void adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                 float* __restrict__ v, long long n, float lr, float b1, float b2, float eps,
                                 const long long* __restrict__ t_done) {
-  // the bias-corrected step size needs two double-precision pow(): one thread per block, not every thread
+  // the bias-corrected step size, once per block and in fp32 like Keras computes it (optimizer_v2/adam.py: tf.pow on
+  // float32 tensors); double-precision pow() costs microseconds on this part
   __shared__ float lr_t_s;
   if (threadIdx.x == 0) {
-    const double t = (double)(*t_done + 1);
-    lr_t_s = (float)((double)lr * sqrt(1.0 - pow((double)b2, t)) / (1.0 - pow((double)b1, t)));
+    const float t = (float)(*t_done + 1);
+    lr_t_s = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
   }
   __syncthreads();
   const float lr_t = lr_t_s;
