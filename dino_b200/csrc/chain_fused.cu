@@ -6,7 +6,7 @@
 // a multiple of 32 when the tile has room, so a warp never straddles two samples).  The current chain state X
 // [128 rows, K <= 128] lives in shared memory in the UMMA K-major SWIZZLE_128B layout; it is the A operand of every
 // contraction.  Roles: 8 epilogue warps (thread = chain row = TMEM lane, two threads per row splitting the column
-// blocks), one control warp (an elected lane streams the TF32 weight tiles by TMA one step ahead and issues the
+// blocks), four row-sum warps, one control warp (an elected lane streams the TF32 weight tiles by TMA one step ahead and issues the
 // tcgen05.mma of each step into one of two TMEM accumulators), one store warp (an elected lane TMA-stores every
 // step result from X to its row-major array in global memory: the weight-gradient launch reads those arrays as
 // MN-major operands, and the backward steps re-read Q_l from them).
@@ -17,8 +17,9 @@
 //   loss                :  X <- G = coef (R_0 - J) / ||J_b||^2 ; statistics
 //   backward l = 0..L-1 :  dQ_l = X W_l ; rs_l[b,:] += sum_rows dQ_l * Q_l ; X <- dR_{l+1} = dQ_l * sg_l (+ dR_skip)
 //
-// Every step has a phase A (accumulator -> X, the only thing the next contraction waits for) and, for the backward
-// steps, a phase B (the row sums) that re-reads the accumulator while the next contraction fills the other one.
+// The epilogue warps only do what the next contraction waits for (accumulator -> X).  The row sums of the backward
+// steps belong to four more warps (one per TMEM lane quarter) that re-read the accumulator of step t while step t+1
+// fills the other one.
 #include <cuda.h>
 
 #include "common.cuh"
@@ -38,7 +39,8 @@ constexpr int CF_X_BYTES = (CF_MAXW / 32) * CF_CHUNK_BYTES;                     
 constexpr int CF_PARTS = 2;                                                        // threads per chain row (column split)
 constexpr int CF_EPI = 128 * CF_PARTS;                                             // 8 epilogue warps: 2 per TMEM lane quarter
 constexpr int CF_EPI_WARPS = CF_EPI / 32;
-constexpr int CF_THREADS = CF_EPI + 64;                                            // + control warp (weight TMA, MMA issue) + store warp (TMA stores of the results)
+constexpr int CF_RS_WARPS = 4;                                                     // row-sum warps: one per TMEM lane quarter
+constexpr int CF_THREADS = CF_EPI + 64 + 32 * CF_RS_WARPS;                         // + control warp (weight TMA, MMA issue) + store warp (TMA stores of the results) + row-sum warps
 constexpr int CF_CW = 16;                                                          // columns per TMEM load / work item
 constexpr int CF_ACC_COLS = 128;                                                   // TMEM columns per accumulator (two of them: steps alternate)
 constexpr int CF_TILE_LD = 36;                                                     // floats per column of a warp's row-sum transposition tile
@@ -202,11 +204,16 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   uint64_t* x_free = w_full + 4;                                             // the stores of the previous result have read X
   uint64_t* fwd_stored = w_full + 5;                                         // every forward chain state has landed in global memory
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 6);
-  float* ex_s = reinterpret_cast<float*>(w_full + 8);                                            // [CF_PARTS][128][2] loss partials of the row parts
+  float* ex_s = reinterpret_cast<float*>(w_full + 16);                                            // [CF_PARTS][128][2] loss partials of the row parts
   float* tiles = ex_s + CF_PARTS * 128 * 2;                                   // [CF_EPI_WARPS][8][CF_TILE_LD] row-sum transposition tiles
+  uint64_t* rs_done = w_full + 8;                                            // [2] the row-sum warps have read accumulator t&1 (step t)
+  uint64_t* mma_done1 = w_full + 10;                                         // mma_done of the odd steps
   uint64_t* mlp_done = w_full + 7;                                           // the MLP forward no longer uses the weight-tile buffers
   float* act_s = tiles + CF_EPI_WARPS * 8 * CF_TILE_LD;                       // [2][16][128] MLP activations of the tile's samples (ping-pong)
 
+  // One completion barrier per accumulator: a waiter that lags a step behind still finds "its" phase in flight or just
+  // completed (a parity wait cannot tell phase p from phase p+2 of the same barrier).
+  auto mma_bar = [&](int t) { return (t & 1) ? mma_done1 : mma_done; };
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int s = net.s, G = net.G, L = net.L;
   const int b0 = blockIdx.x * G;
@@ -228,8 +235,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   for (int e = tid; e < CF_X_BYTES / 16; e += CF_THREADS) reinterpret_cast<float4*>(X)[e] = make_float4(0.f, 0.f, 0.f, 0.f);
   if (warp == CF_EPI_WARPS) {
     if (lane == 0) {
-      cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(x_ready, CF_EPI_WARPS);
-      cf_mbar_init(x_free, 1); cf_mbar_init(fwd_stored, 1); cf_mbar_init(mlp_done, CF_EPI_WARPS);
+      cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(mma_done1, 1); cf_mbar_init(x_ready, CF_EPI_WARPS);
+      cf_mbar_init(x_free, 1); cf_mbar_init(fwd_stored, 1); cf_mbar_init(mlp_done, CF_EPI_WARPS); cf_mbar_init(rs_done, CF_RS_WARPS); cf_mbar_init(rs_done + 1, CF_RS_WARPS);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -275,6 +282,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         const int ksteps = (K + 7) >> 3;
         cf_mbar_wait(x_ready, t & 1);                       // operand X written by the epilogue threads
         CF_STAMP(t, 0);
+        if (t >= 2) cf_mbar_wait(rs_done + buf, ((t >> 1) - 1) & 1);     // accumulator t&1 was last read by the row-sum warps in step t-2
         cf_mbar_wait(w_full + buf, ((t >> 1) + (buf ? used1 : used0)) & 1);           // weight tile landed
         CF_STAMP(t, 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -288,7 +296,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
           for (int j = 0; j < 4; ++j)
             if (c * 4 + j < ksteps) cf_mma(dcol, xd + oc + 2 * j, bd + oc + 2 * j, idesc, (c | j) ? 1u : 0u);
         }
-        cf_commit(mma_done);
+        cf_commit(mma_bar(t));
         CF_STAMP(t, 2);
         if (t + 1 < n_steps) load_w(t + 1);                 // the other buffer was released by step t-1
         CF_STAMP(t, 3);
@@ -347,12 +355,86 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // shared memory must outlive the stores
     }
     __syncwarp();
+  } else if (warp_u >= CF_EPI_WARPS + 2) {
+    // ===== row-sum warps: rs_l[b, n] += sum over the sample's rows of dQ_l * Q_l  (backward steps through a softplus) =====
+    // One warp per TMEM lane quarter, all column blocks of its 32 rows.  They re-read the accumulator of step t while the
+    // epilogue warps and the tensor core are already on step t+1 (two accumulators; the control warp waits for rs_done
+    // before it lets step t+2 overwrite the one read here).
+    const int qw = warp_u & 3;
+    const int r = qw * 32 + lane;
+    const int g_raw = r / srow;
+    const int i_seed = r - g_raw * srow;
+    const bool row_ok = g_raw < nsamp && i_seed < s;
+    const int g = row_ok ? g_raw : 0;
+    const long long grow = row0 + (long long)g * s + i_seed;
+    const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16);
+    const int g_lo = (32 * qw) / srow, g_hi = min((32 * qw + 31) / srow, nsamp - 1);
+    const bool aligned = (srow & 31) == 0;
+    const uint32_t tile_u = cf_smem_u32(tiles) + (uint32_t)((warp_u - CF_EPI_WARPS - 2) * (16 * CF_TILE_LD) * 4);   // two 8-column tiles
+#pragma unroll 1
+    for (int t = 0; t < n_steps; ++t) {
+      const ChainStep& sd = steps.st[t];
+      const int N = sd.N;
+      const bool work = sd.mode == 2 && !(dbg & 16);
+      if (tma_out && do_backward && t == steps.n_fwd) cf_mbar_wait(fwd_stored, 0);   // Q_l are read from global memory from here on
+      const float* const q_p = ws + sd.q_off + grow * sd.q_ld;         // Q_l rows
+      float* const rs_p = ws + sd.rs_off + (long long)b0 * sd.rs_ld;   // row sums of the layer [B, rs_ld] (zeroed by the caller; added to)
+      float qn[CF_CW];
+#pragma unroll
+      for (int j = 0; j < CF_CW; ++j) qn[j] = 0.f;
+      if (work) cf_load_vec16(qn, q_p, 0, sd.q_ld, row_ok);             // first block, requested while the MMA runs
+      cf_mbar_wait(mma_bar(t), (t >> 1) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (work) {
+        const uint32_t acc = taddr + (uint32_t)((t & 1) * CF_ACC_COLS);
+#pragma unroll 1
+        for (int c0 = 0; c0 < N; c0 += CF_CW) {
+          float v[CF_CW], q[CF_CW];
+          cf_tmem_ld16(acc + (uint32_t)c0, v);
+#pragma unroll
+          for (int j = 0; j < CF_CW; ++j) q[j] = qn[j];
+          if (c0 + CF_CW < N) cf_load_vec16(qn, q_p, c0 + CF_CW, sd.q_ld, row_ok);   // next block, in flight during this one
+          if (aligned) {
+            // the warp's 32 rows belong to one sample: transpose the 16 columns through the warp's two tiles (8 columns
+            // each), lane (c, q) adds rows 8q..8q+7 of column c of either tile, two shuffles per tile finish
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              cf_sts32(tile_u + (uint32_t)((j * CF_TILE_LD + lane) * 4), v[j] * q[j]);
+              cf_sts32(tile_u + (uint32_t)(((8 + j) * CF_TILE_LD + lane) * 4), v[8 + j] * q[8 + j]);
+            }
+            __syncwarp();
+            const uint32_t tp = tile_u + (uint32_t)(((lane & 7) * CF_TILE_LD + (lane >> 3) * 8) * 4);
+            const float4 a0 = cf_lds128(tp), c0v = cf_lds128(tp + 16);
+            const float4 a1 = cf_lds128(tp + 8 * CF_TILE_LD * 4), c1v = cf_lds128(tp + 8 * CF_TILE_LD * 4 + 16);
+            float s0 = ((a0.x + a0.y) + (a0.z + a0.w)) + ((c0v.x + c0v.y) + (c0v.z + c0v.w));
+            float s1 = ((a1.x + a1.y) + (a1.z + a1.w)) + ((c1v.x + c1v.y) + (c1v.z + c1v.w));
+            s0 += __shfl_xor_sync(0xffffffffu, s0, 8);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, 8);
+            s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+            // lanes 0-7 publish columns c0..c0+7, lanes 8-15 columns c0+8..c0+15
+            const float sum = (lane & 8) ? s1 : s0;
+            if (lane < 16 && g_lo < nsamp && c0 + lane < N) atomicAdd(rs_p + (long long)g_lo * sd.rs_ld + c0 + lane, sum);
+            __syncwarp();
+          } else {
+            for (int gg = g_lo; gg <= g_hi; ++gg) {           // segmented over the samples under this warp's rows
+              float m[CF_CW];
+#pragma unroll
+              for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[j] * q[j] : 0.f;
+              const float tot = cf_colsum16(m, lane);
+              if (lane < 16 && c0 + lane < N) atomicAdd(rs_p + (long long)gg * sd.rs_ld + c0 + lane, tot);
+            }
+          }
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) cf_mbar_arrive(rs_done + (t & 1));
+    }
   } else {
     // ===== epilogue threads: CF_PARTS threads per chain row (= TMEM lane), alternating 16-column blocks =====
-    // Every step has two phases over the thread's column blocks.  Phase A is the critical path: accumulator ->
-    // next operand X, then X is handed to the tensor core.  Phase B re-reads the same accumulator (the next
-    // contraction writes the OTHER TMEM buffer) and does everything nobody waits for: transposed copies to
-    // global memory, row sums, loss statistics.  Phase B of step t overlaps the contraction of step t+1.
+    // Per step: accumulator -> per-sample scaling / residual / loss gradient -> next operand X, then X is handed to
+    // the tensor core (and to the store warp).  The row sums of the backward steps are the row-sum warps' business.
     const int qw = warp_u & 3;                              // TMEM lane quarter of this warp
     const int part = warp_u >> 2;
     const int r = qw * 32 + lane;
@@ -363,11 +445,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     const long long b = b0 + g;                             // batch sample
     const long long grow = row0 + (long long)g * s + i_seed;   // global chain row
     const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16);
-    const int g_lo = (32 * qw) / srow, g_hi = min((32 * qw + 31) / srow, nsamp - 1);   // samples under this warp's rows
-    const bool aligned = (srow & 31) == 0;                  // a warp never straddles two samples
     const uint32_t xrow = cf_smem_u32(X) + (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
     const int xsw = r & 7;
-    const uint32_t tile_u = cf_smem_u32(tiles) + (uint32_t)(warp_u * (8 * CF_TILE_LD) * 4);
     constexpr int STRIDE = CF_CW * CF_PARTS;
     const int c_first = part * CF_CW;
 
@@ -517,7 +596,6 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       const bool do_round = (next_reads_x || do_backward) && !(dbg & 8);  // only what feeds a later TF32 contraction is rounded
       float* const out_p = ws + sd.out_off + grow * sd.out_ld;
       const float* const add_p = ws + sd.add_off + grow * sd.add_ld;   // residual rows
-      const float* const q_p = ws + sd.q_off + grow * sd.q_ld;         // Q_l rows (row-sum operand)
       const float* const sc_p = ws + sd.sc_off + b * sd.sc_ld;      // this row's sample: per-sample scale vector
       const int sc_len = (sd.sc_ld < ((N + 3) & ~3)) ? sd.sc_ld : ((N + 3) & ~3);
       const float* prow = nullptr;                  // target-Jacobian row (loss)
@@ -530,7 +608,6 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       }
       const bool vec_ok = prow != nullptr && ((reinterpret_cast<uintptr_t>(prow) & 15) == 0);
       const uint32_t acc = taddr + (uint32_t)((t & 1) * CF_ACC_COLS);
-      float* const rs_p = ws + sd.rs_off + (long long)b0 * sd.rs_ld;   // row sums of the layer [B, rs_ld] (zeroed by the caller; added to)
 
       // value of a 16-column block (identical in both phases): residual and per-sample scaling ...
       auto block_pre = [&](float (&x)[CF_CW], const float (&v)[CF_CW], const float (&sc)[CF_CW], int c0) {
@@ -568,16 +645,14 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         if (mode == 1) cf_load16(tg, prow, c0, N, row_ok, vec_ok);
       };
 
-      if (tma_out && do_backward && t == steps.n_fwd) cf_mbar_wait(fwd_stored, 0);   // Q_l are read from global memory from here on
       // ---- while the MMA runs: request the first block's operands ----
-      float sc0[CF_CW], tg0[CF_CW], q0[CF_CW];
+      float sc0[CF_CW], tg0[CF_CW];
 #pragma unroll
-      for (int j = 0; j < CF_CW; ++j) { sc0[j] = 1.f; tg0[j] = 0.f; q0[j] = 0.f; }
+      for (int j = 0; j < CF_CW; ++j) { sc0[j] = 1.f; tg0[j] = 0.f; }
       if (c_first < N) {
         load_sc_tg(sc0, tg0, c_first);
-        if (mode == 2) cf_load_vec16(q0, q_p, c_first, sd.q_ld, row_ok);
       }
-      cf_mbar_wait(mma_done, t & 1);
+      cf_mbar_wait(mma_bar(t), (t >> 1) & 1);
       if (tid == 0) CF_STAMP(t, 4);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
@@ -636,46 +711,6 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       }
       if (tid == 0) CF_STAMP(t, 5);
 
-      // ---- phase B: the row sums, which nobody waits for (overlaps the next contraction) ----
-      if (mode == 2 && !(dbg & 16)) {
-#pragma unroll 1
-        for (int c0 = c_first; c0 < N; c0 += STRIDE) {
-          float v[CF_CW];
-          cf_tmem_ld16(acc + (uint32_t)c0, v);
-          if (!(dbg & 32)) {
-            // rs_l[b, n] = sum over the sample's rows of dQ_l * Q_l   (rows beyond the sample carry zeros in dQ_l)
-            float q[CF_CW];
-#pragma unroll
-            for (int j = 0; j < CF_CW; ++j) q[j] = q0[j];
-            if (c0 != c_first) cf_load_vec16(q, q_p, c0, sd.q_ld, row_ok);
-            if (aligned) {
-              // the warp's 32 rows belong to one sample: transpose 8 columns at a time through the warp's tile,
-              // lane (c, q) adds rows 8q..8q+7 of column c, two shuffles finish; one writer per (quarter, column)
-#pragma unroll
-              for (int h = 0; h < 2; ++h) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) cf_sts32(tile_u + (uint32_t)((j * CF_TILE_LD + lane) * 4), v[8 * h + j] * q[8 * h + j]);
-                __syncwarp();
-                const uint32_t tp = tile_u + (uint32_t)(((lane & 7) * CF_TILE_LD + (lane >> 3) * 8) * 4);
-                const float4 a = cf_lds128(tp), c = cf_lds128(tp + 16);
-                float sum = ((a.x + a.y) + (a.z + a.w)) + ((c.x + c.y) + (c.z + c.w));
-                sum += __shfl_xor_sync(0xffffffffu, sum, 8);
-                sum += __shfl_xor_sync(0xffffffffu, sum, 16);
-                if (lane < 8 && g_lo < nsamp && c0 + 8 * h + lane < N) atomicAdd(rs_p + (long long)g_lo * sd.rs_ld + c0 + 8 * h + lane, sum);
-                __syncwarp();
-              }
-            } else {
-              for (int gg = g_lo; gg <= g_hi; ++gg) {           // segmented over the samples under this warp's rows
-                float m[CF_CW];
-#pragma unroll
-                for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[j] * q[j] : 0.f;
-                const float tot = cf_colsum16(m, lane);
-                if (lane < 16 && c0 + lane < N) atomicAdd(rs_p + (long long)gg * sd.rs_ld + c0 + lane, tot);
-              }
-            }
-          }
-        }
-      }
       // ---- cross-warp leftovers of the step ----
       if (mode == 1) {
         {
@@ -839,7 +874,7 @@ cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, co
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
                                float* stats, const MlpNetDev& mlp, const float* params, const float* m_in, const float* q_tgt,
                                const float* qn2, float coef_q, int mlp_mode, cudaStream_t st) {
-  constexpr int SMEM = 2 * 16 * 128 * 4 + 3 * CF_X_BYTES + 64 + CF_PARTS * 128 * 2 * 4 + CF_EPI_WARPS * 8 * CF_TILE_LD * 4 + 1024;
+  constexpr int SMEM = 2 * 16 * 128 * 4 + 3 * CF_X_BYTES + 128 + CF_PARTS * 128 * 2 * 4 + CF_EPI_WARPS * 8 * CF_TILE_LD * 4 + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(chain_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
