@@ -127,6 +127,21 @@ __device__ __forceinline__ void cf_tmem_ld16(uint32_t taddr, float (&v)[CF_CW]) 
 #pragma unroll
   for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
 }
+__device__ __forceinline__ void cf_tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+}
 // byte offset of (row r, float column k..k+3, k % 4 == 0) inside X (K-major, 128-byte rows, SWIZZLE_128B)
 __device__ __forceinline__ uint32_t cf_xoff(int r, int k) {
   const int c = k >> 5, j = (k & 31) >> 2;
@@ -370,7 +385,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16);
     const int g_lo = (32 * qw) / srow, g_hi = min((32 * qw + 31) / srow, nsamp - 1);
     const bool aligned = (srow & 31) == 0;
-    const uint32_t tile_u = cf_smem_u32(tiles) + (uint32_t)((warp_u - CF_EPI_WARPS - 2) * (16 * CF_TILE_LD) * 4);   // two 8-column tiles
+    // 32 columns x 36 floats per warp: the four tiles run over `tiles` into `act_s`, which the MLP phase no longer needs
+    const uint32_t tile_u = cf_smem_u32(tiles) + (uint32_t)((warp_u - CF_EPI_WARPS - 2) * (32 * CF_TILE_LD) * 4);
 #pragma unroll 1
     for (int t = 0; t < n_steps; ++t) {
       const ChainStep& sd = steps.st[t];
@@ -379,51 +395,63 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       if (tma_out && do_backward && t == steps.n_fwd) cf_mbar_wait(fwd_stored, 0);   // Q_l are read from global memory from here on
       const float* const q_p = ws + sd.q_off + grow * sd.q_ld;         // Q_l rows
       float* const rs_p = ws + sd.rs_off + (long long)b0 * sd.rs_ld;   // row sums of the layer [B, rs_ld] (zeroed by the caller; added to)
-      float qn[CF_CW];
+      // 32 columns per pass: Q_l[row, c0 .. c0+32) (two 64-byte halves per row)
+      float q[32];
+      auto load_q32 = [&](int c0) {
+        float h0[CF_CW], h1[CF_CW];
+        cf_load_vec16(h0, q_p, c0, sd.q_ld, row_ok);
+        cf_load_vec16(h1, q_p, c0 + CF_CW, sd.q_ld, row_ok);
 #pragma unroll
-      for (int j = 0; j < CF_CW; ++j) qn[j] = 0.f;
-      if (work) cf_load_vec16(qn, q_p, 0, sd.q_ld, row_ok);             // first block, requested while the MMA runs
+        for (int j = 0; j < CF_CW; ++j) { q[j] = h0[j]; q[CF_CW + j] = h1[j]; }
+      };
+#pragma unroll
+      for (int j = 0; j < 32; ++j) q[j] = 0.f;
+      if (work) load_q32(0);                                            // first pass, requested while the MMA runs
       cf_mbar_wait(mma_bar(t), (t >> 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       if (work) {
         const uint32_t acc = taddr + (uint32_t)((t & 1) * CF_ACC_COLS);
 #pragma unroll 1
-        for (int c0 = 0; c0 < N; c0 += CF_CW) {
-          float v[CF_CW], q[CF_CW];
-          cf_tmem_ld16(acc + (uint32_t)c0, v);
-#pragma unroll
-          for (int j = 0; j < CF_CW; ++j) q[j] = qn[j];
-          if (c0 + CF_CW < N) cf_load_vec16(qn, q_p, c0 + CF_CW, sd.q_ld, row_ok);   // next block, in flight during this one
+        for (int c0 = 0; c0 < N; c0 += 32) {
+          float v[32];
+          cf_tmem_ld32(acc + (uint32_t)c0, v);
           if (aligned) {
-            // the warp's 32 rows belong to one sample: transpose the 16 columns through the warp's two tiles (8 columns
-            // each), lane (c, q) adds rows 8q..8q+7 of column c of either tile, two shuffles per tile finish
+            // the warp's 32 rows belong to one sample: transpose the 32 columns through the warp's tile, lane (c, i)
+            // adds rows 8i..8i+7 of column c of each 8-column group; two shuffles per group finish (four independent
+            // chains), lane j publishes column c0 + j
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              cf_sts32(tile_u + (uint32_t)((j * CF_TILE_LD + lane) * 4), v[j] * q[j]);
-              cf_sts32(tile_u + (uint32_t)(((8 + j) * CF_TILE_LD + lane) * 4), v[8 + j] * q[8 + j]);
-            }
+            for (int j = 0; j < 32; ++j) cf_sts32(tile_u + (uint32_t)((j * CF_TILE_LD + lane) * 4), v[j] * q[j]);
+            if (c0 + 32 < N) load_q32(c0 + 32);                         // next pass, in flight during the reduction
             __syncwarp();
             const uint32_t tp = tile_u + (uint32_t)(((lane & 7) * CF_TILE_LD + (lane >> 3) * 8) * 4);
-            const float4 a0 = cf_lds128(tp), c0v = cf_lds128(tp + 16);
-            const float4 a1 = cf_lds128(tp + 8 * CF_TILE_LD * 4), c1v = cf_lds128(tp + 8 * CF_TILE_LD * 4 + 16);
-            float s0 = ((a0.x + a0.y) + (a0.z + a0.w)) + ((c0v.x + c0v.y) + (c0v.z + c0v.w));
-            float s1 = ((a1.x + a1.y) + (a1.z + a1.w)) + ((c1v.x + c1v.y) + (c1v.z + c1v.w));
-            s0 += __shfl_xor_sync(0xffffffffu, s0, 8);
-            s1 += __shfl_xor_sync(0xffffffffu, s1, 8);
-            s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
-            s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
-            // lanes 0-7 publish columns c0..c0+7, lanes 8-15 columns c0+8..c0+15
-            const float sum = (lane & 8) ? s1 : s0;
-            if (lane < 16 && g_lo < nsamp && c0 + lane < N) atomicAdd(rs_p + (long long)g_lo * sd.rs_ld + c0 + lane, sum);
+            float sg4[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float4 a = cf_lds128(tp + (uint32_t)(i * 8 * CF_TILE_LD * 4)), c = cf_lds128(tp + (uint32_t)(i * 8 * CF_TILE_LD * 4) + 16);
+              sg4[i] = ((a.x + a.y) + (a.z + a.w)) + ((c.x + c.y) + (c.z + c.w));
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) sg4[i] += __shfl_xor_sync(0xffffffffu, sg4[i], 8);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) sg4[i] += __shfl_xor_sync(0xffffffffu, sg4[i], 16);
+            const int grp = lane >> 3;
+            const float sum = grp == 0 ? sg4[0] : grp == 1 ? sg4[1] : grp == 2 ? sg4[2] : sg4[3];
+            if (g_lo < nsamp && c0 + lane < N) atomicAdd(rs_p + (long long)g_lo * sd.rs_ld + c0 + lane, sum);
             __syncwarp();
           } else {
-            for (int gg = g_lo; gg <= g_hi; ++gg) {           // segmented over the samples under this warp's rows
-              float m[CF_CW];
 #pragma unroll
-              for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[j] * q[j] : 0.f;
-              const float tot = cf_colsum16(m, lane);
-              if (lane < 16 && c0 + lane < N) atomicAdd(rs_p + (long long)gg * sd.rs_ld + c0 + lane, tot);
+            for (int h = 0; h < 2; ++h) {
+              if (c0 + CF_CW * h < N) {
+                for (int gg = g_lo; gg <= g_hi; ++gg) {           // segmented over the samples under this warp's rows
+                  float m[CF_CW];
+#pragma unroll
+                  for (int j = 0; j < CF_CW; ++j) m[j] = (row_ok && g == gg) ? v[CF_CW * h + j] * q[CF_CW * h + j] : 0.f;
+                  const float tot = cf_colsum16(m, lane);
+                  if (lane < 16 && c0 + CF_CW * h + lane < N) atomicAdd(rs_p + (long long)gg * sd.rs_ld + c0 + CF_CW * h + lane, tot);
+                }
+              }
             }
+            if (c0 + 32 < N) load_q32(c0 + 32);
           }
         }
       }
