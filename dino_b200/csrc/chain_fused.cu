@@ -504,33 +504,41 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         a_cur[e] = v;
       }
       asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");
-      const int cl = tid & 63, u = tid >> 6;                 // 256 threads = 4 samples x 64 columns per pass
 #pragma unroll 1
       for (int l = 0; l < mlp.L; ++l) {
         const MlpLayerDev& ly = mlp.layer[l];
         const float* W = reinterpret_cast<const float*>(Wb[l & 1]);
         const int n_in = ly.n_in, n_out = ly.n_out;
+        // 256 threads = 4 samples x 64 columns per pass, or 2 samples x 128 columns for the wider layers
+        const int cw = n_out > 64 ? 128 : 64, su = CF_EPI / cw;
+        const int cl = tid & (cw - 1), u = tid / cw;
         cf_mbar_wait(w_full + (l & 1), (l >> 1) & 1);
 #pragma unroll 1
-        for (int c0 = 0; c0 < n_out; c0 += 64) {
+        for (int c0 = 0; c0 < n_out; c0 += cw) {
           const int c = c0 + cl;
 #pragma unroll 1
-          for (int g0 = 0; g0 < nsamp; g0 += 4) {
+          for (int g0 = 0; g0 < nsamp; g0 += su) {
             const int gI = g0 + u;
             if (c < n_out && gI < nsamp) {
               const float* a = a_cur + gI * 128;
-              float acc0 = ly.boff >= 0 ? __ldg(params + ly.boff + c) : 0.f, acc1 = 0.f;
+              const float* w = W + c;
+              float acc0 = ly.boff >= 0 ? __ldg(params + ly.boff + c) : 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
               int k = 0;
-#pragma unroll 4
-              for (; k + 1 < n_in; k += 2) {                  // (two chains: the FMA latency is the cost here)
-                acc0 = fmaf(a[k], W[k * n_out + c], acc0);
-                acc1 = fmaf(a[k + 1], W[(k + 1) * n_out + c], acc1);
+#pragma unroll 2
+              for (; k + 3 < n_in; k += 4) {                  // four chains: the FMA latency is the cost here
+                const float4 a4 = *reinterpret_cast<const float4*>(a + k);
+                acc0 = fmaf(a4.x, w[k * n_out], acc0);
+                acc1 = fmaf(a4.y, w[(k + 1) * n_out], acc1);
+                acc2 = fmaf(a4.z, w[(k + 2) * n_out], acc2);
+                acc3 = fmaf(a4.w, w[(k + 3) * n_out], acc3);
               }
-              if (k < n_in) acc0 = fmaf(a[k], W[k * n_out + c], acc0);
-              float v = acc0 + acc1;
+              for (; k < n_in; ++k) acc0 = fmaf(a[k], w[k * n_out], acc0);
+              float v = (acc0 + acc1) + (acc2 + acc3);
               if (ly.act) {
-                ws[ly.sg_off + (long long)(b0 + gI) * ly.ld_out + c] = sigmoid_f(v);
-                v = softplus_f(v);
+                // sigmoid and softplus from one exponential: e = exp(-|v|)
+                const float e = expf(-fabsf(v)), r1 = 1.f / (1.f + e);
+                ws[ly.sg_off + (long long)(b0 + gI) * ly.ld_out + c] = v >= 0.f ? r1 : e * r1;
+                v = fmaxf(v, 0.f) + log1pf(e);
               }
               a_nxt[gI * 128 + c] = v;
               ws[ly.z_off + (long long)(b0 + gI) * ly.ld_out + c] = v;
