@@ -178,6 +178,26 @@ __global__ void __launch_bounds__(MT) mlp_backward_fused_kernel(const __grid_con
     stage_weights_async(Wbuf[(net.L - 1) & 1], params + net.layer[net.L - 1].koff,
                         (net.layer[net.L - 1].n_in * net.layer[net.L - 1].n_out + 3) & ~3);
   float* da = dzb + 3 * TS * ld_dz;
+  // sigmoids and row sums of every layer for this tile's samples, fetched up front with all loads in flight (inside the
+  // layer loop each of them would be an exposed L2 round trip): [L][TS][ld_dz] each
+  float* sg_s = da + TS * ld_dz;
+  float* rs_s = sg_s + net.L * TS * ld_dz;
+  for (int l = net.lowest_trainable; l < net.L; ++l) {
+    const MlpLayerDev& ly = net.layer[l];
+    if (!ly.act) continue;
+    const bool has_rs = with_rowsum && ly.rs_off >= 0;
+    for (int e = threadIdx.x; e < TS * ly.n_out; e += MT) {
+      const int t = e / ly.n_out, n = e % ly.n_out;
+      float sv = 0.f, rv = 0.f;
+      if (t < nb) {
+        const long long row = (long long)(b0 + t) * ly.ld_out + n;
+        sv = ws[ly.sg_off + row];
+        if (has_rs) rv = ws[ly.rs_off + row];
+      }
+      sg_s[(l * TS + t) * ld_dz + n] = sv;
+      rs_s[(l * TS + t) * ld_dz + n] = rv;
+    }
+  }
   auto dz_buf = [&](int l) { return dzb + (l % 3) * TS * ld_dz; };
   {
     float* top = dz_buf(net.L);
@@ -198,8 +218,8 @@ __global__ void __launch_bounds__(MT) mlp_backward_fused_kernel(const __grid_con
       if (t < nb) {
         const long long row = (long long)(b0 + t) * ly.ld_out + n;
         if (ly.act) {
-          const float sv = ws[ly.sg_off + row];
-          const float rs = (with_rowsum && ly.rs_off >= 0) ? ws[ly.rs_off + row] : 0.f;
+          const float sv = sg_s[(l * TS + t) * ld_dz + n];
+          const float rs = rs_s[(l * TS + t) * ld_dz + n];
           v = fmaf(rs, 1.f - sv, v * sv);
         }
         if (ly.trainable) ws[ly.da_off + row] = v;
@@ -261,7 +281,7 @@ static int bwd_w_floats(const MlpNetDev& net) {
   return w > 4 ? w : 4;
 }
 static size_t bwd_smem(const MlpNetDev& net) {
-  return (2 * (size_t)bwd_w_floats(net) + 4 * (size_t)TS * net.ld_dz) * sizeof(float);
+  return (2 * (size_t)bwd_w_floats(net) + (4 + 2 * (size_t)net.L) * TS * net.ld_dz) * sizeof(float);
 }
 
 bool mlp_fused_supported(const MlpNetDev& net) {
