@@ -330,6 +330,12 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         const long long bytes = (long long)s * net.d_in * 4;
         for (long long o = (long long)lane * 128; o < bytes; o += 32 * 128)
           asm volatile("prefetch.global.L2 [%0];" ::"l"(base + o));
+        if (mlp_mode > 1) {                                  // ... and the output targets of the in-kernel output loss
+          const int d_out = mlp.layer[mlp.L - 1].n_out;
+          const char* qb = reinterpret_cast<const char*>(q_tgt + sb * d_out);
+          if (lane * 128 < d_out * 4) asm volatile("prefetch.global.L2 [%0];" ::"l"(qb + lane * 128));
+          if (lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(qn2 + sb));
+        }
       }
     }
     if (tma_out && cf_elect_one()) {
@@ -522,7 +528,8 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             if (c < n_out && gI < nsamp) {
               const float* a = a_cur + gI * 128;
               const float* w = W + c;
-              float acc0 = ly.boff >= 0 ? __ldg(params + ly.boff + c) : 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+              const float bias = ly.boff >= 0 ? __ldg(params + ly.boff + c) : 0.f;   // an L2 round trip: consumed after the sums
+              float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
               int k = 0;
 #pragma unroll 2
               for (; k + 3 < n_in; k += 4) {                  // four chains: the FMA latency is the cost here
@@ -533,7 +540,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                 acc3 = fmaf(a4.w, w[(k + 3) * n_out], acc3);
               }
               for (; k < n_in; ++k) acc0 = fmaf(a[k], w[k * n_out], acc0);
-              float v = (acc0 + acc1) + (acc2 + acc3);
+              float v = ((acc0 + acc1) + (acc2 + acc3)) + bias;
               if (ly.act) {
                 // sigmoid and softplus from one exponential: e = exp(-|v|)
                 const float e = expf(-fabsf(v)), r1 = 1.f / (1.f + e);
