@@ -29,8 +29,3 @@ for s in range(17):
     print(f"{s:4d}  " + "  ".join(f"{int(v - t0):9d}" for v in t[s, :7]))
 
 print("kernel entry -> set-up done -> first x_ready -> loop end -> exit (ns):", [int(t[k, 7] - t[0, 7]) for k in range(4)], "first x_ready", int(t[0, 0] - t[0, 7]))
-print("row-sum warp (quarter 2): mma_done seen | tmem_ld of blocks 0..3 | done   (ns since the control thread's x_ready of the step)")
-for s_ in range(9, 17):
-    base = t[s_, 0]
-    e = t[32 + s_]
-    print(f"{s_:4d}  " + "  ".join(f"{int(e[k] - base):6d}" for k in (0, 1, 2, 3, 4, 6)))
