@@ -855,7 +855,7 @@ void chain_fused_build_steps(ChainSteps* steps, const ChainNetDev& net) {
   const int L = net.L;
   auto blank = [] { ChainStep st; st.K = st.N = 0; st.mode = 0; st.add_first = 0; st.write_x = 1;
                     st.sc_ld = st.out_ld = st.add_ld = st.q_ld = st.rs_ld = 0;
-                    st.sc_off = st.out_off = st.outT_off = st.add_off = st.q_off = st.rs_off = -1; return st; };
+                    st.sc_off = st.out_off = st.add_off = st.q_off = st.rs_off = -1; return st; };
   int t = 0;
   for (int l = L - 1; l >= 0; --l, ++t) {
     const ChainLayerDev& ly = net.layer[l];

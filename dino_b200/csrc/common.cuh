@@ -117,8 +117,6 @@ cudaError_t launch_sketch_open(const float* dS, const float* V, const int* idx, 
 cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long n, float lr_t,
                         float b1, float b2, float eps, cudaStream_t st);
 cudaError_t launch_sgd(float* p, const float* g, long long n, float lr, cudaStream_t st);
-cudaError_t launch_transpose(const float* src, long long ld_src, float* dst, long long ld_dst, int rows, int cols,
-                             cudaStream_t st);
 cudaError_t launch_stage_batch(const int* idx_all, const int* pos, int* idx_stage, int B, cudaStream_t st);
 cudaError_t launch_roll_stats(float* stage, float* hist, int* pos, int advance, int* step, long long* t, cudaStream_t st);
 cudaError_t launch_adam_dev(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
@@ -139,10 +137,10 @@ namespace dino {
 
 // Fused tcgen05 chain kernel (chain_fused.cu)
 constexpr int CHAIN_FUSED_MAX_LAYERS = 16;
-// qt_off / drt_off: TRANSPOSED copies [n_out, ldT] of Q_l and dR_{l+1} (operands of the tensor-core weight gradient)
-struct ChainLayerDev { long long q_off, sg_off, rs_off, dr_off, qt_off, drt_off; int n_in, n_out, ld_out, act, skip_from, lands_skip; };
+// q_off / dr_off: row-major chain states Q_l and dR_{l+1} [B*s, ld_out] (also the operands of the weight-gradient launch)
+struct ChainLayerDev { long long q_off, sg_off, rs_off, dr_off; int n_in, n_out, ld_out, act, skip_from, lands_skip; };
 // srow: chain rows reserved per sample inside a CTA tile (s rounded up to a warp when the tile has room, so a warp never straddles two samples)
-struct ChainNetDev { int L, s, G, srow, d_in, ld_in, top_materialised, has_skip; long long r0_off, r0t_off, ldT; ChainLayerDev layer[CHAIN_FUSED_MAX_LAYERS]; };
+struct ChainNetDev { int L, s, G, srow, d_in, ld_in, top_materialised, has_skip; long long r0_off; ChainLayerDev layer[CHAIN_FUSED_MAX_LAYERS]; };
 // One contraction + epilogue of the fused kernel, in execution order (built on the host: the device code
 // carries no layer logic).  Offsets are into the workspace, -1 = absent.
 struct ChainStep {
@@ -153,7 +151,6 @@ struct ChainStep {
   int sc_ld, out_ld, add_ld, q_ld, rs_ld;
   long long sc_off;               // per-sample scale vectors [B, sc_ld]
   long long out_off;              // row-major destination rows
-  long long outT_off;             // transposed destination [N, ldT]
   long long add_off;              // residual rows
   long long q_off;                // Q_l rows (row-sum operand)
   long long rs_off;               // row-sum destination [B, rs_ld]

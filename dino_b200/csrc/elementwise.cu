@@ -425,28 +425,6 @@ cudaError_t launch_sgd(float* p, const float* g, long long n, float lr, cudaStre
   return cudaGetLastError();
 }
 
-// dst[c, r] = src[r, c]  (chain state -> its transpose, the K-major operand of the tensor-core weight gradient)
-__global__ void transpose_kernel(const float* __restrict__ src, long long ld_src, float* __restrict__ dst,
-                                 long long ld_dst, int rows, int cols) {
-  __shared__ float tile[32][33];
-  const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
-  for (int i = threadIdx.y; i < 32; i += 8) {
-    const int r = r0 + i, c = c0 + threadIdx.x;
-    tile[i][threadIdx.x] = (r < rows && c < cols) ? src[(long long)r * ld_src + c] : 0.f;
-  }
-  __syncthreads();
-  for (int i = threadIdx.y; i < 32; i += 8) {
-    const int c = c0 + i, r = r0 + threadIdx.x;
-    if (c < cols && r < rows) dst[(long long)c * ld_dst + r] = tile[threadIdx.x][i];
-  }
-}
-cudaError_t launch_transpose(const float* src, long long ld_src, float* dst, long long ld_dst, int rows, int cols,
-                             cudaStream_t st) {
-  if (rows <= 0 || cols <= 0) return cudaSuccess;
-  transpose_kernel<<<dim3(cdiv(cols, 32), cdiv(rows, 32)), dim3(32, 8), 0, st>>>(src, ld_src, dst, ld_dst, rows, cols);
-  return cudaGetLastError();
-}
-
 // ---- device-side cursors: let a CUDA graph of the training step be replayed with no host arguments ----
 // idx_stage[i] = idx_all[*pos + i]
 __global__ void stage_batch_kernel(const int* __restrict__ idx_all, const int* __restrict__ pos, int* __restrict__ idx_stage, int B) {

@@ -61,7 +61,6 @@ struct LayerPlan {
   long long z_off, sg_off, q_off, rs_off;   // workspace offsets (floats); -1 when absent
   long long wp_off, wtp_off, ld_wp, ld_wtp; // TF32 mode: padded W [n_in][ld_wp] and W^T [n_out][ld_wtp]
   long long dr_off;          // dR_{l+1} = gradient wrt the chain state above this layer [B*s, ld_out]; -1 for the top layer
-  long long qt_off, drt_off; // transposed copies [n_out, ldT] of Q_l and dR_{l+1} (fused tensor-core path)
   long long da_off;          // da_l [B, ld_out] (fused MLP backward keeps every layer's for the grouped weight gradient)
   long long ld_out;          // r4(n_out)
   int lands_skip;            // index l2 of the skip layer whose source is THIS layer's input, or -1
@@ -88,8 +87,6 @@ struct DinoPlan {
   ChainSteps chain_steps;
   bool mlp_in_chain;         // the fused chain kernel also runs the MLP forward and the output loss of its samples
   bool chain_fused;
-  bool tc_wgrad;             // layer-by-layer tf32 path: transposed chain states kept for the tensor-core weight gradient
-  long long ldT, r0t_off;
   // optional per-kernel timing (dino_plan_profile): CUDA events around the Jacobian-chain stage of each step
   // side stream: the chain's weight gradients run concurrently with the MLP backward (fork/join by events)
   cudaStream_t side;
@@ -193,7 +190,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   for (int i = 0; i < 3; ++i) p->off_dz[i] = take(Bm * max_w);
   p->off_da = take(Bm * max_w);
   p->off_r0 = p->off_sk = -1;
-  for (auto& lp : p->layers) { lp.q_off = -1; lp.dr_off = -1; lp.da_off = -1; lp.qt_off = -1; lp.drt_off = -1; }
+  for (auto& lp : p->layers) { lp.q_off = -1; lp.dr_off = -1; lp.da_off = -1; }
   if (p->jac_mode != DINO_JAC_NONE) {
     for (int l = 0; l < p->L; ++l) {
       LayerPlan& lp = p->layers[l];
@@ -263,9 +260,6 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     p->mlp_in_chain = p->chain_fused && p->mlp_fused && !c.has_skip && p->L <= MLP_FUSED_MAX_LAYERS &&
                       getenv("DINO_B200_NO_MLP_IN_CHAIN") == nullptr;
   }
-  p->tc_wgrad = false;
-  p->ldT = 0;
-  p->r0t_off = -1;
   p->ws_floats = off;
   if (p->chain_fused && getenv("DINO_B200_NO_SIDE_STREAM") == nullptr) {
     DINO_CUDA(cudaSetDevice(device));
