@@ -380,6 +380,39 @@ def main():
         roof = {"bound": "tensor", "achieved": achieved_tf, "peak": peaks["tensor"], "unit": "TFLOP/s",
                 "frac": achieved_tf / peaks["tensor"], "traffic": None, "peak_source": peaks["src"],
                 "kernel": "whole H1 step (all launches of one step), algorithmic FLOPs of SURVEY 8d", "step": step_roof}
+    # ---- the chain contraction on its own at a wide layer (cfg5's 1024-wide hidden layers, 256 samples x s = 100 rows):
+    #      the tcgen05 engine next to cuBLAS TF32 on the same operands, CUDA-event timed.  north_star's ">= 50 % of dense
+    #      tensor-core peak on the Jacobian contraction" is about this kernel; cfg2's 50-100 wide layers cannot get there.
+    if args.precision == "tf32" and world == 1 and not args.no_fp32_leg:
+        Mg, Ng, Kg = 25600, 1024, 1024
+        Ag = torch.randn(Mg, Kg, device=dev); Bg_ = torch.randn(Ng, Kg, device=dev); Cg = torch.empty(Mg, Ng, device=dev)
+
+        def _time(fn, iters=20):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record()
+            for _ in range(iters):
+                fn()
+            g1.record()
+            torch.cuda.synchronize()
+            return g0.elapsed_time(g1) / iters
+
+        from dino_b200.model import _stream
+        ms_ours = _time(lambda: _lib.check(lib.dino_gemm_nt(_lib.PREC_TF32, C.c_void_p(Ag.data_ptr()), Kg, C.c_void_p(Bg_.data_ptr()),
+                                                            Kg, C.c_void_p(Cg.data_ptr()), Ng, Mg, Ng, Kg, _stream()), "gemm"))
+        old_tf32 = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = True
+        ms_cublas = _time(lambda: torch.matmul(Ag, Bg_.t()))
+        torch.backends.cuda.matmul.allow_tf32 = old_tf32
+        flg = 2.0 * Mg * Ng * Kg
+        roof["contraction_engine"] = {"kernel": "gemm_tc_kernel (TMA -> tcgen05.mma kind::tf32 -> TMEM), dino_gemm_nt",
+                                      "shape_MNK": [Mg, Ng, Kg], "achieved_tflops": flg / ms_ours / 1e9,
+                                      "cublas_tf32_tflops_same_operands": flg / ms_cublas / 1e9,
+                                      "frac_of_cublas_tf32": ms_cublas / ms_ours,
+                                      "frac_of_bf16_peak": flg / ms_ours / 1e9 / peaks["tensor"]}
+        del Ag, Bg_, Cg
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         import warnings
