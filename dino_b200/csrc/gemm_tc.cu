@@ -8,7 +8,8 @@
 //   * four epilogue warps read TMEM with tcgen05.ld (32 lanes x 32 columns per instruction) and apply
 //     v = (acc + add_pre) * scale[sample] + add_post before storing fp32.
 // Warp roles (192 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 2-5 epilogue.
-// One 128 x BN output tile per CTA.  Out-of-range rows/columns/K are zero-filled by TMA and masked
+// Persistent CTAs (one per SM) walk the 128 x BN output tiles; two TMEM accumulators let the epilogue of a tile overlap
+// the MMAs of the next.  Out-of-range rows/columns/K are zero-filled by TMA and masked
 // in the epilogue, so M, N, K are arbitrary; leading dimensions must be multiples of 4 floats.
 #include <cuda.h>
 
@@ -74,7 +75,8 @@ template <int BN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep) {
   constexpr int A_BYTES = TC_BM * TC_BK * 4, B_BYTES = BN * TC_BK * 4, STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;           // columns of one accumulator
+  constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;               // two accumulators: the epilogue of tile i overlaps the MMAs of tile i+1
   // instruction descriptor: D fp32, A/B tf32, both K-major, N = BN, M = 128
   constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 
@@ -82,12 +84,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + TC_STAGES * STAGE_BYTES);
   uint64_t* empty_bar = full_bar + TC_STAGES;
-  uint64_t* tmem_full_bar = empty_bar + TC_STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  uint64_t* tmem_full_bar = empty_bar + TC_STAGES;          // [2] accumulator complete
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;             // [2] accumulator read out by the four epilogue warps
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN;
   const int nkb = (ep.K + TC_BK - 1) / TC_BK;
+  // persistent: this CTA walks the output tiles blockIdx.x, blockIdx.x + gridDim.x, ... (column tile fastest)
+  const int tiles_n = (ep.N + BN - 1) / BN, n_tiles = tiles_n * ((ep.M + TC_BM - 1) / TC_BM);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
@@ -96,7 +100,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   if (warp == 1) {
     if (lane == 0) {
       for (int i = 0; i < TC_STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); }
-      mbar_init(tmem_full_bar, 1);
+      mbar_init(tmem_full_bar, 1); mbar_init(tmem_full_bar + 1, 1);
+      mbar_init(tmem_empty_bar, 4); mbar_init(tmem_empty_bar + 1, 4);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -111,38 +116,54 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int st = kb % TC_STAGES;
-        const uint32_t ph = (kb / TC_STAGES) & 1;
-        mbar_wait(empty_bar + st, ph ^ 1);
-        mbar_expect_tx(full_bar + st, STAGE_BYTES);
-        uint8_t* sa = smem + st * STAGE_BYTES;
-        tma_load_2d(sa, &tma_a, kb * TC_BK, m0, full_bar + st);
-        tma_load_2d(sa + A_BYTES, &tma_b, kb * TC_BK, n0, full_bar + st);
+      int it = 0;                                    // running stage counter: the ring does not restart per tile
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int m0 = (tile / tiles_n) * TC_BM, n0 = (tile % tiles_n) * BN;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int st = it % TC_STAGES;
+          const uint32_t ph = (it / TC_STAGES) & 1;
+          mbar_wait(empty_bar + st, ph ^ 1);
+          mbar_expect_tx(full_bar + st, STAGE_BYTES);
+          uint8_t* sa = smem + st * STAGE_BYTES;
+          tma_load_2d(sa, &tma_a, kb * TC_BK, m0, full_bar + st);
+          tma_load_2d(sa + A_BYTES, &tma_b, kb * TC_BK, n0, full_bar + st);
+        }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int st = kb % TC_STAGES;
-        const uint32_t ph = (kb / TC_STAGES) & 1;
-        mbar_wait(full_bar + st, ph);
+      int it = 0, i = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
+        const int acc = i & 1;
+        mbar_wait(tmem_empty_bar + acc, ((i >> 1) & 1) ^ 1);      // the epilogue has drained this accumulator (two tiles ago)
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
-        const uint64_t adesc = umma_desc_sw128(sa), bdesc = umma_desc_sw128(sa + A_BYTES);
+        const uint32_t tmem_d = tmem_base + (uint32_t)acc * ACC_COLS;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int st = it % TC_STAGES;
+          const uint32_t ph = (it / TC_STAGES) & 1;
+          mbar_wait(full_bar + st, ph);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
+          const uint64_t adesc = umma_desc_sw128(sa), bdesc = umma_desc_sw128(sa + A_BYTES);
 #pragma unroll
-        for (int k = 0; k < TC_BK / 8; ++k)        // UMMA_K = 8 tf32 = 32 bytes = 2 descriptor units
-          umma_tf32(tmem_base, adesc + 2 * k, bdesc + 2 * k, IDESC, (kb > 0 || k > 0) ? 1u : 0u);
-        umma_commit(empty_bar + st);               // frees the smem stage once these MMAs have read it
+          for (int k = 0; k < TC_BK / 8; ++k)        // UMMA_K = 8 tf32 = 32 bytes = 2 descriptor units
+            umma_tf32(tmem_d, adesc + 2 * k, bdesc + 2 * k, IDESC, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_commit(empty_bar + st);               // frees the smem stage once these MMAs have read it
+        }
+        umma_commit(tmem_full_bar + acc);            // accumulator complete
       }
-      umma_commit(tmem_full_bar);                  // accumulators complete
     }
   } else {
-    // ===== epilogue: TMEM -> registers -> global =====
-    mbar_wait(tmem_full_bar, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    // ===== epilogue: TMEM -> registers -> global, one accumulator behind the MMA issuer =====
     const int q = warp & 3;                        // TMEM lane quarter this warp may access
+    int i = 0;
+#pragma unroll 1
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
+    const int m0 = (tile / tiles_n) * TC_BM, n0 = (tile % tiles_n) * BN;
+    const int acc = i & 1;
+    mbar_wait(tmem_full_bar + acc, (i >> 1) & 1);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const int row = m0 + q * 32 + lane;
     const bool row_ok = row < ep.M;
     const long long b = row_ok ? row / ep.sdim : 0;
@@ -154,7 +175,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     for (int c0 = 0; c0 < BN; c0 += 32) {
       if (n0 + c0 >= ep.N) break;                  // warp-uniform
       uint32_t r[32];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * ACC_COLS + (uint32_t)c0;
       asm volatile(
           "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
           "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -191,6 +212,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           }
         }
       }
+    }
+    // this warp is done reading the accumulator: hand it back to the MMA issuer
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncwarp();
+    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(tmem_empty_bar + acc)) : "memory");
     }
   }
   // ===== teardown =====
@@ -262,7 +288,15 @@ static cudaError_t launch_tc(const GemmOp& op, cudaStream_t st) {
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
-  dim3 grid((op.N + BN - 1) / BN, (op.M + TC_BM - 1) / TC_BM);
+  // persistent CTAs, one per SM: each walks its share of the 128 x BN output tiles
+  static int num_sms = 0;
+  if (num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || num_sms <= 0) num_sms = 148;
+  }
+  const long long n_tiles = (long long)((op.N + BN - 1) / BN) * ((op.M + TC_BM - 1) / TC_BM);
+  const int grid = (int)(n_tiles < num_sms ? n_tiles : num_sms);
   gemm_tc_kernel<BN><<<grid, TC_THREADS, SMEM, st>>>(ma, mb, ep);
   return cudaGetLastError();
 }
