@@ -14,13 +14,13 @@ LIB_PATH = os.path.join(_HERE, "libdino_b200.so")
 
 ACT_LINEAR, ACT_SOFTPLUS = 0, 1
 JAC_NONE, JAC_FULL, JAC_OUT_REDUCED, JAC_SKETCHED = 0, 1, 2, 3
-PREC_FP32, PREC_TF32 = 0, 1
+PREC_FP32, PREC_TF32, PREC_FP32X3 = 0, 1, 2
 STAT_L2_SUM, STAT_H1_SUM, STAT_EQ_SUM, STAT_NQ_SUM, STAT_JROW_SUM, STAT_COUNT, STAT_JROWS = range(7)
 STAT_SLOTS = 8
 NOALLOC_MAX_BATCH, NOALLOC_MAX_WIDTH = 256, 1024
 
 JAC_MODES = {"none": JAC_NONE, "full": JAC_FULL, "out_reduced": JAC_OUT_REDUCED, "sketched": JAC_SKETCHED}
-PRECISIONS = {"fp32": PREC_FP32, "tf32": PREC_TF32}
+PRECISIONS = {"fp32": PREC_FP32, "tf32": PREC_TF32, "fp32x3": PREC_FP32X3}
 
 
 class DinoLayerSpec(C.Structure):

@@ -22,7 +22,7 @@
 // fills the other one.
 #include <cuda.h>
 
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace dino {
 
@@ -40,7 +40,10 @@ constexpr int CF_PARTS = 2;                                                     
 constexpr int CF_EPI = 128 * CF_PARTS;                                             // 8 epilogue warps: 2 per TMEM lane quarter
 constexpr int CF_EPI_WARPS = CF_EPI / 32;
 constexpr int CF_RS_WARPS = 4;                                                     // row-sum warps: one per TMEM lane quarter
-constexpr int CF_THREADS = CF_EPI + 64 + 32 * CF_RS_WARPS;                         // + control warp (weight TMA, MMA issue) + store warp (TMA stores of the results) + row-sum warps
+constexpr int CF_THREADS = CF_EPI + 64 + 32 * CF_RS_WARPS + 32;                    // + control warp (MMA issue) + store warp (TMA stores of the results) + row-sum warps + weight warp (TMA loads of the weight tiles)
+constexpr int CF_W_WARP = CF_EPI_WARPS + 2 + CF_RS_WARPS;                          // index of the weight warp
+constexpr int CF_SLOTS = 8;                                                        // weight ring: 16 KB slots, one per 32-column K chunk of a weight tile (hi or lo)
+constexpr int CF_XLO_COL = 2 * 128;                                                // fp32x3: TMEM columns of X_lo, the low part of the operand tile (A operand from tensor memory)
 constexpr int CF_CW = 16;                                                          // columns per TMEM load / work item
 constexpr int CF_ACC_COLS = 128;                                                   // TMEM columns per accumulator (two of them: steps alternate)
 constexpr int CF_TILE_LD = 36;                                                     // floats per column of a warp's row-sum transposition tile
@@ -142,6 +145,21 @@ __device__ __forceinline__ void cf_tmem_ld32(uint32_t taddr, float (&v)[32]) {
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
 }
+__device__ __forceinline__ void cf_tmem_st16(uint32_t taddr, const float (&v)[CF_CW]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+        "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+        "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+        "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
+      : "memory");
+}
+__device__ __forceinline__ void cf_tmem_st4(uint32_t taddr, float a, float b, float c, float d) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
+               ::"r"(taddr), "r"(__float_as_uint(a)), "r"(__float_as_uint(b)), "r"(__float_as_uint(c)), "r"(__float_as_uint(d)) : "memory");
+}
+__device__ __forceinline__ void cf_tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 // byte offset of (row r, float column k..k+3, k % 4 == 0) inside X (K-major, 128-byte rows, SWIZZLE_128B)
 __device__ __forceinline__ uint32_t cf_xoff(int r, int k) {
   const int c = k >> 5, j = (k & 31) >> 2;
@@ -208,22 +226,24 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                    const float* __restrict__ jn2, const int* __restrict__ idx, const float* __restrict__ seed, int B,
                    float coef, int do_loss, int do_backward, float* __restrict__ stats,
                    const __grid_constant__ MlpNetDev mlp, const float* __restrict__ params, const float* __restrict__ m_in,
-                   const float* __restrict__ q_tgt, const float* __restrict__ qn2, float coef_q, int mlp_mode) {
+                   const float* __restrict__ q_tgt, const float* __restrict__ qn2, float coef_q, int mlp_mode, int split) {
   extern __shared__ uint8_t cf_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cf_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* X = smem;
-  uint8_t* Wb[2] = {smem + CF_X_BYTES, smem + 2 * CF_X_BYTES};
-  uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + 3 * CF_X_BYTES);     // [2]
+  uint8_t* Wb[2] = {smem + CF_X_BYTES, smem + 2 * CF_X_BYTES};              // the weight ring (CF_SLOTS x 16 KB); its two halves first serve the MLP phase
+  uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + 3 * CF_X_BYTES);     // [2] MLP phase: fp32 weights of layer l landed in Wb[l & 1]
   uint64_t* mma_done = w_full + 2;
   uint64_t* x_ready = w_full + 3;
   uint64_t* x_free = w_full + 4;                                             // the stores of the previous result have read X
   uint64_t* fwd_stored = w_full + 5;                                         // every forward chain state has landed in global memory
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 6);
-  float* ex_s = reinterpret_cast<float*>(w_full + 16);                                            // [CF_PARTS][128][2] loss partials of the row parts
-  float* tiles = ex_s + CF_PARTS * 128 * 2;                                   // [CF_EPI_WARPS][8][CF_TILE_LD] row-sum transposition tiles
   uint64_t* rs_done = w_full + 8;                                            // [2] the row-sum warps have read accumulator t&1 (step t)
   uint64_t* mma_done1 = w_full + 10;                                         // mma_done of the odd steps
   uint64_t* mlp_done = w_full + 7;                                           // the MLP forward no longer uses the weight-tile buffers
+  uint64_t* slot_full = w_full + 16;                                         // [CF_SLOTS] weight ring: chunk landed
+  uint64_t* slot_empty = w_full + 16 + CF_SLOTS;                             // [CF_SLOTS] weight ring: the MMAs that read the chunk are complete
+  float* ex_s = reinterpret_cast<float*>(w_full + 16 + 2 * CF_SLOTS);        // [CF_PARTS][128][2] loss partials of the row parts
+  float* tiles = ex_s + CF_PARTS * 128 * 2;                                   // [CF_EPI_WARPS][8][CF_TILE_LD] row-sum transposition tiles
   float* act_s = tiles + CF_EPI_WARPS * 8 * CF_TILE_LD;                       // [2][16][128] MLP activations of the tile's samples (ping-pong)
 
   // One completion barrier per accumulator: a waiter that lags a step behind still finds "its" phase in flight or just
@@ -252,10 +272,11 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     if (lane == 0) {
       cf_mbar_init(w_full, 1); cf_mbar_init(w_full + 1, 1); cf_mbar_init(mma_done, 1); cf_mbar_init(mma_done1, 1); cf_mbar_init(x_ready, CF_EPI_WARPS);
       cf_mbar_init(x_free, 1); cf_mbar_init(fwd_stored, 1); cf_mbar_init(mlp_done, CF_EPI_WARPS); cf_mbar_init(rs_done, CF_RS_WARPS); cf_mbar_init(rs_done + 1, CF_RS_WARPS);
+      for (int i = 0; i < CF_SLOTS; ++i) { cf_mbar_init(slot_full + i, 1); cf_mbar_init(slot_empty + i, 1); }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(cf_smem_u32(tmem_slot)), "r"(2u * CF_ACC_COLS) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(cf_smem_u32(tmem_slot)), "r"(split ? 512u : 2u * CF_ACC_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the zero fill of X must be visible to the tensor core
@@ -271,34 +292,20 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     // (elect.sync, not `lane == 0`: the compiler then knows a single lane is active and feeds the uniform
     //  datapath directly instead of looping over possibly-divergent lanes)
     if (cf_elect_one()) {
-      auto load_w = [&](int t) {
-        const int nch = (steps.st[t].K + 31) >> 5, buf = t & 1;
-        const CUtensorMap* map = t < L ? &maps.fwd[L - 1 - t] : &maps.bwd[t - L];
-        cf_mbar_expect_tx(w_full + buf, (uint32_t)nch * CF_CHUNK_BYTES);
-        for (int c = 0; c < nch; ++c) cf_tma_load(Wb[buf] + c * CF_CHUNK_BYTES, map, c * 32, 0, w_full + buf);
-      };
-      // the in-kernel MLP forward borrows the weight-tile buffers and their barriers first: wait until it is done with
-      // them, and count the barrier phases it has used up
-      const int used0 = mlp_mode > 0 ? (mlp.L + 1) / 2 : 0, used1 = mlp_mode > 0 ? mlp.L / 2 : 0;
-      if (mlp_mode > 0) {
-        cf_mbar_wait(mlp_done, 0);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      }
-      load_w(0);
       const uint64_t xd = cf_desc(cf_smem_u32(X));
-      const uint64_t wd0 = cf_desc(cf_smem_u32(Wb[0])), wd1 = cf_desc(cf_smem_u32(Wb[1]));
+      const uint32_t w_u = cf_smem_u32(Wb[0]);
+      const uint32_t xlo = tmem_base + (uint32_t)CF_XLO_COL;
+      int slot = 0, round = 0;                              // position in the weight ring (the weight warp walks it in the same order)
 #pragma unroll 1
       for (int t = 0; t < n_steps; ++t) {
         const int buf = t & 1;
         const int K = steps.st[t].K, N = steps.st[t].N;
         const uint32_t n16 = (uint32_t)((N + 15) & ~15);
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((n16 >> 3) << 17) | ((128u >> 4) << 24);
-        const uint64_t bd = buf ? wd1 : wd0;
         const int ksteps = (K + 7) >> 3;
         cf_mbar_wait(x_ready, t & 1);                       // operand X written by the epilogue threads
         CF_STAMP(t, 0);
         if (t >= 2) cf_mbar_wait(rs_done + buf, ((t >> 1) - 1) & 1);     // accumulator t&1 was last read by the row-sum warps in step t-2
-        cf_mbar_wait(w_full + buf, ((t >> 1) + (buf ? used1 : used0)) & 1);           // weight tile landed
         CF_STAMP(t, 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         // descriptor start addresses advance by 32 bytes per 8-wide K step, 16 KB per 32-column chunk (no carry out
@@ -307,14 +314,34 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
 #pragma unroll 1
         for (int c = 0; c * 4 < ksteps; ++c) {              // one 32-column chunk of X / the weight tile = four K steps
           const uint64_t oc = (uint64_t)(c * (CF_CHUNK_BYTES >> 4));
+          const int s_hi = slot;
+          cf_mbar_wait(slot_full + s_hi, round & 1);        // weight chunk landed
+          if (++slot == CF_SLOTS) { slot = 0; ++round; }
+          const uint64_t bh = cf_desc(w_u + (uint32_t)(s_hi * CF_CHUNK_BYTES));
+          int s_lo = 0;
+          uint64_t bl = 0;
+          if (split) {
+            s_lo = slot;
+            cf_mbar_wait(slot_full + s_lo, round & 1);
+            if (++slot == CF_SLOTS) { slot = 0; ++round; }
+            bl = cf_desc(w_u + (uint32_t)(s_lo * CF_CHUNK_BYTES));
+          }
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            if (c * 4 + j < ksteps) cf_mma(dcol, xd + oc + 2 * j, bd + oc + 2 * j, idesc, (c | j) ? 1u : 0u);
+            if (c * 4 + j < ksteps) {
+              cf_mma(dcol, xd + oc + 2 * j, bh + 2 * j, idesc, (c | j) ? 1u : 0u);
+              if (split) {
+                // fp32x3: x = hi + lo, w = hi + lo; the tensor core reads the hi parts out of the fp32 containers
+                cf_mma(dcol, xd + oc + 2 * j, bl + 2 * j, idesc, 1u);                                   // x_hi * w_lo
+                tc::umma_tf32_ts(dcol, xlo + (uint32_t)(c * 32 + j * 8), bh + 2 * j, idesc, 1u);        // x_lo * w_hi
+              }
+            }
+          cf_commit(slot_empty + s_hi);                     // the slot is free once these MMAs have read it
+          if (split) cf_commit(slot_empty + s_lo);
         }
         cf_commit(mma_bar(t));
         CF_STAMP(t, 2);
-        if (t + 1 < n_steps) load_w(t + 1);                 // the other buffer was released by step t-1
-        CF_STAMP(t, 3);
       }
     }
     __syncwarp();
@@ -376,7 +403,33 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // shared memory must outlive the stores
     }
     __syncwarp();
-  } else if (warp_u >= CF_EPI_WARPS + 2) {
+  } else if (warp_u == CF_W_WARP) {
+    // ===== weight warp: one elected lane streams the weight tiles of every step through the ring, as far ahead as
+    // the ring has room (a tile = one 16 KB slot per 32 K columns; fp32x3 brings the lo tile of each chunk as well) =====
+    if (cf_elect_one()) {
+      // the in-kernel MLP forward borrows the ring's memory first: wait until it is done with it
+      if (mlp_mode > 0) {
+        cf_mbar_wait(mlp_done, 0);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      }
+      int slot = 0, round = 0;
+#pragma unroll 1
+      for (int t = 0; t < n_steps; ++t) {
+        const int nch = (steps.st[t].K + 31) >> 5;
+        const CUtensorMap* mh = t < L ? &maps.fwd[L - 1 - t] : &maps.bwd[t - L];
+        const CUtensorMap* ml = t < L ? &maps.fwd_lo[L - 1 - t] : &maps.bwd_lo[t - L];
+        for (int c = 0; c < nch; ++c) {
+          for (int h = 0; h < (split ? 2 : 1); ++h) {
+            cf_mbar_wait(slot_empty + slot, (round & 1) ^ 1);
+            cf_mbar_expect_tx(slot_full + slot, (uint32_t)CF_CHUNK_BYTES);
+            cf_tma_load(Wb[0] + slot * CF_CHUNK_BYTES, h ? ml : mh, c * 32, 0, slot_full + slot);
+            if (++slot == CF_SLOTS) { slot = 0; ++round; }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp_u >= CF_EPI_WARPS + 2 && warp_u < CF_W_WARP) {
     // ===== row-sum warps: rs_l[b, n] += sum over the sample's rows of dQ_l * Q_l  (backward steps through a softplus) =====
     // One warp per TMEM lane quarter, all column blocks of its 32 rows.  They re-read the accumulator of step t while the
     // epilogue warps and the tensor core are already on step t+1 (two accumulators; the control warp waits for rs_done
@@ -483,6 +536,19 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     const int xsw = r & 7;
     constexpr int STRIDE = CF_CW * CF_PARTS;
     const int c_first = part * CF_CW;
+    const uint32_t xlo_t = taddr + (uint32_t)CF_XLO_COL;   // this row's X_lo columns (fp32x3)
+    if (split) {
+      // X_lo starts as zeros (the contractions read whole 8-column K steps of it); each row part clears its half
+      float z16[CF_CW];
+#pragma unroll
+      for (int j = 0; j < CF_CW; ++j) z16[j] = 0.f;
+#pragma unroll
+      for (int c0 = 0; c0 < CF_MAXW / CF_PARTS; c0 += CF_CW) cf_tmem_st16(xlo_t + (uint32_t)(part * (CF_MAXW / CF_PARTS) + c0), z16);
+      cf_tmem_st_wait();
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(CF_EPI) : "memory");
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
 
     // ---- the network itself for the tile's samples: z_{l+1} = act(z_l W_l + b_l), plain fp32 FMAs ----
     // (a few thousand multiply-adds per sample: not worth a launch of its own.  One thread per (sample, output column),
@@ -611,7 +677,9 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             *reinterpret_cast<float4*>(ws + top.q_off + grow * top.ld_out + k) = make_float4(t4[0], t4[1], t4[2], t4[3]);
         }
         cf_sts128(cf_smem_u32(X) + cf_xoff(r, k), t4[0], t4[1], t4[2], t4[3]);
+        if (split) cf_tmem_st4(xlo_t + (uint32_t)k, tc::tf32_lo(t4[0]), tc::tf32_lo(t4[1]), tc::tf32_lo(t4[2]), tc::tf32_lo(t4[3]));
       }
+      if (split) { cf_tmem_st_wait(); asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
       if (lane == 0) cf_mbar_arrive(x_ready);
@@ -636,7 +704,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       const bool add_on = sd.add_off >= 0;
       const bool add_first = sd.add_first != 0;
       const bool sc_on = sd.sc_off >= 0 && !(dbg & 64);
-      const bool do_round = (next_reads_x || do_backward) && !(dbg & 8);  // only what feeds a later TF32 contraction is rounded
+      const bool do_round = (next_reads_x || do_backward) && !(dbg & 8) && !split;  // tf32: what feeds a later contraction is rounded to nearest; fp32x3 keeps fp32 and splits it
       float* const out_p = ws + sd.out_off + grow * sd.out_ld;
       const float* const add_p = ws + sd.add_off + grow * sd.add_ld;   // residual rows
       const float* const sc_p = ws + sd.sc_off + b * sd.sc_ld;      // this row's sample: per-sample scale vector
@@ -728,6 +796,12 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
 #pragma unroll
             for (int j = 0; j < CF_CW; j += 4)
               cf_sts128(xb + (uint32_t)(((j0 + (j >> 2)) ^ xsw) << 4), x[j], x[j + 1], x[j + 2], x[j + 3]);
+            if (split) {
+              float lo[CF_CW];
+#pragma unroll
+              for (int j = 0; j < CF_CW; ++j) lo[j] = tc::tf32_lo(x[j]);
+              cf_tmem_st16(xlo_t + (uint32_t)c0, lo);
+            }
           }
           if (thread_out && row_ok) cf_store_vec16(out_p, c0, sd.out_ld, x);     // padded columns are exact zeros
         };
@@ -746,6 +820,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
       } else if (tma_out) {
         cf_mbar_wait(x_free, t & 1);
       }
+      if (split) cf_tmem_st_wait();
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       if (t + 1 < n_steps || (tma_out && out_on)) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -790,7 +865,7 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
   __syncthreads();
   if (tid == 0) CF_STAMP(3, 7);
   if (warp_u == CF_EPI_WARPS)
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2u * CF_ACC_COLS) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(split ? 512u : 2u * CF_ACC_COLS) : "memory");
 }
 
 // ---- host ---------------------------------------------------------------------------------------------
@@ -799,7 +874,8 @@ typedef CUresult (*PFN_cfEncode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, 
                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const ChainSteps& steps, long long max_rows, const float* ws,
-                             const long long* wp_off, const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp) {
+                             const long long* wp_off, const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp,
+                             const long long* wp_lo_off, const long long* wtp_lo_off) {
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult qres;
   if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
@@ -846,6 +922,10 @@ bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const Chai
     // forward: B operand stored [N = n_in][K = n_out] = padded W_l ; backward: [N = n_out][K = n_in] = padded W_l^T
     if (!mk(&maps->fwd[l], ws + wp_off[l], ly.n_in, ly.n_out, ld_wp[l])) return false;
     if (!mk(&maps->bwd[l], ws + wtp_off[l], ly.n_out, ly.n_in, ld_wtp[l])) return false;
+    if (wp_lo_off && wp_lo_off[l] >= 0) {     // fp32x3: the low parts of the same tiles
+      if (!mk(&maps->fwd_lo[l], ws + wp_lo_off[l], ly.n_in, ly.n_out, ld_wp[l])) return false;
+      if (!mk(&maps->bwd_lo[l], ws + wtp_lo_off[l], ly.n_out, ly.n_in, ld_wtp[l])) return false;
+    }
   }
   return true;
 }
@@ -916,17 +996,15 @@ cudaError_t chain_fused_read_trace(unsigned long long* out) {
 cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, const ChainSteps& steps, float* ws, const float* jt, const float* jn2,
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
                                float* stats, const MlpNetDev& mlp, const float* params, const float* m_in, const float* q_tgt,
-                               const float* qn2, float coef_q, int mlp_mode, cudaStream_t st) {
-  constexpr int SMEM = 2 * 16 * 128 * 4 + 3 * CF_X_BYTES + 128 + CF_PARTS * 128 * 2 * 4 + CF_EPI_WARPS * 8 * CF_TILE_LD * 4 + 1024;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(chain_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+                               const float* qn2, float coef_q, int mlp_mode, int split, cudaStream_t st) {
+  constexpr int SMEM = 2 * 16 * 128 * 4 + 3 * CF_X_BYTES + (16 + 2 * CF_SLOTS) * 8 + CF_PARTS * 128 * 2 * 4 + CF_EPI_WARPS * 8 * CF_TILE_LD * 4 + 1024;
+  static_assert(SMEM <= 232448, "shared memory budget of one CTA");
+  static std::atomic<unsigned long long> attr_mask{0};
+  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(chain_fused_kernel), SMEM, attr_mask);
+  if (e != cudaSuccess) return e;
   const int ctas = (B + net.G - 1) / net.G;
   chain_fused_kernel<<<ctas, CF_THREADS, SMEM, st>>>(maps, net, steps, ws, jt, jn2, idx, seed, B, coef, do_loss, do_backward, stats,
-                                                      mlp, params, m_in, q_tgt, qn2, coef_q, mlp_mode);
+                                                      mlp, params, m_in, q_tgt, qn2, coef_q, mlp_mode, split);
   return cudaGetLastError();
 }
 

@@ -56,7 +56,7 @@ struct GemmGroup { int n; int z_start[GEMM_GROUP_MAX + 1]; GemmOp ops[GEMM_GROUP
 cudaError_t launch_gemm_simt_grouped(GemmGroup& g, int num_sms, cudaStream_t st);
 // the same group on the tensor cores (wgrad_tc.cu): X^T Y with MN-major TF32 UMMA operands, widths <= 128
 bool wgrad_tc_supported(const GemmOp& op);
-cudaError_t launch_wgrad_tc(const GemmGroup& g, int num_sms, cudaStream_t st);
+cudaError_t launch_wgrad_tc(const GemmGroup& g, int split, int num_sms, cudaStream_t st);
 
 // Fused small-network MLP kernels (mlp_fused.cu): one CTA runs every layer for a tile of samples.
 struct MlpLayerDev {
@@ -78,13 +78,15 @@ cudaError_t launch_mlp_forward_fused(const MlpNetDev& net, const float* params, 
 cudaError_t launch_mlp_backward_fused(const MlpNetDev& net, const float* params, float* ws, float* grad, int B,
                                       int with_rowsum, cudaStream_t st);
 // tcgen05 TF32 engine (gemm_tc.cu): both operands K-major (a_sk == b_sk == 1), 16-byte row pitches,
-// epilogue limited to add_pre / scale / add_post.  gemm_tc_supported() says whether an op qualifies.
+// every epilogue term of GemmOp except atomic_c / split-K.  gemm_tc_supported() says whether an op qualifies.
 bool gemm_tc_supported(const GemmOp& op);
-cudaError_t launch_gemm_tc(const GemmOp& op, cudaStream_t st);
+cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st);   // split: fp32x3 (three MMAs on hi/lo operand splits)
 
 // weight staging for the TMA-fed engine: padded copy Wp[n_in][r4(n_out)] and transpose WTp[n_out][r4(n_in)]
-struct PrepEntry { long long koff, wp_off, wtp_off; int n_in, n_out, ld_wp, ld_wtp; };
-struct PrepTable { int n; PrepEntry e[32]; };
+// mode 0 (tf32): both copies rounded to nearest TF32.  mode 1 (fp32x3): exact copies, plus (when wp_lo_off >= 0) the low
+// parts w - trunc_tf32(w) of both for the fused chain kernel, whose weight tiles are not split on chip
+struct PrepEntry { long long koff, wp_off, wtp_off, wp_lo_off, wtp_lo_off; int n_in, n_out, ld_wp, ld_wtp; };
+struct PrepTable { int n, mode; PrepEntry e[32]; };
 cudaError_t launch_prep_weights(const float* params, float* ws, const PrepTable& t, int max_in, int max_out,
                                 cudaStream_t st);
 // rowsum[b,n] = sum_i dq[b*s+i,n]*q[b*s+i,n];  dq[row,n] = dq[row,n]*scale[b,n] + add_post[row,n]   (in place)
@@ -157,15 +159,17 @@ struct ChainStep {
 };
 struct ChainSteps { int n_fwd, n_all; ChainStep st[2 * CHAIN_FUSED_MAX_LAYERS]; };
 // fwd / bwd: weight tiles per layer; out[t]: row-major destination of step t's result (TMA store from the operand tile)
-struct ChainMaps { CUtensorMap fwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap bwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap out[2 * CHAIN_FUSED_MAX_LAYERS]; CUtensorMap top; };
+struct ChainMaps { CUtensorMap fwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap bwd[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap fwd_lo[CHAIN_FUSED_MAX_LAYERS]; CUtensorMap bwd_lo[CHAIN_FUSED_MAX_LAYERS];
+                   CUtensorMap out[2 * CHAIN_FUSED_MAX_LAYERS]; CUtensorMap top; };
 bool chain_fused_supported(const ChainNetDev& net);
 bool chain_fused_encode_maps(ChainMaps* maps, const ChainNetDev& net, const ChainSteps& steps, long long max_rows, const float* ws,
-                             const long long* wp_off, const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp);
+                             const long long* wp_off, const long long* ld_wp, const long long* wtp_off, const long long* ld_wtp,
+                             const long long* wp_lo_off, const long long* wtp_lo_off);
 void chain_fused_build_steps(ChainSteps* steps, const ChainNetDev& net);
 cudaError_t launch_chain_fused(const ChainMaps& maps, const ChainNetDev& net, const ChainSteps& steps, float* ws, const float* jt, const float* jn2,
                                const int* idx, const float* seed, int B, float coef, int do_loss, int do_backward,
                                float* stats, const MlpNetDev& mlp, const float* params, const float* m_in, const float* q_tgt,
-                               const float* qn2, float coef_q, int mlp_mode, cudaStream_t st);
+                               const float* qn2, float coef_q, int mlp_mode, int split, cudaStream_t st);
 
 cudaError_t chain_fused_read_trace(unsigned long long* out);
 

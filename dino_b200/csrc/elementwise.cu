@@ -235,16 +235,25 @@ __global__ void prep_weights_kernel(const float* __restrict__ params, float* __r
   const int k0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
   if (k0 >= e.n_in || n0 >= e.n_out) return;
   const float* W = params + e.koff;
+  const bool lo = e.wp_lo_off >= 0;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
     const int k = k0 + i, n = n0 + threadIdx.x;
-    const float v = (k < e.n_in && n < e.n_out) ? round_tf32_f(W[(long long)k * e.n_out + n]) : 0.f;
+    const float w = (k < e.n_in && n < e.n_out) ? W[(long long)k * e.n_out + n] : 0.f;
+    const float v = t.mode == 0 ? round_tf32_f(w) : w;
     tile[i][threadIdx.x] = v;
-    if (k < e.n_in && n < e.ld_wp) ws[e.wp_off + (long long)k * e.ld_wp + n] = v;
+    if (k < e.n_in && n < e.ld_wp) {
+      ws[e.wp_off + (long long)k * e.ld_wp + n] = v;
+      if (lo) ws[e.wp_lo_off + (long long)k * e.ld_wp + n] = v - __uint_as_float(__float_as_uint(v) & 0xffffe000u);
+    }
   }
   __syncthreads();
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
     const int n = n0 + i, k = k0 + threadIdx.x;
-    if (n < e.n_out && k < e.ld_wtp) ws[e.wtp_off + (long long)n * e.ld_wtp + k] = tile[threadIdx.x][i];
+    if (n < e.n_out && k < e.ld_wtp) {
+      const float v = tile[threadIdx.x][i];
+      ws[e.wtp_off + (long long)n * e.ld_wtp + k] = v;
+      if (lo) ws[e.wtp_lo_off + (long long)n * e.ld_wtp + k] = v - __uint_as_float(__float_as_uint(v) & 0xffffe000u);
+    }
   }
 }
 cudaError_t launch_prep_weights(const float* params, float* ws, const PrepTable& t, int max_in, int max_out,

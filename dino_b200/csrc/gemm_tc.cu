@@ -1,116 +1,101 @@
-// tcgen05 engine: C[M,N] = A[M,K] * Bt[N,K]^T in TF32 with fp32 accumulation in tensor memory.
+// tcgen05 engine: C[M,N] = epilogue(A[M,K] * Bt[N,K]^T), fp32 accumulation in tensor memory, in two arithmetic modes:
+//   tf32   one kind::tf32 MMA per 8-wide K step (operands read as TF32: 10 mantissa bits)
+//   fp32x3 three MMAs per K step on on-chip hi/lo splits of BOTH operands (tc_common.cuh): fp32-grade products
 //
-// This is the Jacobian-chain contraction of the H1 step ([B*s, n] x [n, n'] with a per-sample column
-// scale) on the 5th-generation tensor cores:
-//   * operands are fp32 in HBM (the hardware reads them as TF32), both K-major; 128 x 32 / BN x 32
-//     tiles are brought in by TMA (cp.async.bulk.tensor, SWIZZLE_128B) through a 4-stage mbarrier ring;
-//   * one elected thread issues tcgen05.mma.kind::tf32 (UMMA 128 x BN x 8), accumulators live in TMEM;
-//   * four epilogue warps read TMEM with tcgen05.ld (32 lanes x 32 columns per instruction) and apply
-//     v = (acc + add_pre) * scale[sample] + add_post before storing fp32.
-// Warp roles (192 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 2-5 epilogue.
-// Persistent CTAs (one per SM) walk the 128 x BN output tiles; two TMEM accumulators let the epilogue of a tile overlap
-// the MMAs of the next.  Out-of-range rows/columns/K are zero-filled by TMA and masked
-// in the epilogue, so M, N, K are arbitrary; leading dimensions must be multiples of 4 floats.
+// This is the Jacobian-chain contraction of the H1 step ([B*s, n] x [n, n'] with a per-sample column scale), the
+// data-gradient contraction of the backward chain (with the cross-row d sigma sum fused into the epilogue) and the
+// network's own forward / backward GEMMs (bias + softplus + sigmoid epilogue):
+//   * operands are fp32 in HBM, both K-major; 128 x BK / BN x BK tiles arrive by TMA (cp.async.bulk.tensor, 128- or
+//     64-byte swizzle) through an mbarrier ring;
+//   * fp32x3: four converter warps turn every landed stage into its lo tile (x - trunc_tf32(x)) beside it;
+//   * one elected thread issues tcgen05.mma.kind::tf32 (UMMA 128 x BN x 8), accumulators live in TMEM (two of them:
+//     the epilogue of a tile overlaps the MMAs of the next);
+//   * four epilogue warps read TMEM with tcgen05.ld (32 lanes x 32 columns per instruction), apply
+//         rowsum[b,n] += acc * yref ; v = act(acc + bias) ; v = (v + add_pre) * scale[sample] + add_post
+//     and hand 32 x 32 blocks to TMA stores through a swizzled staging buffer (coalesced, clipped at M and N).
+// Warp roles: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 2-5 epilogue, warps 6-9 converters.
+// Persistent CTAs (one per SM) walk the 128 x BN output tiles.  Out-of-range rows/columns/K are zero-filled by TMA,
+// so M, N, K are arbitrary; leading dimensions must be multiples of 4 floats.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace dino {
 
-constexpr int TC_BM = 128, TC_BK = 32, TC_STAGES = 4, TC_THREADS = 192;
+using namespace tc;
+
+constexpr int TC_BM = 128;
 
 struct TcEpilogue {
   int M, N, K;
-  float* C; long long ldc;
+  int has_c;
   int sdim;
   const float* scale; long long ld_sc;
   const float* add_pre; long long ld_ap;
   const float* add_post; long long ld_apo;
+  const float* bias;
+  int act; float* s_out; long long ld_s;
+  const float* yref; long long ld_y; float* rowsum; long long ld_rs;
   int round_tf32;
 };
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra WAIT_DONE;\n\t"
-      "bra WAIT_LOOP;\n\t"
-      "WAIT_DONE:\n\t"
-      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-      "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// K-major operand tile, 128-byte rows, SWIZZLE_128B: 8-row groups 1024 B apart (SBO), LBO unused (=1).
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-  return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+// 4 floats of a row at column n (n % 4 == 0): vector load when the four lie inside N, guarded scalars at the edge
+__device__ __forceinline__ float4 tc_ld4(const float* row, int n, int N) {
+  if (n + 3 < N) return *reinterpret_cast<const float4*>(row + n);
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (n < N) v.x = row[n];
+  if (n + 1 < N) v.y = row[n + 1];
+  if (n + 2 < N) v.z = row[n + 2];
+  return v;
 }
 
-template <int BN>
-__global__ void __launch_bounds__(TC_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep) {
-  constexpr int A_BYTES = TC_BM * TC_BK * 4, B_BYTES = BN * TC_BK * 4, STAGE_BYTES = A_BYTES + B_BYTES;
+template <int BN, int BK, int STAGES, bool SPLIT>
+__global__ void __launch_bounds__(SPLIT ? 320 : 192, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+               const __grid_constant__ CUtensorMap tma_c, const TcEpilogue ep) {
+  constexpr int A_BYTES = TC_BM * BK * 4, B_BYTES = BN * BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
+  constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
   constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;           // columns of one accumulator
   constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;               // two accumulators: the epilogue of tile i overlaps the MMAs of tile i+1
-  // instruction descriptor: D fp32, A/B tf32, both K-major, N = BN, M = 128
-  constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+  constexpr int EPI_BUF = 32 * 128;                          // one 32 x 32 fp32 block, 128-byte rows, SWIZZLE_128B
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + TC_STAGES * STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + TC_STAGES;
-  uint64_t* tmem_full_bar = empty_bar + TC_STAGES;          // [2] accumulator complete
-  uint64_t* tmem_empty_bar = tmem_full_bar + 2;             // [2] accumulator read out by the four epilogue warps
+  uint8_t* epi_stage = smem + STAGES * STAGE_BYTES;          // [4 warps][2][EPI_BUF]
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_stage + 4 * 2 * EPI_BUF);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* conv_bar = empty_bar + STAGES;                   // lo tiles of the stage written (fp32x3)
+  uint64_t* tmem_full_bar = conv_bar + STAGES;               // [2] accumulator complete
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;              // [2] accumulator read out by the four epilogue warps
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nkb = (ep.K + TC_BK - 1) / TC_BK;
+  const int nkb = (ep.K + BK - 1) / BK;
   // persistent: this CTA walks the output tiles blockIdx.x, blockIdx.x + gridDim.x, ... (column tile fastest)
   const int tiles_n = (ep.N + BN - 1) / BN, n_tiles = tiles_n * ((ep.M + TC_BM - 1) / TC_BM);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+    if (ep.has_c) asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_c) : "memory");
   }
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < TC_STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); }
+      for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); mbar_init(conv_bar + i, 4); }
       mbar_init(tmem_full_bar, 1); mbar_init(tmem_full_bar + 1, 1);
       mbar_init(tmem_empty_bar, 4); mbar_init(tmem_empty_bar + 1, 4);
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      fence_mbar_init();
     }
     __syncwarp();
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  tc_fence_before();
   __syncthreads();
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -120,107 +105,168 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int m0 = (tile / tiles_n) * TC_BM, n0 = (tile % tiles_n) * BN;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
-          const int st = it % TC_STAGES;
-          const uint32_t ph = (it / TC_STAGES) & 1;
+          const int st = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(empty_bar + st, ph ^ 1);
-          mbar_expect_tx(full_bar + st, STAGE_BYTES);
+          mbar_expect_tx(full_bar + st, RAW_BYTES);
           uint8_t* sa = smem + st * STAGE_BYTES;
-          tma_load_2d(sa, &tma_a, kb * TC_BK, m0, full_bar + st);
-          tma_load_2d(sa + A_BYTES, &tma_b, kb * TC_BK, n0, full_bar + st);
+          tma_load_2d(sa, &tma_a, kb * BK, m0, full_bar + st);
+          tma_load_2d(sa + A_BYTES, &tma_b, kb * BK, n0, full_bar + st);
         }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
+      const uint32_t idesc = idesc_tf32(BN);
       int it = 0, i = 0;
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
         const int acc = i & 1;
         mbar_wait(tmem_empty_bar + acc, ((i >> 1) & 1) ^ 1);      // the epilogue has drained this accumulator (two tiles ago)
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)acc * ACC_COLS;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
-          const int st = it % TC_STAGES;
-          const uint32_t ph = (it / TC_STAGES) & 1;
-          mbar_wait(full_bar + st, ph);
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const int st = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait((SPLIT ? conv_bar : full_bar) + st, ph);
+          tc_fence_after();
           const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
-          const uint64_t adesc = umma_desc_sw128(sa), bdesc = umma_desc_sw128(sa + A_BYTES);
+          const uint64_t adesc = BK == 32 ? desc_k_sw128(sa) : desc_k_sw64(sa);
+          const uint64_t bdesc = BK == 32 ? desc_k_sw128(sa + A_BYTES) : desc_k_sw64(sa + A_BYTES);
+          constexpr uint64_t LO = RAW_BYTES >> 4;    // the lo tiles sit RAW_BYTES above their sources
 #pragma unroll
-          for (int k = 0; k < TC_BK / 8; ++k)        // UMMA_K = 8 tf32 = 32 bytes = 2 descriptor units
-            umma_tf32(tmem_d, adesc + 2 * k, bdesc + 2 * k, IDESC, (kb > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < BK / 8; ++k) {         // UMMA_K = 8 tf32 = 32 bytes = 2 descriptor units
+            umma_tf32(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            if (SPLIT) {
+              umma_tf32(tmem_d, adesc + LO + 2 * k, bdesc + 2 * k, idesc, 1u);
+              umma_tf32(tmem_d, adesc + 2 * k, bdesc + LO + 2 * k, idesc, 1u);
+            }
+          }
           umma_commit(empty_bar + st);               // frees the smem stage once these MMAs have read it
         }
         umma_commit(tmem_full_bar + acc);            // accumulator complete
       }
     }
-  } else {
-    // ===== epilogue: TMEM -> registers -> global, one accumulator behind the MMA issuer =====
-    const int q = warp & 3;                        // TMEM lane quarter this warp may access
-    int i = 0;
-#pragma unroll 1
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
-    const int m0 = (tile / tiles_n) * TC_BM, n0 = (tile % tiles_n) * BN;
-    const int acc = i & 1;
-    mbar_wait(tmem_full_bar + acc, (i >> 1) & 1);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const int row = m0 + q * 32 + lane;
-    const bool row_ok = row < ep.M;
-    const long long b = row_ok ? row / ep.sdim : 0;
-    float* crow = ep.C + (long long)row * ep.ldc;
-    const float* sc = ep.scale ? ep.scale + b * ep.ld_sc : nullptr;
-    const float* ap = ep.add_pre ? ep.add_pre + (long long)row * ep.ld_ap : nullptr;
-    const float* apo = ep.add_post ? ep.add_post + (long long)row * ep.ld_apo : nullptr;
-#pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
-      if (n0 + c0 >= ep.N) break;                  // warp-uniform
-      uint32_t r[32];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * ACC_COLS + (uint32_t)c0;
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-            "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-            "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-            "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-          : "r"(taddr));
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      if (row_ok) {
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const int n = n0 + c0 + j;
-          if (n + 3 < ep.N) {
-            float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                                   __uint_as_float(r[j + 3]));
-            if (ap) { const float4 t = *reinterpret_cast<const float4*>(ap + n); v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w; }
-            if (sc) { const float4 t = *reinterpret_cast<const float4*>(sc + n); v.x *= t.x; v.y *= t.y; v.z *= t.z; v.w *= t.w; }
-            if (apo) { const float4 t = *reinterpret_cast<const float4*>(apo + n); v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w; }
-            if (ep.round_tf32) { v.x = round_tf32_f(v.x); v.y = round_tf32_f(v.y); v.z = round_tf32_f(v.z); v.w = round_tf32_f(v.w); }
-            *reinterpret_cast<float4*>(crow + n) = v;
-          } else {
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              if (n + u < ep.N) {
-                float v = __uint_as_float(r[j + u]);
-                if (ap) v += ap[n + u];
-                if (sc) v *= sc[n + u];
-                if (apo) v += apo[n + u];
-                crow[n + u] = ep.round_tf32 ? round_tf32_f(v) : v;
-              }
-            }
-          }
+  } else if (warp >= 6) {
+    // ===== converters (fp32x3): lo tile of every landed stage =====
+    if (SPLIT) {
+      const int t = threadIdx.x - 192;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int st = it % STAGES;
+          mbar_wait(full_bar + st, (it / STAGES) & 1);
+          const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
+          split_lo_tile(sa, sa + RAW_BYTES, RAW_BYTES, t, 128);
+          fence_async_smem();                        // generic-proxy writes -> visible to the tensor core
+          __syncwarp();
+          if (lane == 0) mbar_arrive(conv_bar + st);
         }
       }
     }
-    // this warp is done reading the accumulator: hand it back to the MMA issuer
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncwarp();
-    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(tmem_empty_bar + acc)) : "memory");
+  } else {
+    // ===== epilogue: TMEM -> registers -> staging -> TMA store, one accumulator behind the MMA issuer =====
+    const int q = warp & 3;                        // TMEM lane quarter this warp may access
+    const uint32_t my_stage = smem_u32(epi_stage + q * 2 * EPI_BUF);
+    const uint32_t sw = (uint32_t)(lane & 7);
+    int i = 0, n_stores = 0;
+#pragma unroll 1
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
+      const int m0 = (tile / tiles_n) * TC_BM, n0 = (tile % tiles_n) * BN;
+      const int acc = i & 1;
+      mbar_wait(tmem_full_bar + acc, (i >> 1) & 1);
+      tc_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < ep.M;
+      const int b = row_ok ? row / ep.sdim : 0;
+      const float* sc = ep.scale ? ep.scale + (long long)b * ep.ld_sc : nullptr;
+      const float* ap = ep.add_pre ? ep.add_pre + (long long)row * ep.ld_ap : nullptr;
+      const float* apo = ep.add_post ? ep.add_post + (long long)row * ep.ld_apo : nullptr;
+      const float* yr = ep.yref ? ep.yref + (long long)row * ep.ld_y : nullptr;
+      float* so = ep.s_out ? ep.s_out + (long long)row * ep.ld_s : nullptr;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        if (n0 + c0 >= ep.N) break;                  // warp-uniform
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * ACC_COLS + (uint32_t)c0, v);
+        if (yr) {
+          // d sigma term: rowsum[sample, n] += sum over the sample's chain rows of acc * yref  (segmented over the
+          // samples under this warp's 32 rows; lane j ends up with column j)
+          float p[32];
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 y = row_ok ? tc_ld4(yr, n0 + c0 + j, ep.N) : make_float4(0.f, 0.f, 0.f, 0.f);
+            p[j] = v[j] * y.x; p[j + 1] = v[j + 1] * y.y; p[j + 2] = v[j + 2] * y.z; p[j + 3] = v[j + 3] * y.w;
+          }
+          const int r_first = m0 + q * 32;
+          if (r_first < ep.M) {
+            const int b_lo = r_first / ep.sdim, b_hi = min(r_first + 31, ep.M - 1) / ep.sdim;
+            for (int bb = b_lo; bb <= b_hi; ++bb) {
+              float mm[32];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) mm[j] = (row_ok && b == bb) ? p[j] : 0.f;
+              const float tot = colsum32(mm, lane);
+              if (n0 + c0 + lane < ep.N) atomicAdd(ep.rowsum + (long long)bb * ep.ld_rs + n0 + c0 + lane, tot);
+            }
+          }
+        }
+        if (!ep.has_c && !so) continue;
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const int n = n0 + c0 + j;
+            if (n < ep.N) {
+              float4 x = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              if (ep.bias) { const float4 t = tc_ld4(ep.bias, n, ep.N); x.x += t.x; x.y += t.y; x.z += t.z; x.w += t.w; }
+              if (ep.act) {
+                // sigmoid and softplus from one exponential: e = exp(-|x|)
+                float xs[4] = {x.x, x.y, x.z, x.w}, sg[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  const float e = expf(-fabsf(xs[u])), r1 = 1.f / (1.f + e);
+                  sg[u] = xs[u] >= 0.f ? r1 : e * r1;
+                  xs[u] = fmaxf(xs[u], 0.f) + log1pf(e);
+                }
+                if (so) {
+                  if (n + 3 < ep.N) *reinterpret_cast<float4*>(so + n) = make_float4(sg[0], sg[1], sg[2], sg[3]);
+                  else {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) if (n + u < ep.N) so[n + u] = sg[u];
+                  }
+                }
+                x = make_float4(xs[0], xs[1], xs[2], xs[3]);
+              }
+              if (ap) { const float4 t = tc_ld4(ap, n, ep.N); x.x += t.x; x.y += t.y; x.z += t.z; x.w += t.w; }
+              if (sc) { const float4 t = tc_ld4(sc, n, ep.N); x.x *= t.x; x.y *= t.y; x.z *= t.z; x.w *= t.w; }
+              if (apo) { const float4 t = tc_ld4(apo, n, ep.N); x.x += t.x; x.y += t.y; x.z += t.z; x.w += t.w; }
+              if (ep.round_tf32) { x.x = round_tf32_f(x.x); x.y = round_tf32_f(x.y); x.z = round_tf32_f(x.z); x.w = round_tf32_f(x.w); }
+              v[j] = x.x; v[j + 1] = x.y; v[j + 2] = x.z; v[j + 3] = x.w;
+            }
+          }
+        }
+        if (ep.has_c) {
+          // the block leaves through a TMA store (rows >= M and columns >= N are clipped by the hardware)
+          const uint32_t buf = my_stage + (uint32_t)((n_stores & 1) * EPI_BUF);
+          if (n_stores >= 2 && lane == 0) tma_store_wait_read<1>();   // the store that last read this buffer is done with it
+          __syncwarp();
+          const uint32_t rowb = buf + (uint32_t)(lane * 128);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) sts128(rowb + ((((uint32_t)j) ^ sw) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) { tma_store_2d(&tma_c, buf, n0 + c0, m0 + q * 32); tma_store_commit(); }
+          ++n_stores;
+        }
+      }
+      // this warp is done reading the accumulator: hand it back to the MMA issuer
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
     }
+    if (lane == 0) tma_store_wait_all<0>();          // shared memory must outlive the stores
   }
   // ===== teardown =====
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  tc_fence_before();
   __syncthreads();
   if (warp == 1)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
@@ -244,68 +290,132 @@ static PFN_tmapEncodeTiled get_encode() {
   return g_encode;
 }
 
-// 2-D fp32 row-major [rows, cols] (leading dimension ld floats) -> tiles of box_rows x 32 columns.
-static bool make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long ld, int box_rows) {
+cudaError_t tc_set_smem_once(const void* func, int bytes, std::atomic<unsigned long long>& mask) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (mask.load(std::memory_order_acquire) & bit) return cudaSuccess;
+  e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return e;
+  mask.fetch_or(bit, std::memory_order_release);
+  return cudaSuccess;
+}
+
+int tc_current_num_sms() {
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  int n = cache[dev & 63].load(std::memory_order_relaxed);
+  if (n > 0) return n;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  cache[dev & 63].store(n, std::memory_order_relaxed);
+  return n;
+}
+
+namespace {
+struct MapKey {
+  const void* base; unsigned long long inner, outer; long long ld; unsigned bi, bo; int sw;
+  bool operator==(const MapKey& o) const {
+    return base == o.base && inner == o.inner && outer == o.outer && ld == o.ld && bi == o.bi && bo == o.bo && sw == o.sw;
+  }
+};
+struct MapSlot { bool used; MapKey key; CUtensorMap map; };
+constexpr int MAP_CACHE = 256;
+}  // namespace
+
+bool tc_make_map(CUtensorMap* out, const float* base, unsigned long long inner, unsigned long long outer, long long ld,
+                 unsigned box_inner, unsigned box_outer, int swizzle) {
+  static thread_local MapSlot cache[MAP_CACHE];      // direct-mapped; device addresses are unique across devices (UVA)
+  const MapKey key{base, inner, outer, ld, box_inner, box_outer, swizzle};
+  unsigned long long h = reinterpret_cast<uintptr_t>(base) >> 4;
+  h = h * 0x9E3779B97F4A7C15ull + inner * 1315423911ull + outer * 2654435761ull + (unsigned long long)ld * 97 + box_inner * 31 + box_outer * 7 + swizzle;
+  MapSlot& s = cache[(h >> 20) % MAP_CACHE];
+  if (s.used && s.key == key) { *out = s.map; return true; }
   PFN_tmapEncodeTiled enc = get_encode();
   if (!enc) return false;
-  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
   cuuint64_t gstride[1] = {(cuuint64_t)ld * sizeof(float)};
-  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1, 1};
-  return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estr,
-             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  if (enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estr,
+          CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return false;
+  s.used = true; s.key = key; s.map = *out;
+  return true;
 }
 
 bool gemm_tc_supported(const GemmOp& op) {
   if (op.a_sk != 1 || op.b_sk != 1) return false;                  // both operands K-major
   if (op.a_mod > 0 || op.b_kmod > 0) return false;
-  if (op.rowsum || op.act || op.bias || op.atomic_c || op.k_per_split) return false;
-  if (op.C == nullptr || (op.ldc & 3)) return false;
+  if (op.atomic_c || op.k_per_split) return false;
+  if (op.C == nullptr && op.rowsum == nullptr) return false;
+  if (op.C && ((op.ldc & 3) || (reinterpret_cast<uintptr_t>(op.C) & 15))) return false;
   if ((op.a_sm & 3) || (op.b_sn & 3)) return false;                // TMA: 16-byte row pitch
-  if ((reinterpret_cast<uintptr_t>(op.A) & 15) || (reinterpret_cast<uintptr_t>(op.B) & 15) ||
-      (reinterpret_cast<uintptr_t>(op.C) & 15)) return false;
+  if ((reinterpret_cast<uintptr_t>(op.A) & 15) || (reinterpret_cast<uintptr_t>(op.B) & 15)) return false;
   if (op.scale && ((op.ld_sc & 3) || (reinterpret_cast<uintptr_t>(op.scale) & 15))) return false;
   if (op.add_pre && ((op.ld_ap & 3) || (reinterpret_cast<uintptr_t>(op.add_pre) & 15))) return false;
   if (op.add_post && ((op.ld_apo & 3) || (reinterpret_cast<uintptr_t>(op.add_post) & 15))) return false;
+  if (op.bias && (reinterpret_cast<uintptr_t>(op.bias) & 15)) return false;
+  if (op.s_out && ((op.ld_s & 3) || (reinterpret_cast<uintptr_t>(op.s_out) & 15))) return false;
+  if (op.rowsum && (!op.yref || (op.ld_y & 3) || (reinterpret_cast<uintptr_t>(op.yref) & 15))) return false;
+  if (op.act && !op.C) return false;
   return op.M > 0 && op.N > 0 && op.K > 0;
 }
 
-template <int BN>
+template <int BN, int BK, int STAGES, bool SPLIT>
 static cudaError_t launch_tc(const GemmOp& op, cudaStream_t st) {
-  CUtensorMap ma, mb;
+  CUtensorMap ma, mb, mc;
+  const int sw_in = BK == 32 ? (int)CU_TENSOR_MAP_SWIZZLE_128B : (int)CU_TENSOR_MAP_SWIZZLE_64B;
   // A[M,K] rows of a_sm floats; B operand is stored [N][K] (element (k,n) at n*b_sn + k)
-  if (!make_map(&ma, op.A, op.M, op.K, op.a_sm, TC_BM) || !make_map(&mb, op.B, op.N, op.K, op.b_sn, BN))
+  if (!tc_make_map(&ma, op.A, op.K, op.M, op.a_sm, BK, TC_BM, sw_in) || !tc_make_map(&mb, op.B, op.K, op.N, op.b_sn, BK, BN, sw_in))
     return cudaErrorInvalidValue;
+  if (op.C) {
+    if (!tc_make_map(&mc, op.C, op.N, op.M, op.ldc, 32, 32, (int)CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+  } else {
+    mc = ma;
+  }
   TcEpilogue ep;
-  ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.C = op.C; ep.ldc = op.ldc; ep.sdim = op.sdim > 0 ? op.sdim : 1;
+  ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.has_c = op.C ? 1 : 0; ep.sdim = op.sdim > 0 ? op.sdim : 1;
   ep.scale = op.scale; ep.ld_sc = op.ld_sc; ep.add_pre = op.add_pre; ep.ld_ap = op.ld_ap;
-  ep.add_post = op.add_post; ep.ld_apo = op.ld_apo; ep.round_tf32 = op.round_tf32;
-  constexpr int SMEM = TC_STAGES * (TC_BM * TC_BK * 4 + BN * TC_BK * 4) + 256 + 1024;
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-    if (e != cudaSuccess) return e;
-    attr_done = true;
-  }
+  ep.add_post = op.add_post; ep.ld_apo = op.ld_apo; ep.bias = op.bias; ep.act = op.act;
+  ep.s_out = op.act ? op.s_out : nullptr; ep.ld_s = op.ld_s;
+  ep.yref = op.rowsum ? op.yref : nullptr; ep.ld_y = op.ld_y; ep.rowsum = op.rowsum; ep.ld_rs = op.ld_rs;
+  ep.round_tf32 = SPLIT ? 0 : op.round_tf32;
+  constexpr int RAW = (TC_BM + BN) * BK * 4;
+  constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + 4 * 2 * 32 * 128 + 256 + 1024;
+  static_assert(SMEM <= 232448, "shared memory budget of one CTA");
+  static std::atomic<unsigned long long> attr_mask{0};
+  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(gemm_tc_kernel<BN, BK, STAGES, SPLIT>), SMEM, attr_mask);
+  if (e != cudaSuccess) return e;
   // persistent CTAs, one per SM: each walks its share of the 128 x BN output tiles
-  static int num_sms = 0;
-  if (num_sms == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || num_sms <= 0) num_sms = 148;
-  }
+  const int num_sms = tc_current_num_sms();
   const long long n_tiles = (long long)((op.N + BN - 1) / BN) * ((op.M + TC_BM - 1) / TC_BM);
   const int grid = (int)(n_tiles < num_sms ? n_tiles : num_sms);
-  gemm_tc_kernel<BN><<<grid, TC_THREADS, SMEM, st>>>(ma, mb, ep);
+  gemm_tc_kernel<BN, BK, STAGES, SPLIT><<<grid, SPLIT ? 320 : 192, SMEM, st>>>(ma, mb, mc, ep);
   return cudaGetLastError();
 }
 
-cudaError_t launch_gemm_tc(const GemmOp& op, cudaStream_t st) {
+cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st) {
   if (!gemm_tc_supported(op)) return cudaErrorNotSupported;
-  if (op.N <= 64) return launch_tc<64>(op, st);
-  if (op.N <= 128) return launch_tc<128>(op, st);
-  return launch_tc<256>(op, st);
+  static const int variant = getenv("DINO_TC_VARIANT") ? atoi(getenv("DINO_TC_VARIANT")) : 0;   // read once per process
+  const int num_sms = tc_current_num_sms();
+  const long long m_tiles = (op.M + TC_BM - 1) / TC_BM;
+  // widest tile that still gives every SM work (small-M contractions: the network's own forward / backward)
+  int bn = 256;
+  if (op.N <= 128 || m_tiles * ((op.N + 255) / 256) * 2 <= num_sms) bn = 128;
+  if (op.N <= 64 || (bn == 128 && m_tiles * ((op.N + 127) / 128) * 2 <= num_sms)) bn = 64;
+  if (split) {
+    if (bn == 64) return launch_tc<64, 32, 4, true>(op, st);
+    if (bn == 128) return launch_tc<128, 32, 3, true>(op, st);
+    if (variant == 1) return launch_tc<256, 32, 2, true>(op, st);
+    if (variant == 2) return launch_tc<128, 32, 3, true>(op, st);
+    return launch_tc<256, 16, 4, true>(op, st);
+  }
+  if (bn == 64) return launch_tc<64, 32, 4, false>(op, st);
+  if (bn == 128) return launch_tc<128, 32, 4, false>(op, st);
+  return launch_tc<256, 32, 4, false>(op, st);
 }
 
 }  // namespace dino

@@ -59,7 +59,8 @@ struct LayerPlan {
   int n_in, n_out, act, has_bias, trainable, skip_from;
   long long koff, boff;      // offsets in the parameter arena (floats)
   long long z_off, sg_off, q_off, rs_off;   // workspace offsets (floats); -1 when absent
-  long long wp_off, wtp_off, ld_wp, ld_wtp; // TF32 mode: padded W [n_in][ld_wp] and W^T [n_out][ld_wtp]
+  long long wp_off, wtp_off, ld_wp, ld_wtp; // tensor-core modes: padded W [n_in][ld_wp] and W^T [n_out][ld_wtp]
+  long long wp_lo_off, wtp_lo_off;          // fp32x3 + fused chain kernel: their low parts
   long long dr_off;          // dR_{l+1} = gradient wrt the chain state above this layer [B*s, ld_out]; -1 for the top layer
   long long da_off;          // da_l [B, ld_out] (fused MLP backward keeps every layer's for the grouped weight gradient)
   long long ld_out;          // r4(n_out)
@@ -69,6 +70,8 @@ struct LayerPlan {
 struct DinoPlan {
   int device, num_sms;
   int d_in, d_out, L, jac_mode, s, max_batch, precision;
+  bool tc;                   // contractions on the tcgen05 engine (tf32 / fp32x3)
+  int split;                 // 1: fp32x3 (three MMAs on hi/lo operand splits)
   std::vector<LayerPlan> layers;
   long long n_params;
   bool seed_shared;          // FULL / OUT_REDUCED
@@ -106,7 +109,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   if (!spec || !out) return fail("dino_plan_create: null argument");
   if (spec->n_layers < 1 || spec->d_in < 1 || spec->max_batch < 1) return fail("dino_plan_create: bad sizes");
   if (spec->jac_mode < DINO_JAC_NONE || spec->jac_mode > DINO_JAC_SKETCHED) return fail("dino_plan_create: bad jac_mode");
-  if (spec->precision != DINO_PREC_FP32 && spec->precision != DINO_PREC_TF32)
+  if (spec->precision != DINO_PREC_FP32 && spec->precision != DINO_PREC_TF32 && spec->precision != DINO_PREC_FP32X3)
     return fail("dino_plan_create: bad precision");
   int ndev = 0;
   DINO_CUDA(cudaGetDeviceCount(&ndev));
@@ -123,6 +126,8 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   p->jac_mode = spec->jac_mode;
   p->max_batch = spec->max_batch;
   p->precision = spec->precision;
+  p->tc = spec->precision != DINO_PREC_FP32;
+  p->split = spec->precision == DINO_PREC_FP32X3 ? 1 : 0;
   p->ws = nullptr;
   p->side = nullptr; p->ev_fork = p->ev_join = p->ev_prep = nullptr;
   p->profile = false; p->prof_ms = 0.0; p->prof_n = 0; p->ev_pending = false; p->ev0 = p->ev1 = nullptr;
@@ -166,7 +171,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   const LayerPlan& last = p->layers[p->L - 1];
   p->top_materialised = p->jac_mode != DINO_JAC_NONE &&
                         (!p->seed_shared || last.act == DINO_ACT_SOFTPLUS || last.skip_from >= 0 ||
-                         p->precision == DINO_PREC_TF32 /* TMA-addressable operand for the tensor-core weight gradient */);
+                         p->tc /* TMA-addressable operand for the tensor-core weight gradient */);
 
   // ---- workspace layout ------------------------------------------------------------------------
   const long long Bm = p->max_batch, Ms = Bm * (long long)p->s;
@@ -225,14 +230,15 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   }
   p->prep.n = 0;
   p->max_in = p->max_out = 1;
-  for (auto& lp : p->layers) { lp.wp_off = lp.wtp_off = -1; lp.ld_wp = r4(lp.n_out); lp.ld_wtp = r4(lp.n_in); }
-  if (p->precision == DINO_PREC_TF32 && p->jac_mode != DINO_JAC_NONE) {
-    if (p->L > 32) { delete p; return fail("dino_plan_create: TF32 mode supports at most 32 layers"); }
+  p->prep.mode = p->split;
+  for (auto& lp : p->layers) { lp.wp_off = lp.wtp_off = lp.wp_lo_off = lp.wtp_lo_off = -1; lp.ld_wp = r4(lp.n_out); lp.ld_wtp = r4(lp.n_in); }
+  if (p->tc && p->jac_mode != DINO_JAC_NONE) {
+    if (p->L > 32) { delete p; return fail("dino_plan_create: the tensor-core modes support at most 32 layers"); }
     for (auto& lp : p->layers) {
       lp.wp_off = take((long long)lp.n_in * lp.ld_wp);
       lp.wtp_off = take((long long)lp.n_out * lp.ld_wtp);
       PrepEntry& e = p->prep.e[p->prep.n++];
-      e.koff = lp.koff; e.wp_off = lp.wp_off; e.wtp_off = lp.wtp_off;
+      e.koff = lp.koff; e.wp_off = lp.wp_off; e.wtp_off = lp.wtp_off; e.wp_lo_off = e.wtp_lo_off = -1;
       e.n_in = lp.n_in; e.n_out = lp.n_out; e.ld_wp = (int)lp.ld_wp; e.ld_wtp = (int)lp.ld_wtp;
       if (lp.n_in > p->max_in) p->max_in = lp.n_in;
       if (lp.n_out > p->max_out) p->max_out = lp.n_out;
@@ -240,7 +246,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   }
   p->chain_fused = false;
   p->mlp_in_chain = false;
-  if (p->precision == DINO_PREC_TF32 && (p->jac_mode == DINO_JAC_FULL || p->jac_mode == DINO_JAC_OUT_REDUCED) &&
+  if (p->tc && (p->jac_mode == DINO_JAC_FULL || p->jac_mode == DINO_JAC_OUT_REDUCED) &&
       p->L <= CHAIN_FUSED_MAX_LAYERS && getenv("DINO_B200_NO_FUSED_CHAIN") == nullptr) {
     ChainNetDev& c = p->chain;
     memset(&c, 0, sizeof(c));
@@ -259,6 +265,15 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     if (p->chain_fused) chain_fused_build_steps(&p->chain_steps, c);
     p->mlp_in_chain = p->chain_fused && p->mlp_fused && !c.has_skip && p->L <= MLP_FUSED_MAX_LAYERS &&
                       getenv("DINO_B200_NO_MLP_IN_CHAIN") == nullptr;
+    if (p->chain_fused && p->split) {
+      // the fused kernel takes its weight tiles ready-made: it needs their low parts from memory as well
+      for (int l = 0; l < p->L; ++l) {
+        LayerPlan& lp = p->layers[l];
+        lp.wp_lo_off = take((long long)lp.n_in * lp.ld_wp);
+        lp.wtp_lo_off = take((long long)lp.n_out * lp.ld_wtp);
+        p->prep.e[l].wp_lo_off = lp.wp_lo_off; p->prep.e[l].wtp_lo_off = lp.wtp_lo_off;
+      }
+    }
   }
   p->ws_floats = off;
   if (p->chain_fused && getenv("DINO_B200_NO_SIDE_STREAM") == nullptr) {
@@ -300,11 +315,14 @@ extern "C" int dino_plan_bind_workspace(DinoPlan* plan, void* d_ws, size_t bytes
   plan->ws = static_cast<float*>(d_ws);
   if (plan->chain_fused) {
     long long wp[CHAIN_FUSED_MAX_LAYERS], lwp[CHAIN_FUSED_MAX_LAYERS], wtp[CHAIN_FUSED_MAX_LAYERS], lwtp[CHAIN_FUSED_MAX_LAYERS];
+    long long wpl[CHAIN_FUSED_MAX_LAYERS], wtpl[CHAIN_FUSED_MAX_LAYERS];
     for (int l = 0; l < plan->L; ++l) {
       wp[l] = plan->layers[l].wp_off; lwp[l] = plan->layers[l].ld_wp;
       wtp[l] = plan->layers[l].wtp_off; lwtp[l] = plan->layers[l].ld_wtp;
+      wpl[l] = plan->layers[l].wp_lo_off; wtpl[l] = plan->layers[l].wtp_lo_off;
     }
-    if (!chain_fused_encode_maps(&plan->chain_maps, plan->chain, plan->chain_steps, (long long)plan->max_batch * plan->s, plan->ws, wp, lwp, wtp, lwtp))
+    if (!chain_fused_encode_maps(&plan->chain_maps, plan->chain, plan->chain_steps, (long long)plan->max_batch * plan->s, plan->ws, wp, lwp, wtp, lwtp,
+                                 wpl, wtpl))
       return fail("dino_plan_bind_workspace: cuTensorMapEncodeTiled failed for the fused chain kernel");
   }
   if (plan->off_ident >= 0)
@@ -316,6 +334,9 @@ extern "C" int dino_plan_bind_workspace(DinoPlan* plan, void* d_ws, size_t bytes
 static int check_call(const DinoPlan* p, const float* params, const DinoBatch* b, int B, bool need_targets) {
   if (!p || !params || !b) return fail("null argument");
   if (!p->ws) return fail("workspace not bound (dino_plan_bind_workspace)");
+  int cur = -1;
+  if (cudaGetDevice(&cur) != cudaSuccess || cur != p->device)
+    return fail("the plan belongs to CUDA device " + std::to_string(p->device) + " but device " + std::to_string(cur) + " is current");
   if (B < 1 || B > p->max_batch) return fail("batch size outside [1, max_batch]");
   if (!b->m) return fail("batch.m is null");
   if (p->jac_mode == DINO_JAC_SKETCHED && (!b->U || !b->V)) return fail("sketched Jacobian needs batch.U and batch.V");
@@ -327,11 +348,17 @@ static int check_call(const DinoPlan* p, const float* params, const DinoBatch* b
   return 0;
 }
 
-static int gemm(const DinoPlan* p, const GemmOp& op, cudaStream_t st) {
-  if (p->precision == DINO_PREC_TF32 && gemm_tc_supported(op)) {
-    DINO_LAUNCH(launch_gemm_tc(op, st));
+// force_split: the network's own (small) GEMMs keep fp32-grade products in the tf32 mode too
+static int gemm(const DinoPlan* p, const GemmOp& op, cudaStream_t st, bool force_split = false) {
+  if (p->tc && gemm_tc_supported(op)) {
+    DINO_LAUNCH(launch_gemm_tc(op, force_split ? 1 : p->split, st));
     return 0;
   }
+  DINO_LAUNCH(launch_gemm_simt(op, p->num_sms, st));
+  return 0;
+}
+
+static int gemm_simt_only(const DinoPlan* p, const GemmOp& op, cudaStream_t st) {
   DINO_LAUNCH(launch_gemm_simt(op, p->num_sms, st));
   return 0;
 }
@@ -342,6 +369,10 @@ static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b,
     DINO_LAUNCH(launch_mlp_forward_fused(p->mlp, params, ws, b->m, b->idx, B, st));
     return 0;
   }
+  // wide networks: the network's own GEMMs run on the tcgen05 engine too (always with fp32-grade products); they read
+  // the staged weight copies, so those are written first
+  const bool tc_mlp = p->tc && p->prep.n > 0 && !p->chain_fused;
+  if (tc_mlp) DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
   DINO_LAUNCH(launch_gather_rows(b->m, b->idx, B, p->d_in, p->d_in, ws + p->off_z0, p->ld_in, st));
   const float* zin = ws + p->off_z0;
   long long ld_zin = p->ld_in;
@@ -349,7 +380,8 @@ static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b,
     const LayerPlan& lp = p->layers[l];
     GemmOp op = gemm_op_zero();
     op.A = zin; op.a_sm = ld_zin; op.a_sk = 1;
-    op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1;
+    if (tc_mlp) { op.B = ws + lp.wtp_off; op.b_sk = 1; op.b_sn = lp.ld_wtp; }   // K-major W^T for the tcgen05 engine
+    else { op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1; }
     op.M = B; op.N = lp.n_out; op.K = lp.n_in;
     op.C = ws + lp.z_off; op.ldc = lp.ld_out;
     op.bias = lp.has_bias ? params + lp.boff : nullptr;
@@ -360,7 +392,7 @@ static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b,
       op.add_post = j == 0 ? ws + p->off_z0 : ws + p->layers[j - 1].z_off;
       op.ld_apo = j == 0 ? p->ld_in : p->layers[j - 1].ld_out;
     }
-    if (gemm(p, op, st)) return 1;
+    if (tc_mlp ? gemm(p, op, st, true) : gemm_simt_only(p, op, st)) return 1;
     zin = ws + lp.z_off; ld_zin = lp.ld_out;
   }
   return 0;
@@ -394,8 +426,9 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
     top = {seed, ld_seed, s};
   }
   *top_out = top;
-  const bool tc = p->precision == DINO_PREC_TF32;
-  if (tc) DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
+  const bool tc = p->tc;
+  // (the staged weight copies were written ahead of the MLP forward; with the fused MLP kernels, here)
+  if (tc && (p->mlp_fused || p->chain_fused)) DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
   for (int l = L - 1; l >= 0; --l) {
     const LayerPlan& lp = p->layers[l];
     GemmOp op = gemm_op_zero();
@@ -414,7 +447,7 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
       const LayerPlan& below = p->layers[l - 1];
       if (below.act == DINO_ACT_SOFTPLUS) { op.scale = ws + below.sg_off; op.ld_sc = below.ld_out; }
       op.C = ws + below.q_off; op.ldc = below.ld_out;
-      op.round_tf32 = tc ? 1 : 0;
+      op.round_tf32 = (tc && !p->split) ? 1 : 0;
     } else {
       op.C = ws + p->off_r0; op.ldc = p->ld_in;
     }
@@ -445,13 +478,8 @@ static int run_chain_fused(DinoPlan* p, const float* params, const DinoBatch* b,
     }
     DINO_CUDA(cudaEventRecord(p->ev0, st));
   }
-  {
-    const char* dbg = getenv("DINO_CF_DBG");
-    const int knobs = dbg ? atoi(dbg) << 8 : 0;
-    DINO_LAUNCH(launch_chain_fused(p->chain_maps, p->chain, p->chain_steps, ws, b->J, b->J_sqnorm, b->idx, seed, B, coef, do_loss,
-                                   do_backward | (do_backward ? knobs : 0), stats, p->mlp, params, b->m, b->q, b->q_sqnorm, coef_q,
-                                   mlp_mode, st));
-  }
+  DINO_LAUNCH(launch_chain_fused(p->chain_maps, p->chain, p->chain_steps, ws, b->J, b->J_sqnorm, b->idx, seed, B, coef, do_loss,
+                                 do_backward, stats, p->mlp, params, b->m, b->q, b->q_sqnorm, coef_q, mlp_mode, p->split, st));
   if (p->profile) { DINO_CUDA(cudaEventRecord(p->ev1, st)); p->ev_pending = true; }
   return 0;
 }
@@ -508,16 +536,16 @@ static int push_wgrad(DinoPlan* p, GemmGroup& g, const GemmOp& op, cudaStream_t 
   return 0;
 }
 static int flush_wgrad(DinoPlan* p, GemmGroup& g, cudaStream_t st) {
-  if (g.n > 0 && p->precision == DINO_PREC_TF32) {
+  if (g.n > 0 && p->tc) {
     // tensor-core weight gradients for every op that qualifies; the rest stays on the SIMT engine
-    static GemmGroup tc, rest;
+    GemmGroup tc, rest;
     tc.n = rest.n = 0;
     for (int i = 0; i < g.n; ++i) {
       if (wgrad_tc_supported(g.ops[i])) tc.ops[tc.n++] = g.ops[i];
       else if (g.ops[i].a_sm == 1 && g.ops[i].b_sn == 1) rest.ops[rest.n++] = g.ops[i];
       else DINO_LAUNCH(launch_gemm_simt(g.ops[i], p->num_sms, st));
     }
-    if (tc.n > 0) DINO_LAUNCH(launch_wgrad_tc(tc, p->num_sms, st));
+    if (tc.n > 0) DINO_LAUNCH(launch_wgrad_tc(tc, p->split, p->num_sms, st));
     if (rest.n > 0) DINO_LAUNCH(launch_gemm_simt_grouped(rest, p->num_sms, st));
   } else if (g.n > 0) {
     DINO_LAUNCH(launch_gemm_simt_grouped(g, p->num_sms, st));
@@ -555,16 +583,21 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
     op.M = M; op.N = lp.n_out; op.K = lp.n_in; op.sdim = s;
     const float* skip_add = nullptr; long long ld_skip = 0;
     if (need_out && lp.skip_from >= 0) { skip_add = dr_ptr(lp.skip_from); ld_skip = dr_ld(lp.skip_from); }
-    if (p->precision == DINO_PREC_TF32 && need_out) {
-      // tensor-core path: dQ_l = dR_l W_l with the K-major copy W_l^T; the cross-row d sigma sum and the
-      // per-sample scaling follow in one pass over the tile (rowsum_scale_kernel)
+    if (p->tc && qmod == 0) {
+      // tensor-core path: dQ_l = dR_l W_l with the K-major copy W_l^T; the cross-row d sigma sum, the per-sample
+      // scaling and the residual all happen in the epilogue of the same launch
       op.B = ws + lp.wtp_off; op.b_sk = 1; op.b_sn = lp.ld_wtp;
-      op.C = dr_ptr(l + 1); op.ldc = dr_ld(l + 1);
-      if (!need_rs) { op.add_post = skip_add; op.ld_apo = ld_skip; op.round_tf32 = 1; }
+      if (need_rs) {
+        op.yref = q; op.ld_y = ldq;
+        op.rowsum = ws + lp.rs_off; op.ld_rs = lp.ld_out;
+        op.scale = ws + lp.sg_off; op.ld_sc = lp.ld_out;
+      }
+      if (need_out) {
+        op.C = dr_ptr(l + 1); op.ldc = dr_ld(l + 1);
+        op.add_post = skip_add; op.ld_apo = ld_skip;
+        op.round_tf32 = p->split ? 0 : 1;
+      }
       if (gemm(p, op, st)) return 1;
-      if (need_rs)
-        DINO_LAUNCH(launch_rowsum_scale(dr_ptr(l + 1), dr_ld(l + 1), q, ldq, ws + lp.sg_off, lp.ld_out, skip_add,
-                                        ld_skip, ws + lp.rs_off, lp.ld_out, B, s, lp.n_out, 1, 1, st));
       continue;
     }
     op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1;      // W_l
@@ -603,6 +636,7 @@ static int run_mlp_backward(DinoPlan* p, const float* params, int B, float* grad
     return 0;
   }
   auto dz_ptr = [&](int l) { return ws + p->off_dz[l % 3]; };
+  const bool tc_mlp = p->tc && p->prep.n > 0 && !p->chain_fused;
   int lowest_trainable = L;
   for (int l = 0; l < L; ++l)
     if (p->layers[l].trainable) { lowest_trainable = l; break; }
@@ -625,16 +659,20 @@ static int run_mlp_backward(DinoPlan* p, const float* params, int B, float* grad
       op.B = da; op.b_sk = p->ld_dz; op.b_sn = 1;
       op.M = lp.n_in; op.N = lp.n_out; op.K = B;
       op.C = grad + lp.koff; op.ldc = lp.n_out; op.atomic_c = 1;
-      if (gemm(p, op, st)) return 1;
+      // (da / dz live in rotating buffers: this contraction cannot wait for the grouped launch at the end of the step)
+      GemmGroup one;
+      one.n = 1; one.ops[0] = op;
+      if (flush_wgrad(p, one, st)) return 1;
     }
     if (l > lowest_trainable) {   // dz_l = da_l W_l^T [+ dz above the residual block that starts here]
       GemmOp op = gemm_op_zero();
       op.A = da; op.a_sm = p->ld_dz; op.a_sk = 1;
-      op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out;
+      if (tc_mlp) { op.B = ws + lp.wp_off; op.b_sk = 1; op.b_sn = lp.ld_wp; }     // 16-byte-pitch copy of W_l
+      else { op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out; }
       op.M = B; op.N = lp.n_in; op.K = lp.n_out;
       op.C = dz_ptr(l); op.ldc = p->ld_dz;
       if (lp.lands_skip >= 0) { op.add_post = dz_ptr(lp.lands_skip + 1); op.ld_apo = p->ld_dz; }
-      if (gemm(p, op, st)) return 1;
+      if (tc_mlp ? gemm(p, op, st, true) : gemm_simt_only(p, op, st)) return 1;
     }
   }
   return 0;
@@ -790,9 +828,9 @@ extern "C" int dino_gemm_nt(int engine, const float* A, int64_t lda, const float
   op.A = A; op.a_sm = lda; op.a_sk = 1;
   op.B = Bt; op.b_sk = 1; op.b_sn = ldb;
   op.M = M; op.N = N; op.K = K; op.C = C; op.ldc = ldc;
-  if (engine == DINO_PREC_TF32) {
-    if (!gemm_tc_supported(op)) return fail("dino_gemm_nt: operands do not meet the TF32 engine's alignment rules");
-    DINO_LAUNCH(launch_gemm_tc(op, S(stream)));
+  if (engine == DINO_PREC_TF32 || engine == DINO_PREC_FP32X3) {
+    if (!gemm_tc_supported(op)) return fail("dino_gemm_nt: operands do not meet the tcgen05 engine's alignment rules");
+    DINO_LAUNCH(launch_gemm_tc(op, engine == DINO_PREC_FP32X3 ? 1 : 0, S(stream)));
   } else {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -805,7 +843,7 @@ extern "C" int dino_gemm_nt(int engine, const float* A, int64_t lda, const float
 extern "C" int dino_gemm_nt_acc(int engine, const float* XT, int64_t ldx, const float* YT, int64_t ldy, float* C,
                                 int32_t rows, int32_t n_in, int32_t n_out, dino_stream_t stream) {
   if (!XT || !YT || !C) return fail("dino_gemm_nt_acc: null argument");
-  static GemmGroup g;
+  GemmGroup g;
   g.n = 1;
   GemmOp& op = g.ops[0];
   op = gemm_op_zero();
@@ -816,9 +854,9 @@ extern "C" int dino_gemm_nt_acc(int engine, const float* XT, int64_t ldx, const 
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (engine == DINO_PREC_TF32) {
+  if (engine == DINO_PREC_TF32 || engine == DINO_PREC_FP32X3) {
     if (!wgrad_tc_supported(op)) return fail("dino_gemm_nt_acc: operands do not meet the tensor-core weight-gradient rules");
-    DINO_LAUNCH(launch_wgrad_tc(g, sms, S(stream)));
+    DINO_LAUNCH(launch_wgrad_tc(g, engine == DINO_PREC_FP32X3 ? 1 : 0, sms, S(stream)));
   } else {
     DINO_LAUNCH(launch_gemm_simt(op, sms, S(stream)));
   }
@@ -828,7 +866,7 @@ extern "C" int dino_gemm_nt_acc(int engine, const float* XT, int64_t ldx, const 
 extern "C" int dino_gemm_tn_acc(int engine, const float* X, int64_t ldx, const float* Y, int64_t ldy, float* C,
                                 int32_t rows, int32_t n_in, int32_t n_out, dino_stream_t stream) {
   if (!X || !Y || !C) return fail("dino_gemm_tn_acc: null argument");
-  static GemmGroup g;
+  GemmGroup g;
   g.n = 1;
   GemmOp& op = g.ops[0];
   op = gemm_op_zero();
@@ -839,9 +877,9 @@ extern "C" int dino_gemm_tn_acc(int engine, const float* X, int64_t ldx, const f
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (engine == DINO_PREC_TF32) {
+  if (engine == DINO_PREC_TF32 || engine == DINO_PREC_FP32X3) {
     if (!wgrad_tc_supported(op)) return fail("dino_gemm_tn_acc: operands do not meet the tensor-core weight-gradient rules");
-    DINO_LAUNCH(launch_wgrad_tc(g, sms, S(stream)));
+    DINO_LAUNCH(launch_wgrad_tc(g, engine == DINO_PREC_FP32X3 ? 1 : 0, sms, S(stream)));
   } else {
     DINO_LAUNCH(launch_gemm_simt(op, sms, S(stream)));
   }

@@ -8,20 +8,21 @@
 // plain SWIZZLE_128B) are still accepted.  Pipeline: TMA 3-stage ring -> tcgen05.mma.kind::tf32 -> TMEM ->
 // red.global.add.  Output tiles of 128 x 128; wide layers are covered by several tiles (blockIdx.x enumerates op,
 // tile, split).  The launch is sized to ONE wave of CTAs: every extra split adds 128 x n_out atomics.
+// fp32x3 mode: four converter warps write the lo tile (x - trunc_tf32(x)) of every landed stage beside it and each
+// 8-row reduction step issues three MMAs (tc_common.cuh), which makes the reduction fp32-grade.
 #include <cuda.h>
 
 #include <cstdlib>
 #include <mutex>
 
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace dino {
 
 constexpr int WG_BK = 32;                       // reduction rows per stage (one 128-byte swizzle row)
-constexpr int WG_STAGES = 3;   // 96 KB: leaves room for a fused-MLP CTA on the same SM (the two overlap on separate streams)
+constexpr int WG_STAGES = 3;   // tf32: 96 KB, leaves room for a fused-MLP CTA on the same SM (the two overlap on separate streams); fp32x3: 192 KB
 constexpr int WG_OPER_BYTES = 128 * WG_BK * 4;  // 16 KB: up to 128 operand rows x 32 reduction elements
-constexpr int WG_STAGE_BYTES = 2 * WG_OPER_BYTES;
-constexpr int WG_THREADS = 192;
+constexpr int WG_RAW_BYTES = 2 * WG_OPER_BYTES;
 
 struct WgOp {
   float* C;                 // gradient block [n_in, n_out], ldc = n_out
@@ -60,13 +61,16 @@ __device__ __forceinline__ uint64_t wg_desc_mn(uint32_t saddr) {
   return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)((WG_BK * 128) >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) | (1ull << 46) | (1ull << 61);
 }
 
-__global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_constant__ WgGroup g) {
+template <bool SPLIT>
+__global__ void __launch_bounds__(SPLIT ? 320 : 192, 1) wgrad_tc_kernel(const __grid_constant__ WgGroup g) {
+  constexpr int WG_STAGE_BYTES = SPLIT ? 2 * WG_RAW_BYTES : WG_RAW_BYTES;
   extern __shared__ uint8_t wg_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(wg_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + WG_STAGES * WG_STAGE_BYTES);
   uint64_t* empty_bar = full_bar + WG_STAGES;
   uint64_t* done_bar = empty_bar + WG_STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+  uint64_t* conv_bar = done_bar + 1;                      // [WG_STAGES] lo tiles written (fp32x3)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(conv_bar + WG_STAGES);
 
   int oi = 0;
   while (oi + 1 < g.n && (int)blockIdx.x >= g.op[oi + 1].z_start) ++oi;
@@ -84,6 +88,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
       for (int i = 0; i < WG_STAGES; ++i) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(wg_u32(full_bar + i)), "r"(1u));
         asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(wg_u32(empty_bar + i)), "r"(1u));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(wg_u32(conv_bar + i)), "r"(4u));
       }
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(wg_u32(done_bar)), "r"(1u));
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -121,7 +126,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
             continue;
           }
           asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(wg_u32(full_bar + st)),
-                       "r"((uint32_t)WG_STAGE_BYTES) : "memory");
+                       "r"((uint32_t)WG_RAW_BYTES) : "memory");
           asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                        ::"r"(wg_u32(sx)), "l"(mx), "r"(wg_u32(full_bar + st)), "r"(k0), "r"(m0) : "memory");
           asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -137,23 +142,35 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
         const uint64_t kstep = op.mn ? 64 : 2;      // descriptor start-address advance per 8 reduction rows (16-byte units)
         for (int c = 0; c < nchunks; ++c) {
           const int st = c % WG_STAGES;
-          wg_wait(full_bar + st, (c / WG_STAGES) & 1);
+          wg_wait((SPLIT ? conv_bar : full_bar) + st, (c / WG_STAGES) & 1);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t sx = wg_u32(smem + st * WG_STAGE_BYTES), sy = sx + WG_OPER_BYTES;
           const uint64_t ad = op.mn ? wg_desc_mn(sx) : wg_desc(sx), bd = op.mn ? wg_desc_mn(sy) : wg_desc(sy);
+          constexpr uint64_t LO = WG_RAW_BYTES >> 4;        // the lo tiles sit WG_RAW_BYTES above their sources
 #pragma unroll
           for (int k = 0; k < WG_BK / 8; ++k) {
-            const uint32_t acc = (c > 0 || k > 0) ? 1u : 0u;
-            asm volatile(
-                "{\n\t"
-                ".reg .pred p;\n\t"
-                "setp.ne.b32 p, %4, 0;\n\t"
-                "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-                "}" ::"r"(tmem_base), "l"(ad + kstep * k), "l"(bd + kstep * k), "r"(idesc), "r"(acc) : "memory");
+            tc::umma_tf32(tmem_base, ad + kstep * k, bd + kstep * k, idesc, (c > 0 || k > 0) ? 1u : 0u);
+            if (SPLIT) {
+              tc::umma_tf32(tmem_base, ad + LO + kstep * k, bd + kstep * k, idesc, 1u);
+              tc::umma_tf32(tmem_base, ad + kstep * k, bd + LO + kstep * k, idesc, 1u);
+            }
           }
           asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(wg_u32(empty_bar + st)) : "memory");
         }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(wg_u32(done_bar)) : "memory");
+      }
+    } else if (warp >= 6) {
+      // converters (fp32x3): lo tile of every landed stage (whole stage: the layout does not matter elementwise)
+      if (SPLIT) {
+        for (int c = 0; c < nchunks; ++c) {
+          const int st = c % WG_STAGES;
+          wg_wait(full_bar + st, (c / WG_STAGES) & 1);
+          const uint32_t sx = wg_u32(smem + st * WG_STAGE_BYTES);
+          tc::split_lo_tile(sx, sx + WG_RAW_BYTES, WG_RAW_BYTES, (int)threadIdx.x - 192, 128);
+          tc::fence_async_smem();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(conv_bar + st);
+        }
       }
     } else {
       // epilogue: TMEM lane = n_in index m, columns = n_out index
@@ -191,48 +208,17 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(const __grid_co
 }
 
 // ---- host ---------------------------------------------------------------------------------------------
-typedef CUresult (*PFN_wgEncode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static PFN_wgEncode wg_encoder() {
-  static PFN_wgEncode enc = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* fn = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-      enc = reinterpret_cast<PFN_wgEncode>(fn);
-  });
-  return enc;
-}
 // operand stored [n, rows] with pitch ld floats: box = 128 operand rows x 32 reduction elements
 static bool wg_map(CUtensorMap* m, const float* base, int n, int rows, long long ld) {
-  PFN_wgEncode enc = wg_encoder();
-  if (!enc) return false;
-  cuuint64_t gdim[2] = {(cuuint64_t)rows, (cuuint64_t)n};
-  cuuint64_t gstr[1] = {(cuuint64_t)ld * sizeof(float)};
-  cuuint32_t box[2] = {(cuuint32_t)WG_BK, 128};
-  cuuint32_t es[2] = {1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, es,
-             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  return tc_make_map(m, base, (unsigned long long)rows, (unsigned long long)n, ld, WG_BK, 128, (int)CU_TENSOR_MAP_SWIZZLE_128B);
 }
-
 // operand stored ROW-major [rows, n] with pitch ld floats: box = 32 columns x WG_BK reduction rows, 32-byte-atom swizzle
 static bool wg_map_mn(CUtensorMap* m, const float* base, int n, int rows, long long ld) {
-  PFN_wgEncode enc = wg_encoder();
-  if (!enc) return false;
-  cuuint64_t gdim[2] = {(cuuint64_t)n, (cuuint64_t)rows};
-  cuuint64_t gstr[1] = {(cuuint64_t)ld * sizeof(float)};
-  cuuint32_t box[2] = {32, (cuuint32_t)WG_BK};
-  cuuint32_t es[2] = {1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, es,
-             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  return tc_make_map(m, base, (unsigned long long)n, (unsigned long long)rows, ld, 32, WG_BK, (int)CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
 }
 
 // The ops passed here describe C[M,N] += A[M,K] * Bt[N,K]^T with BOTH operands K-major (a_sk == b_sk == 1):
-// A = XT (pitch a_sm), B = YT (pitch b_sn).
+// A = XT (pitch a_sm), B = YT (pitch b_sn), or both MN-major (a_sm == b_sn == 1: the row-major chain states).
 bool wgrad_tc_supported(const GemmOp& op) {
   if (!op.atomic_c || op.b_kmod > 0 || op.a_mod > 0) return false;
   if (op.M < 1 || op.N < 1 || op.K < 1) return false;
@@ -245,15 +231,15 @@ bool wgrad_tc_supported(const GemmOp& op) {
   return op.ldc == op.N;
 }
 
-cudaError_t launch_wgrad_tc(const GemmGroup& gg, int num_sms, cudaStream_t st) {
+cudaError_t launch_wgrad_tc(const GemmGroup& gg, int split, int num_sms, cudaStream_t st) {
   if (gg.n <= 0) return cudaSuccess;
-  static WgGroup g;                      // about 7 KB: keep it off the stack; plans are single-threaded
+  WgGroup g;                             // kernel parameter (about 7 KB), built on the stack: nothing is shared between host threads
   g.n = gg.n;
-  // work of an op ~ tiles * rows; share about 2 waves of CTAs between the ops in that proportion
+  // work of an op ~ tiles * rows; share about one wave of CTAs between the ops in that proportion
   double total_work = 0.0;
   for (int i = 0; i < gg.n; ++i)
     total_work += (double)gg.ops[i].K * ((gg.ops[i].M + 127) / 128) * ((gg.ops[i].N + 127) / 128);
-  static const double wg_waves = getenv("DINO_WG_WAVES") ? atof(getenv("DINO_WG_WAVES")) : 1.0;
+  static const double wg_waves = getenv("DINO_WG_WAVES") ? atof(getenv("DINO_WG_WAVES")) : 1.0;   // read once per process
   const double target_ctas = wg_waves * num_sms;
   int z = 0;
   for (int i = 0; i < gg.n; ++i) {
@@ -276,14 +262,19 @@ cudaError_t launch_wgrad_tc(const GemmGroup& gg, int num_sms, cudaStream_t st) {
       if (!wg_map_mn(&g.mx[i], o.A, o.M, o.K, o.a_sk) || !wg_map_mn(&g.my[i], o.B, o.N, o.K, o.b_sk)) return cudaErrorInvalidValue;
     } else if (!wg_map(&g.mx[i], o.A, o.M, o.K, o.a_sm) || !wg_map(&g.my[i], o.B, o.N, o.K, o.b_sn)) return cudaErrorInvalidValue;
   }
-  constexpr int SMEM = WG_STAGES * WG_STAGE_BYTES + 128 + 1024;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+  if (split) {
+    constexpr int SMEM = WG_STAGES * 2 * WG_RAW_BYTES + 128 + 1024;
+    static std::atomic<unsigned long long> mask{0};
+    cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(wgrad_tc_kernel<true>), SMEM, mask);
     if (e != cudaSuccess) return e;
-    configured = true;
+    wgrad_tc_kernel<true><<<z, 320, SMEM, st>>>(g);
+  } else {
+    constexpr int SMEM = WG_STAGES * WG_RAW_BYTES + 128 + 1024;
+    static std::atomic<unsigned long long> mask{0};
+    cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(wgrad_tc_kernel<false>), SMEM, mask);
+    if (e != cudaSuccess) return e;
+    wgrad_tc_kernel<false><<<z, 192, SMEM, st>>>(g);
   }
-  wgrad_tc_kernel<<<z, WG_THREADS, SMEM, st>>>(g);
   return cudaGetLastError();
 }
 

@@ -412,6 +412,12 @@ class TrainEngine:
         Bg = self.batch_size if Bg is None else int(Bg)
         if Bg > self.remaining() or self.host_step >= self.steps_cap + 1:
             raise RuntimeError("TrainEngine.step: not enough samples left in the installed order")
+        if self.plan.handle is None:
+            # the network changed under the engine (layer.trainable toggled -> plans invalidated): take a fresh plan
+            # and drop the graphs that replay the old workspace
+            self.plan = self.model._plan(self.plan.max_batch)
+            self.graphs.clear()
+            self.seen.clear()
         key = self._key()
         entry = self.graphs.get(Bg)
         if entry is not None and entry[1] != key:
@@ -435,8 +441,12 @@ class TrainEngine:
                 self.captured_kernels += kernels                # counted by the library but not executed
                 g.replay()
                 self.replayed_kernels += kernels
-            except Exception:
-                self.use_graph = False          # e.g. a collective that cannot be captured: stay eager
+            except _lib.DinoLibraryError:
+                raise                           # a real error of the step itself: never swallow it
+            except RuntimeError as exc:         # stream capture refused (e.g. a collective that cannot be captured)
+                import warnings
+                warnings.warn(f"dino_b200: CUDA-graph capture of the training step failed ({exc}); staying eager")
+                self.use_graph = False
                 torch.cuda.synchronize()
                 self._enqueue(Bg)
         else:
@@ -468,24 +478,25 @@ class History:
 
 
 def _combine_stats(stats: np.ndarray, weights, jac: bool):
-    """Keras aggregation (TF-knowledge): every reported value is the batch-size-weighted mean of
-    the per-batch values.  stats: [n_batches, STAT_SLOTS] per-batch sums from the loss kernels."""
+    """Keras aggregation (TF-knowledge, Keras 2.7): the losses are batch-size-weighted means of the per-batch values
+    (LossesContainer passes sample_weight = batch size); the function metrics l2_accuracy / f_accuracy_matrix return
+    one scalar per batch and go through MeanMetricWrapper, so every batch counts ONCE, also a short last one.
+    stats: [n_batches, STAT_SLOTS] per-batch sums from the loss kernels."""
     s = stats.astype(np.float64)
     cnt = s[:, _lib.STAT_COUNT]
     keep = cnt > 0
     s, cnt = s[keep], cnt[keep]
     wts = cnt / cnt.sum()
+    uni = np.full(len(cnt), 1.0 / max(len(cnt), 1))
     l2 = s[:, _lib.STAT_L2_SUM] / cnt
     out_q = [l2, 1.0 - np.sqrt(l2), 1.0 - np.sqrt(s[:, _lib.STAT_EQ_SUM] / s[:, _lib.STAT_NQ_SUM])]
     if not jac:
         loss = weights[0] * l2
-        vals = [loss, out_q[1]]
-        return [float((v * wts).sum()) for v in vals]
+        return [float((loss * wts).sum()), float((out_q[1] * uni).sum())]
     h1 = s[:, _lib.STAT_H1_SUM] / cnt
     loss = weights[0] * l2 + weights[1] * h1
-    vals = [loss, l2, h1, out_q[1], out_q[2], 1.0 - np.sqrt(s[:, _lib.STAT_JROW_SUM] / s[:, _lib.STAT_JROWS]),
-            1.0 - np.sqrt(h1)]
-    return [float((v * wts).sum()) for v in vals]
+    accs = [out_q[1], out_q[2], 1.0 - np.sqrt(s[:, _lib.STAT_JROW_SUM] / s[:, _lib.STAT_JROWS]), 1.0 - np.sqrt(h1)]
+    return [float((v * wts).sum()) for v in (loss, l2, h1)] + [float((v * uni).sum()) for v in accs]
 
 
 _LOSS_NAMES = {"normalized_mse", "normalized_mse_matrix"}
@@ -502,7 +513,7 @@ class DinoModel:
         self.seed_dim = {"none": 0, "full": core.d_out}.get(jac_mode, seed_dim)
         # Phi [d_Q, r_out] of equip_model_with_output_reduced_jacobian; the chain is seeded with Phi^T
         self.output_basis = None if output_basis is None else np.asarray(output_basis, dtype=np.float32)
-        self.precision = precision or os.environ.get("DINO_B200_PRECISION", "fp32")
+        self.precision = precision or os.environ.get("DINO_B200_PRECISION", "fp32x3")
         self.optimizer = None
         self.loss_weights = [1.0, 1.0]
         self._compiled = False
@@ -605,9 +616,10 @@ class DinoModel:
     def _plan(self, max_batch: int) -> _Plan:
         key = (self.jac_mode, self.seed_dim, _lib.PRECISIONS[self.precision])
         plan = self.core._plans.get(key)
-        if plan is None or plan.max_batch < max_batch:
-            if plan is not None:
-                plan.close()
+        if plan is None or plan.handle is None or plan.max_batch < max_batch:
+            # A larger plan REPLACES the cached one but never destroys it: a live TrainEngine (or a captured CUDA
+            # graph of fit_generator) may still hold the smaller plan and its workspace; that object is released
+            # when its last user lets go of it (_Plan.__del__).
             plan = _Plan(self.core, self.jac_mode, self.seed_dim, max_batch, _lib.PRECISIONS[self.precision])
             self.core._plans[key] = plan
         return plan
@@ -876,7 +888,8 @@ class DinoModel:
                     dp.all_reduce_sum(S["stats"])
                 S["host"].copy_(S["stats"], non_blocking=True)      # device->host read of the step's result
 
-            gkey = (Bl, opt.kind, float(opt.learning_rate), tuple(self.loss_weights), self.core.device_params().data_ptr())
+            gkey = (Bl, opt.kind, float(opt.learning_rate), tuple(self.loss_weights), self.core.device_params().data_ptr(),
+                    id(plan))
             entry = S.get("graph")
             if entry is not None and entry[1] != gkey:
                 entry = None
@@ -891,9 +904,13 @@ class DinoModel:
                     with torch.cuda.graph(g, stream=side):
                         enqueue()
                     compute.wait_stream(side)
-                    S["graph"] = (g, gkey)
+                    S["graph"] = (g, gkey, plan)          # the graph replays this plan's workspace: keep it alive
                     g.replay()
-                except Exception:
+                except _lib.DinoLibraryError:
+                    raise
+                except RuntimeError as exc:
+                    import warnings
+                    warnings.warn(f"dino_b200: CUDA-graph capture of the pipelined step failed ({exc}); staying eager")
                     pipe["no_graph"] = True
                     torch.cuda.synchronize()
                     enqueue()

@@ -98,6 +98,20 @@ def random_weights(arch: Arch, rng: np.random.Generator, teacher: bool):
     return out
 
 
+def student_weights(arch: Arch, seed: int, teacher_weights=None, bias_noise=0.0):
+    """Student initialisation of SURVEY.md 8d: glorot-uniform kernels and zero biases from ``default_rng(seed)``; a
+    frozen output layer is copied from the teacher; ``bias_noise`` > 0 draws N(0, bias_noise^2) biases instead (tests)."""
+    rng = np.random.default_rng(seed)
+    w = random_weights(arch, rng, teacher=False)
+    if teacher_weights is not None and "output_layer" in w:
+        w["output_layer"] = [a.copy() for a in teacher_weights["output_layer"]]
+    if bias_noise:
+        for name, arrs in w.items():
+            if len(arrs) == 2 and name != "output_layer":
+                arrs[1] = rng.normal(0, bias_noise, arrs[1].shape).astype(np.float32)
+    return w
+
+
 def teacher_eval(arch: Arch, weights, m: np.ndarray, want_jacobian=True, chunk=256):
     """q = net(m) and J = d net / d m ([n, d_out, d_in]) by a forward-mode chain, in float64."""
     table = layer_table(arch)

@@ -31,8 +31,11 @@ typedef void* dino_stream_t; /* cudaStream_t */
 enum { DINO_ACT_LINEAR = 0, DINO_ACT_SOFTPLUS = 1 };
 /* which second model output the network is equipped with (jacobianConstruction.py:102,128,155) */
 enum { DINO_JAC_NONE = 0, DINO_JAC_FULL = 1, DINO_JAC_OUT_REDUCED = 2, DINO_JAC_SKETCHED = 3 };
-/* arithmetic of the Jacobian-chain contractions */
-enum { DINO_PREC_FP32 = 0, DINO_PREC_TF32 = 1 };
+/* arithmetic of the contractions (Jacobian chain, data gradients, weight gradients):
+ *   FP32    SIMT FFMA, no tensor cores                                   parity bar 1e-4 (reference: Keras floatx fp32)
+ *   TF32    tcgen05 kind::tf32, one MMA per product (10-bit mantissas)   reported variant, bars 5e-3 / 1e-2
+ *   FP32X3  tcgen05 kind::tf32, three MMAs on hi/lo operand splits       parity bar 1e-4; the default of the host layer */
+enum { DINO_PREC_FP32 = 0, DINO_PREC_TF32 = 1, DINO_PREC_FP32X3 = 2 };
 
 /* One Keras Dense layer: y = act(x W + b) [+ input of layer skip_from]; W is [n_in, n_out]
  * (Keras kernel layout).  Mirrors tf.keras.layers.Dense as used at neuralNetworks.py:34-61,
@@ -171,7 +174,7 @@ int dino_forward_noalloc(const DinoNetSpec* spec, const float* d_params, const f
 
 /* The contraction primitive of the Jacobian chain on its own: C[M,N] = A[M,K] * Bt[N,K]^T, fp32 in and
  * out (what a TF MatMul inside tape.batch_jacobian computes, jacobianConstruction.py:149).  engine =
- * DINO_PREC_FP32 (SIMT FFMA) or DINO_PREC_TF32 (tcgen05 + TMA; needs lda, ldb, ldc multiples of 4 and
+ * DINO_PREC_FP32 (SIMT FFMA) or DINO_PREC_TF32 / DINO_PREC_FP32X3 (tcgen05 + TMA; need lda, ldb, ldc multiples of 4 and
  * 16-byte aligned bases).  Used by the parity tests and the kernel micro-benchmarks. */
 int dino_gemm_nt(int engine, const float* d_A, int64_t lda, const float* d_Bt, int64_t ldb, float* d_C,
                  int64_t ldc, int32_t M, int32_t N, int32_t K, dino_stream_t stream);

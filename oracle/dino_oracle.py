@@ -316,13 +316,18 @@ def slice_batch(data: Batch, idx) -> Batch:
 
 
 def evaluate(net: ONet, data: Batch, batch_size=32, **kw):
-    """Keras ``evaluate`` (TF-knowledge): per-batch values averaged with batch-size weights."""
+    """Keras ``evaluate`` (TF-knowledge, Keras 2.7): the three losses are averaged with batch-size weights
+    (LossesContainer: sample_weight = batch size); the four function metrics return one scalar per batch and go
+    through MeanMetricWrapper, so each batch counts once, whatever its size."""
     n = data.m.shape[0]
-    acc = np.zeros(7)
+    loss_acc, met_acc, nb = np.zeros(3), np.zeros(4), 0
     for s in range(0, n, batch_size):
         idx = np.arange(s, min(n, s + batch_size))
-        acc += np.array(evaluate_batch(net, slice_batch(data, idx), **kw)) * len(idx)
-    return list(acc / n)
+        vals = np.array(evaluate_batch(net, slice_batch(data, idx), **kw))
+        loss_acc += vals[:3] * len(idx)
+        met_acc += vals[3:]
+        nb += 1
+    return list(loss_acc / n) + list(met_acc / nb)
 
 
 # --------------------------------------------------------------------------------------

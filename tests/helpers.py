@@ -22,16 +22,7 @@ def oracle_batch(data, idx=None, dtype=torch.float64, U=None, V=None):
     return O.Batch(t(data["m"]), t(data["q"]), t(data["J"]), t(U), t(V))
 
 
-def student_weights(arch, seed, teacher_weights=None, bias_noise=0.0):
-    rng = np.random.default_rng(seed)
-    w = S.random_weights(arch, rng, teacher=False)
-    if teacher_weights is not None and "output_layer" in w:
-        w["output_layer"] = [a.copy() for a in teacher_weights["output_layer"]]
-    if bias_noise:
-        for name, arrs in w.items():
-            if len(arrs) == 2 and name != "output_layer":
-                arrs[1] = rng.normal(0, bias_noise, arrs[1].shape).astype(np.float32)
-    return w
+student_weights = S.student_weights
 
 
 def rel_err(a, b):

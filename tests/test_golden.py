@@ -52,6 +52,22 @@ def test_keras_metric_aggregation_from_kernel_statistics():
     assert np.allclose(v, want, rtol=1e-12)
 
 
+def test_keras_metric_aggregation_with_a_short_last_batch():
+    """n % batch_size != 0: the three losses are batch-size weighted, the four accuracies count each batch once."""
+    from dino_b200.model import _combine_stats
+    from dino_b200 import _lib
+    st = np.zeros((2, _lib.STAT_SLOTS))
+    for i, (cnt, l2, h1) in enumerate([(32, 0.04, 0.09), (5, 0.16, 0.25)]):
+        st[i, _lib.STAT_COUNT], st[i, _lib.STAT_JROWS] = cnt, cnt * 3
+        st[i, _lib.STAT_L2_SUM], st[i, _lib.STAT_H1_SUM] = l2 * cnt, h1 * cnt
+        st[i, _lib.STAT_EQ_SUM], st[i, _lib.STAT_NQ_SUM] = l2 * cnt, cnt
+        st[i, _lib.STAT_JROW_SUM] = h1 * cnt * 3
+    v = _combine_stats(st, [1.0, 1.0], True)
+    wl2, wh1 = (32 * 0.04 + 5 * 0.16) / 37, (32 * 0.09 + 5 * 0.25) / 37
+    assert np.allclose(v[:3], [wl2 + wh1, wl2, wh1], rtol=1e-12)
+    assert np.allclose(v[3:], [1 - (0.2 + 0.4) / 2, 1 - (0.2 + 0.4) / 2, 1 - (0.3 + 0.5) / 2, 1 - (0.3 + 0.5) / 2], rtol=1e-12)
+
+
 def _svd_data():
     return {k: G["svd_" + k] for k in ("m_data", "q_data", "U_data", "sigma_data", "V_data")}
 

@@ -1,6 +1,6 @@
 """-m gpu parity tests: the CUDA path (through the C ABI, via DinoModel) against the CPU oracle on
-the same seeded inputs.  Tolerances: the product computes in fp32 (SIMT FFMA engine), the oracle
-in fp64; north_star asks for 1e-4 relative in fp32, the asserts below are tighter where fp32
+the same seeded inputs, in both fp32-grade modes (tcgen05 fp32x3 and the SIMT FFMA engine).  The oracle
+computes in fp64; north_star asks for 1e-4 relative in fp32, the asserts below are tighter where fp32
 round-off allows."""
 import numpy as np
 import pytest
@@ -16,6 +16,14 @@ from dino_b200.construction import (equip_model_with_full_jacobian, equip_model_
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-4
+
+
+@pytest.fixture(params=["fp32x3", "fp32"], autouse=True)
+def precision(request, monkeypatch):
+    """Both 1e-4 modes: the tensor-core fp32x3 arithmetic (the default of DinoModel) and the SIMT fp32 engine."""
+    monkeypatch.setenv("DINO_B200_PRECISION", request.param)
+    return request.param
+
 
 
 def _problem(arch, n, seed):

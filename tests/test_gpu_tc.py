@@ -30,7 +30,7 @@ def _gemm(engine, A, Bt, M, N, K, lda, ldb, ldc):
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 64, 32), (100, 50, 50), (1600, 50, 100), (300, 100, 50), (257, 130, 70),
-                                   (512, 400, 200), (1000, 1024, 1024), (128, 8, 8), (5, 52, 300)])
+                                   (512, 400, 200), (1000, 1024, 1024), (128, 8, 8), (5, 52, 300), (8192, 520, 100)])
 def test_tf32_gemm_matches_fp64(cuda_device, M, N, K):
     rng = np.random.default_rng(M * 7 + N * 3 + K)
     r4 = lambda n: (n + 3) & ~3
@@ -46,6 +46,10 @@ def test_tf32_gemm_matches_fp64(cuda_device, M, N, K):
     got = _gemm(_lib.PREC_TF32, dA, dB, M, N, K, lda, ldb, ldc)
     assert np.isfinite(got).all()
     assert np.abs(got - want).max() < 2e-3 * np.sqrt(K) * 4, np.abs(got - want).max()
+    # fp32x3: three MMAs on hi/lo splits of both operands -> fp32-grade products
+    got3 = _gemm(_lib.PREC_FP32X3, dA, dB, M, N, K, lda, ldb, ldc)
+    assert np.isfinite(got3).all()
+    assert np.abs(got3 - want).max() < 1e-5 * np.sqrt(K) * 4, np.abs(got3 - want).max()
 
 
 @pytest.mark.parametrize("rows,n_in,n_out", [(64, 32, 32), (240, 13, 8), (1000, 50, 50), (12800, 100, 50), (300, 128, 128),
@@ -59,7 +63,7 @@ def test_tf32_weight_gradient_contraction(cuda_device, rows, n_in, n_out):
     YT = np.full((n_out, ld), 1e30, np.float32); YT[:, :rows] = rng.normal(size=(n_out, rows))
     C0 = rng.normal(size=(n_in, n_out)).astype(np.float32)
     want = C0 + XT[:, :rows].astype(np.float64) @ YT[:, :rows].astype(np.float64).T
-    for engine, tol in ((_lib.PREC_FP32, 1e-5), (_lib.PREC_TF32, 2e-3)):
+    for engine, tol in ((_lib.PREC_FP32, 1e-5), (_lib.PREC_TF32, 2e-3), (_lib.PREC_FP32X3, 1e-5)):
         dX, dY, dC = torch.from_numpy(XT).cuda(), torch.from_numpy(YT).cuda(), torch.from_numpy(C0.copy()).cuda()
         _lib.check(lib.dino_gemm_nt_acc(engine, C.c_void_p(dX.data_ptr()), ld, C.c_void_p(dY.data_ptr()), ld,
                                         C.c_void_p(dC.data_ptr()), rows, n_in, n_out, _stream()), "dino_gemm_nt_acc")
@@ -80,7 +84,7 @@ def test_tf32_weight_gradient_contraction_row_major(cuda_device, rows, n_in, n_o
     Y = np.full((rows, ldy), 1e30, np.float32); Y[:, :n_out] = rng.normal(size=(rows, n_out))
     C0 = rng.normal(size=(n_in, n_out)).astype(np.float32)
     want = C0 + X[:, :n_in].astype(np.float64).T @ Y[:, :n_out].astype(np.float64)
-    for engine, tol in ((_lib.PREC_FP32, 1e-5), (_lib.PREC_TF32, 2e-3)):
+    for engine, tol in ((_lib.PREC_FP32, 1e-5), (_lib.PREC_TF32, 2e-3), (_lib.PREC_FP32X3, 1e-5)):
         dX, dY, dC = torch.from_numpy(X).cuda(), torch.from_numpy(Y).cuda(), torch.from_numpy(C0.copy()).cuda()
         _lib.check(lib.dino_gemm_tn_acc(engine, C.c_void_p(dX.data_ptr()), ldx, C.c_void_p(dY.data_ptr()), ldy,
                                         C.c_void_p(dC.data_ptr()), rows, n_in, n_out, _stream()), "dino_gemm_tn_acc")
