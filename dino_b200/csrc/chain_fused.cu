@@ -311,35 +311,48 @@ chain_fused_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         // descriptor start addresses advance by 32 bytes per 8-wide K step, 16 KB per 32-column chunk (no carry out
         // of the 14-bit address field: the tiles sit below 256 KB)
         const uint32_t dcol = tmem_base + (uint32_t)(buf * CF_ACC_COLS);
+        const int nch = (ksteps + 3) >> 2;                  // 32-column chunks of X / the weight tile (four K steps each)
+        const int slot0 = slot, round0 = round;             // the step's chunks sit in consecutive ring slots: hi (, lo) per chunk
+        auto slot_of = [&](int i) { int sl = slot0 + i; return sl >= CF_SLOTS ? sl - CF_SLOTS : sl; };
+        auto round_of = [&](int i) { return slot0 + i >= CF_SLOTS ? round0 + 1 : round0; };
+        const int per = split ? 2 : 1;
+        if (split) {
+          // fp32x3, pass 1: the two small cross terms of every K step, x_hi * w_lo and x_lo * w_hi (the tensor core reads
+          // the hi parts out of the fp32 containers).  They go FIRST: the tensor core adds into its fp32 accumulator with
+          // truncation, an error of ~2^-24 of the accumulator's magnitude per MMA, and while only cross terms (2^-11 of
+          // the result) are in it that error is nil.  The main sum below then costs K/8 truncations, not 3K/8.
 #pragma unroll 1
-        for (int c = 0; c * 4 < ksteps; ++c) {              // one 32-column chunk of X / the weight tile = four K steps
-          const uint64_t oc = (uint64_t)(c * (CF_CHUNK_BYTES >> 4));
-          const int s_hi = slot;
-          cf_mbar_wait(slot_full + s_hi, round & 1);        // weight chunk landed
-          if (++slot == CF_SLOTS) { slot = 0; ++round; }
-          const uint64_t bh = cf_desc(w_u + (uint32_t)(s_hi * CF_CHUNK_BYTES));
-          int s_lo = 0;
-          uint64_t bl = 0;
-          if (split) {
-            s_lo = slot;
-            cf_mbar_wait(slot_full + s_lo, round & 1);
-            if (++slot == CF_SLOTS) { slot = 0; ++round; }
-            bl = cf_desc(w_u + (uint32_t)(s_lo * CF_CHUNK_BYTES));
+          for (int c = 0; c < nch; ++c) {
+            const uint64_t oc = (uint64_t)(c * (CF_CHUNK_BYTES >> 4));
+            cf_mbar_wait(slot_full + slot_of(2 * c), round_of(2 * c) & 1);
+            cf_mbar_wait(slot_full + slot_of(2 * c + 1), round_of(2 * c + 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t bh = cf_desc(w_u + (uint32_t)(slot_of(2 * c) * CF_CHUNK_BYTES));
+            const uint64_t bl = cf_desc(w_u + (uint32_t)(slot_of(2 * c + 1) * CF_CHUNK_BYTES));
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (c * 4 + j < ksteps) {
+                cf_mma(dcol, xd + oc + 2 * j, bl + 2 * j, idesc, (c | j) ? 1u : 0u);
+                tc::umma_tf32_ts(dcol, xlo + (uint32_t)(c * 32 + j * 8), bh + 2 * j, idesc, 1u);
+              }
           }
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+#pragma unroll 1
+        for (int c = 0; c < nch; ++c) {                     // main products x_hi * w_hi (tf32: the only pass)
+          const uint64_t oc = (uint64_t)(c * (CF_CHUNK_BYTES >> 4));
+          if (!split) {
+            cf_mbar_wait(slot_full + slot_of(c), round_of(c) & 1);       // weight chunk landed
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          }
+          const uint64_t bh = cf_desc(w_u + (uint32_t)(slot_of(per * c) * CF_CHUNK_BYTES));
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            if (c * 4 + j < ksteps) {
-              cf_mma(dcol, xd + oc + 2 * j, bh + 2 * j, idesc, (c | j) ? 1u : 0u);
-              if (split) {
-                // fp32x3: x = hi + lo, w = hi + lo; the tensor core reads the hi parts out of the fp32 containers
-                cf_mma(dcol, xd + oc + 2 * j, bl + 2 * j, idesc, 1u);                                   // x_hi * w_lo
-                tc::umma_tf32_ts(dcol, xlo + (uint32_t)(c * 32 + j * 8), bh + 2 * j, idesc, 1u);        // x_lo * w_hi
-              }
-            }
-          cf_commit(slot_empty + s_hi);                     // the slot is free once these MMAs have read it
-          if (split) cf_commit(slot_empty + s_lo);
+            if (c * 4 + j < ksteps) cf_mma(dcol, xd + oc + 2 * j, bh + 2 * j, idesc, (split || (c | j)) ? 1u : 0u);
+          cf_commit(slot_empty + slot_of(per * c));         // the slot is free once the MMAs issued so far have read it
+          if (split) cf_commit(slot_empty + slot_of(per * c + 1));
         }
+        slot = slot0 + per * nch;
+        if (slot >= CF_SLOTS) { slot -= CF_SLOTS; ++round; }
         cf_commit(mma_bar(t));
         CF_STAMP(t, 2);
       }

@@ -59,7 +59,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   constexpr int A_BYTES = TC_BM * BK * 4, B_BYTES = BN * BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
   constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;           // columns of one accumulator
-  constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;               // two accumulators: the epilogue of tile i overlaps the MMAs of tile i+1
+  // fp32x3 keeps TWO accumulators per tile: the hi*hi products in one, the two small cross terms in the other.  The
+  // tensor core adds into its fp32 accumulator with truncation, a bias of ~2^-25 of the accumulator's magnitude per
+  // MMA; the cross terms are 2^-11 of the main sum, so their MMAs cost nothing in a separate accumulator, and the main
+  // one sees K/8 additions instead of 3K/8.  The epilogue adds the two in fp32.
+  constexpr uint32_t SET_COLS = SPLIT ? 2 * ACC_COLS : ACC_COLS;
+  constexpr int NACC = 2 * SET_COLS <= 512 ? 2 : 1;          // two sets when they fit: the epilogue of tile i overlaps the MMAs of tile i+1
+  constexpr uint32_t TMEM_COLS = NACC * SET_COLS;
   constexpr int EPI_BUF = 32 * 128;                          // one 32 x 32 fp32 block, 128-byte rows, SWIZZLE_128B
 
   extern __shared__ uint8_t smem_raw[];
@@ -121,10 +127,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       const uint32_t idesc = idesc_tf32(BN);
       int it = 0, i = 0;
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
-        const int acc = i & 1;
-        mbar_wait(tmem_empty_bar + acc, ((i >> 1) & 1) ^ 1);      // the epilogue has drained this accumulator (two tiles ago)
+        const int acc = i % NACC;
+        mbar_wait(tmem_empty_bar + acc, ((i / NACC) & 1) ^ 1);    // the epilogue has drained this accumulator set
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + (uint32_t)acc * ACC_COLS;
+        const uint32_t tmem_d = tmem_base + (uint32_t)acc * SET_COLS;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int st = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
@@ -138,8 +144,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           for (int k = 0; k < BK / 8; ++k) {         // UMMA_K = 8 tf32 = 32 bytes = 2 descriptor units
             umma_tf32(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
             if (SPLIT) {
-              umma_tf32(tmem_d, adesc + LO + 2 * k, bdesc + 2 * k, idesc, 1u);
-              umma_tf32(tmem_d, adesc + 2 * k, bdesc + LO + 2 * k, idesc, 1u);
+              umma_tf32(tmem_d + ACC_COLS, adesc + LO + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+              umma_tf32(tmem_d + ACC_COLS, adesc + 2 * k, bdesc + LO + 2 * k, idesc, 1u);
             }
           }
           umma_commit(empty_bar + st);               // frees the smem stage once these MMAs have read it
@@ -173,8 +179,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll 1
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
       const int m0 = (tile / tiles_n) * TC_BM, n0 = (tile % tiles_n) * BN;
-      const int acc = i & 1;
-      mbar_wait(tmem_full_bar + acc, (i >> 1) & 1);
+      const int acc = i % NACC;
+      mbar_wait(tmem_full_bar + acc, (i / NACC) & 1);
       tc_fence_after();
       const int row = m0 + q * 32 + lane;
       const bool row_ok = row < ep.M;
@@ -188,7 +194,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       for (int c0 = 0; c0 < BN; c0 += 32) {
         if (n0 + c0 >= ep.N) break;                  // warp-uniform
         float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * ACC_COLS + (uint32_t)c0, v);
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * SET_COLS + (uint32_t)c0, v);
+        if (SPLIT) {
+          float x[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * SET_COLS + ACC_COLS + (uint32_t)c0, x);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += x[j];
+        }
         if (yr) {
           // d sigma term: rowsum[sample, n] += sum over the sample's chain rows of acc * yref  (segmented over the
           // samples under this warp's 32 rows; lane j ends up with column j)

@@ -781,7 +781,8 @@ extern "C" int dino_adam(float* params, const float* grad, float* m, float* v, i
                          float b2, float eps, int64_t t, dino_stream_t stream) {
   if (!params || !grad || !m || !v) return fail("dino_adam: null argument");
   if (t < 1) return fail("dino_adam: step t must be >= 1");
-  const double lr_t = (double)lr * sqrt(1.0 - pow((double)b2, (double)t)) / (1.0 - pow((double)b1, (double)t));
+  // the same formula as adam_dev_kernel (1 - b^t = -expm1(t log b)), in double
+  const double lr_t = (double)lr * sqrt(-expm1((double)t * log((double)b2))) / (-expm1((double)t * log((double)b1)));
   DINO_LAUNCH(launch_adam(params, grad, m, v, count, (float)lr_t, b1, b2, eps, S(stream)));
   return 0;
 }

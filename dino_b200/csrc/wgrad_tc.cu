@@ -23,6 +23,7 @@ constexpr int WG_BK = 32;                       // reduction rows per stage (one
 constexpr int WG_STAGES = 3;   // tf32: 96 KB, leaves room for a fused-MLP CTA on the same SM (the two overlap on separate streams); fp32x3: 192 KB
 constexpr int WG_OPER_BYTES = 128 * WG_BK * 4;  // 16 KB: up to 128 operand rows x 32 reduction elements
 constexpr int WG_RAW_BYTES = 2 * WG_OPER_BYTES;
+constexpr int WG_X3_CHUNKS = 32;                // fp32x3: longest reduction (in chunks of WG_BK rows) one TMEM accumulator takes
 
 struct WgOp {
   float* C;                 // gradient block [n_in, n_out], ldc = n_out
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(SPLIT ? 320 : 192, 1) wgrad_tc_kernel(const __
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(wg_u32(tmem_slot)), "r"(128u) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(wg_u32(tmem_slot)), "r"(SPLIT ? 256u : 128u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -151,8 +152,10 @@ __global__ void __launch_bounds__(SPLIT ? 320 : 192, 1) wgrad_tc_kernel(const __
           for (int k = 0; k < WG_BK / 8; ++k) {
             tc::umma_tf32(tmem_base, ad + kstep * k, bd + kstep * k, idesc, (c > 0 || k > 0) ? 1u : 0u);
             if (SPLIT) {
-              tc::umma_tf32(tmem_base, ad + LO + kstep * k, bd + kstep * k, idesc, 1u);
-              tc::umma_tf32(tmem_base, ad + kstep * k, bd + LO + kstep * k, idesc, 1u);
+              // the cross terms go to an accumulator of their own (columns 128..255): the tensor core's accumulation
+              // truncates, so the long main sum should see as few additions as possible (see gemm_tc.cu)
+              tc::umma_tf32(tmem_base + 128u, ad + LO + kstep * k, bd + kstep * k, idesc, (c > 0 || k > 0) ? 1u : 0u);
+              tc::umma_tf32(tmem_base + 128u, ad + kstep * k, bd + LO + kstep * k, idesc, 1u);
             }
           }
           asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(wg_u32(empty_bar + st)) : "memory");
@@ -192,6 +195,12 @@ __global__ void __launch_bounds__(SPLIT ? 320 : 192, 1) wgrad_tc_kernel(const __
               "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
             : "r"(taddr));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (SPLIT) {
+          float x[32];
+          tc::tmem_ld32(taddr + 128u, x);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + x[j]);
+        }
         if (m < op.n_in) {
           float* crow = op.C + (long long)m * op.n_out + n0 + c0;
 #pragma unroll
@@ -204,7 +213,7 @@ __global__ void __launch_bounds__(SPLIT ? 320 : 192, 1) wgrad_tc_kernel(const __
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 1)
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(SPLIT ? 256u : 128u) : "memory");
 }
 
 // ---- host ---------------------------------------------------------------------------------------------
@@ -251,6 +260,9 @@ cudaError_t launch_wgrad_tc(const GemmGroup& gg, int split, int num_sms, cudaStr
     w.n_tiles = (o.N + 127) / 128;
     const int tiles = m_tiles * w.n_tiles;
     long long splits = (long long)(target_ctas * ((double)o.K * tiles / total_work) / tiles + 0.999);
+    // fp32x3: at most WG_X3_CHUNKS chunks (4 x that many additions into the main accumulator) per CTA; the partial sums
+    // of the CTAs meet in fp32 atomics, which round to nearest
+    if (split && splits * WG_X3_CHUNKS < chunks) splits = (chunks + WG_X3_CHUNKS - 1) / WG_X3_CHUNKS;
     if (splits > chunks) splits = chunks;
     if (splits < 1) splits = 1;
     w.chunks_per_cta = (int)((chunks + splits - 1) / splits);

@@ -231,3 +231,34 @@ def test_bench_config_shapes_gradients(cuda_device):
         for a, b in zip(before[name], after):
             assert H.rel_err(a - b, grads[gi].numpy()) < 2e-4, name
             gi += 1
+
+
+def test_adam_step_size_host_and_device_agree_with_double(cuda_device):
+    """lr_t = lr sqrt(1 - b2^t) / (1 - b1^t) over 1 .. 10^5 steps: dino_adam (step number from the host) and
+    dino_adam_dev (step number read on the device) against the oracle's double-precision value.  One parameter with
+    g = 1, m = v = 0 moves by -lr_t (1 - b1) / (sqrt(1 - b2) + eps), which gives lr_t back."""
+    import ctypes as C
+    import math
+    from dino_b200.model import _stream
+    lib = _lib.load()
+    lr, b1, b2, eps = 1e-3, 0.9, 0.999, 1e-7
+    f32 = lambda x: float(np.float32(x))
+    unit = (1.0 - f32(b1)) / (math.sqrt(1.0 - f32(b2)) + f32(eps))
+    for t in (1, 2, 3, 10, 100, 1000, 6931, 10000, 31623, 100000):
+        want = f32(lr) * math.sqrt(1.0 - f32(b2) ** t) / (1.0 - f32(b1) ** t)
+        got = []
+        for dev_counter in (False, True):
+            p = torch.zeros(4, device="cuda"); g = torch.ones(4, device="cuda")
+            m = torch.zeros(4, device="cuda"); v = torch.zeros(4, device="cuda")
+            if dev_counter:
+                done = torch.tensor([t - 1], dtype=torch.int64, device="cuda")
+                _lib.check(lib.dino_adam_dev(C.c_void_p(p.data_ptr()), C.c_void_p(g.data_ptr()), C.c_void_p(m.data_ptr()),
+                                             C.c_void_p(v.data_ptr()), 4, lr, b1, b2, eps, C.c_void_p(done.data_ptr()),
+                                             _stream()), "dino_adam_dev")
+            else:
+                _lib.check(lib.dino_adam(C.c_void_p(p.data_ptr()), C.c_void_p(g.data_ptr()), C.c_void_p(m.data_ptr()),
+                                         C.c_void_p(v.data_ptr()), 4, lr, b1, b2, eps, t, _stream()), "dino_adam")
+            got.append(-float(p[0].item()) / unit)
+        assert abs(got[0] - want) < 2e-6 * want, (t, got, want)
+        assert abs(got[1] - want) < 2e-6 * want, (t, got, want)
+        assert abs(got[0] - got[1]) < 1e-6 * want, (t, got)
