@@ -12,7 +12,10 @@
 //     the epilogue of a tile overlaps the MMAs of the next);
 //   * four epilogue warps read TMEM with tcgen05.ld (32 lanes x 32 columns per instruction), apply
 //         rowsum[b,n] += acc * yref ; v = act(acc + bias) ; v = (v + add_pre) * scale[sample] + add_post
-//     and hand 32 x 32 blocks to TMA stores through a swizzled staging buffer (coalesced, clipped at M and N).
+//     and write 32 x 32 blocks through a swizzled staging buffer, so that every store instruction covers whole
+//     128-byte lines of C (a thread owns a ROW of the accumulator; stored directly, a warp would touch 32 lines per
+//     instruction).  TMA stores were tried here first: with two 4 KB boxes in flight per warp their issue-to-read
+//     latency, not bandwidth, set the pace (0.9 TB/s of output at K = 200).
 // Warp roles: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 2-5 epilogue, warps 6-9 converters.
 // Persistent CTAs (one per SM) walk the 128 x BN output tiles.  Out-of-range rows/columns/K are zero-filled by TMA,
 // so M, N, K are arbitrary; leading dimensions must be multiples of 4 floats.
@@ -31,7 +34,7 @@ constexpr int TC_BM = 128;
 
 struct TcEpilogue {
   int M, N, K;
-  int has_c;
+  float* C; long long ldc;
   int sdim;
   const float* scale; long long ld_sc;
   const float* add_pre; long long ld_ap;
@@ -52,10 +55,11 @@ __device__ __forceinline__ float4 tc_ld4(const float* row, int n, int N) {
   return v;
 }
 
-template <int BN, int BK, int STAGES, bool SPLIT>
-__global__ void __launch_bounds__(SPLIT ? 320 : 192, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-               const __grid_constant__ CUtensorMap tma_c, const TcEpilogue ep) {
+// EPI: 0 plain store; 1 chain terms (rowsum / add_pre / scale / add_post / rounding); 2 network terms (bias / softplus +
+// sigmoid / add_pre / add_post)
+template <int BN, int BK, int STAGES, bool SPLIT, int EPI>
+__global__ void __launch_bounds__(320, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep) {
   constexpr int A_BYTES = TC_BM * BK * 4, B_BYTES = BN * BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
   constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;           // columns of one accumulator
@@ -66,12 +70,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   constexpr uint32_t SET_COLS = SPLIT ? 2 * ACC_COLS : ACC_COLS;
   constexpr int NACC = 2 * SET_COLS <= 512 ? 2 : 1;          // two sets when they fit: the epilogue of tile i overlaps the MMAs of tile i+1
   constexpr uint32_t TMEM_COLS = NACC * SET_COLS;
-  constexpr int EPI_BUF = 32 * 128;                          // one 32 x 32 fp32 block, 128-byte rows, SWIZZLE_128B
+  constexpr int EPI_BUF = 32 * 128;                          // one 32 x 32 fp32 block, 128-byte rows, chunks swizzled by the row
+  constexpr int NEPI = SPLIT ? 4 : 8;                        // epilogue warps (warps 2 .. 2 + NEPI - 1); fp32x3: warps 6-9 are the converters
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* epi_stage = smem + STAGES * STAGE_BYTES;          // [4 warps][2][EPI_BUF]
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_stage + 4 * 2 * EPI_BUF);
+  uint8_t* epi_stage = smem + STAGES * STAGE_BYTES;          // [NEPI warps][EPI_BUF]
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_stage + NEPI * EPI_BUF);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* conv_bar = empty_bar + STAGES;                   // lo tiles of the stage written (fp32x3)
   uint64_t* tmem_full_bar = conv_bar + STAGES;               // [2] accumulator complete
@@ -86,13 +91,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
-    if (ep.has_c) asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_c) : "memory");
   }
   if (warp == 1) {
     if (lane == 0) {
       for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); mbar_init(conv_bar + i, 4); }
       mbar_init(tmem_full_bar, 1); mbar_init(tmem_full_bar + 1, 1);
-      mbar_init(tmem_empty_bar, 4); mbar_init(tmem_empty_bar + 1, 4);
+      mbar_init(tmem_empty_bar, NEPI); mbar_init(tmem_empty_bar + 1, NEPI);
       fence_mbar_init();
     }
     __syncwarp();
@@ -153,9 +157,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         umma_commit(tmem_full_bar + acc);            // accumulator complete
       }
     }
-  } else if (warp >= 6) {
+  } else if (SPLIT && warp >= 6) {
     // ===== converters (fp32x3): lo tile of every landed stage =====
-    if (SPLIT) {
+    {
       const int t = threadIdx.x - 192;
       int it = 0;
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -171,11 +175,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       }
     }
   } else {
-    // ===== epilogue: TMEM -> registers -> staging -> TMA store, one accumulator behind the MMA issuer =====
+    // ===== epilogue: TMEM -> registers -> staging -> global, one accumulator behind the MMA issuer =====
+    // The warps of the epilogue run a dependent instruction stream at ~13 cycles per instruction (1.5 warps per
+    // scheduler): what counts is the NUMBER of instructions per 32 x 32 block.  The epilogue class is a template
+    // parameter (no per-element tests of absent terms), whole blocks take unguarded vector loads, and tf32 (whose main
+    // loop is 3x shorter) splits the column blocks of a lane quarter over two warps.
     const int q = warp & 3;                        // TMEM lane quarter this warp may access
-    const uint32_t my_stage = smem_u32(epi_stage + q * 2 * EPI_BUF);
+    const int ew = warp - 2;                       // epilogue warp index
+    const int half = ew >> 2;                      // NEPI == 8: even / odd column blocks
+    const uint32_t my_stage = smem_u32(epi_stage + ew * EPI_BUF);
     const uint32_t sw = (uint32_t)(lane & 7);
-    int i = 0, n_stores = 0;
+    int i = 0;
 #pragma unroll 1
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
       const int m0 = (tile / tiles_n) * TC_BM, n0 = (tile % tiles_n) * BN;
@@ -185,31 +195,48 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       const int row = m0 + q * 32 + lane;
       const bool row_ok = row < ep.M;
       const int b = row_ok ? row / ep.sdim : 0;
-      const float* sc = ep.scale ? ep.scale + (long long)b * ep.ld_sc : nullptr;
-      const float* ap = ep.add_pre ? ep.add_pre + (long long)row * ep.ld_ap : nullptr;
-      const float* apo = ep.add_post ? ep.add_post + (long long)row * ep.ld_apo : nullptr;
-      const float* yr = ep.yref ? ep.yref + (long long)row * ep.ld_y : nullptr;
-      float* so = ep.s_out ? ep.s_out + (long long)row * ep.ld_s : nullptr;
+      const float* sc = (EPI == 1 && ep.scale) ? ep.scale + (long long)b * ep.ld_sc : nullptr;
+      const float* ap = (EPI != 0 && ep.add_pre) ? ep.add_pre + (long long)row * ep.ld_ap : nullptr;
+      const float* apo = (EPI != 0 && ep.add_post) ? ep.add_post + (long long)row * ep.ld_apo : nullptr;
+      const float* yr = (EPI == 1 && ep.yref) ? ep.yref + (long long)row * ep.ld_y : nullptr;
+      float* so = (EPI == 2 && ep.s_out) ? ep.s_out + (long long)row * ep.ld_s : nullptr;
+      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * SET_COLS;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = half * 32; c0 < BN; c0 += 32 * (NEPI / 4)) {
         if (n0 + c0 >= ep.N) break;                  // warp-uniform
+        const int nb = n0 + c0;
+        const bool full = nb + 32 <= ep.N;           // warp-uniform: the block lies inside N
         float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * SET_COLS + (uint32_t)c0, v);
+        tmem_ld32(tacc + (uint32_t)c0, v);
         if (SPLIT) {
           float x[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * SET_COLS + ACC_COLS + (uint32_t)c0, x);
+          tmem_ld32(tacc + ACC_COLS + (uint32_t)c0, x);
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += x[j];
         }
-        if (yr) {
+        // 32 floats of a row-indexed operand at this block's columns (zeros outside the matrix)
+        auto load32 = [&](float (&d)[32], const float* rowp, bool ok) {
+          if (full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 t = ok ? *reinterpret_cast<const float4*>(rowp + nb + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+              d[j] = t.x; d[j + 1] = t.y; d[j + 2] = t.z; d[j + 3] = t.w;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 t = ok ? tc_ld4(rowp, nb + j, ep.N) : make_float4(0.f, 0.f, 0.f, 0.f);
+              d[j] = t.x; d[j + 1] = t.y; d[j + 2] = t.z; d[j + 3] = t.w;
+            }
+          }
+        };
+        if (EPI == 1 && yr) {
           // d sigma term: rowsum[sample, n] += sum over the sample's chain rows of acc * yref  (segmented over the
           // samples under this warp's 32 rows; lane j ends up with column j)
           float p[32];
+          load32(p, yr, row_ok);
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 y = row_ok ? tc_ld4(yr, n0 + c0 + j, ep.N) : make_float4(0.f, 0.f, 0.f, 0.f);
-            p[j] = v[j] * y.x; p[j + 1] = v[j + 1] * y.y; p[j + 2] = v[j + 2] * y.z; p[j + 3] = v[j + 3] * y.w;
-          }
+          for (int j = 0; j < 32; ++j) p[j] *= v[j];
           const int r_first = m0 + q * 32;
           if (r_first < ep.M) {
             const int b_lo = r_first / ep.sdim, b_hi = min(r_first + 31, ep.M - 1) / ep.sdim;
@@ -218,56 +245,90 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll
               for (int j = 0; j < 32; ++j) mm[j] = (row_ok && b == bb) ? p[j] : 0.f;
               const float tot = colsum32(mm, lane);
-              if (n0 + c0 + lane < ep.N) atomicAdd(ep.rowsum + (long long)bb * ep.ld_rs + n0 + c0 + lane, tot);
+              if (nb + lane < ep.N) atomicAdd(ep.rowsum + (long long)bb * ep.ld_rs + nb + lane, tot);
             }
           }
+          if (!ep.C) continue;
         }
-        if (!ep.has_c && !so) continue;
-        if (row_ok) {
+        if (EPI == 2) {
+          if (ep.bias) {
+            float t[32];
+            load32(t, ep.bias, true);
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const int n = n0 + c0 + j;
-            if (n < ep.N) {
-              float4 x = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-              if (ep.bias) { const float4 t = tc_ld4(ep.bias, n, ep.N); x.x += t.x; x.y += t.y; x.z += t.z; x.w += t.w; }
-              if (ep.act) {
-                // sigmoid and softplus from one exponential: e = exp(-|x|)
-                float xs[4] = {x.x, x.y, x.z, x.w}, sg[4];
+            for (int j = 0; j < 32; ++j) v[j] += t[j];
+          }
+          if (ep.act) {
+            // sigmoid and softplus from one exponential: e = exp(-|x|)
+            float sg[32];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                  const float e = expf(-fabsf(xs[u])), r1 = 1.f / (1.f + e);
-                  sg[u] = xs[u] >= 0.f ? r1 : e * r1;
-                  xs[u] = fmaxf(xs[u], 0.f) + log1pf(e);
-                }
-                if (so) {
-                  if (n + 3 < ep.N) *reinterpret_cast<float4*>(so + n) = make_float4(sg[0], sg[1], sg[2], sg[3]);
-                  else {
+            for (int j = 0; j < 32; ++j) {
+              const float e = expf(-fabsf(v[j])), r1 = 1.f / (1.f + e);
+              sg[j] = v[j] >= 0.f ? r1 : e * r1;
+              v[j] = fmaxf(v[j], 0.f) + log1pf(e);
+            }
+            if (so && row_ok) {
+              if (full) {
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) if (n + u < ep.N) so[n + u] = sg[u];
-                  }
-                }
-                x = make_float4(xs[0], xs[1], xs[2], xs[3]);
+                for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(so + nb + j) = make_float4(sg[j], sg[j + 1], sg[j + 2], sg[j + 3]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (nb + j < ep.N) so[nb + j] = sg[j];
               }
-              if (ap) { const float4 t = tc_ld4(ap, n, ep.N); x.x += t.x; x.y += t.y; x.z += t.z; x.w += t.w; }
-              if (sc) { const float4 t = tc_ld4(sc, n, ep.N); x.x *= t.x; x.y *= t.y; x.z *= t.z; x.w *= t.w; }
-              if (apo) { const float4 t = tc_ld4(apo, n, ep.N); x.x += t.x; x.y += t.y; x.z += t.z; x.w += t.w; }
-              if (ep.round_tf32) { x.x = round_tf32_f(x.x); x.y = round_tf32_f(x.y); x.z = round_tf32_f(x.z); x.w = round_tf32_f(x.w); }
-              v[j] = x.x; v[j + 1] = x.y; v[j + 2] = x.z; v[j + 3] = x.w;
             }
           }
         }
-        if (ep.has_c) {
-          // the block leaves through a TMA store (rows >= M and columns >= N are clipped by the hardware)
-          const uint32_t buf = my_stage + (uint32_t)((n_stores & 1) * EPI_BUF);
-          if (n_stores >= 2 && lane == 0) tma_store_wait_read<1>();   // the store that last read this buffer is done with it
-          __syncwarp();
-          const uint32_t rowb = buf + (uint32_t)(lane * 128);
+        if (EPI != 0) {
+          if (ap) {
+            float t[32];
+            load32(t, ap, row_ok);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) sts128(rowb + ((((uint32_t)j) ^ sw) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-          fence_async_smem();
-          __syncwarp();
-          if (lane == 0) { tma_store_2d(&tma_c, buf, n0 + c0, m0 + q * 32); tma_store_commit(); }
-          ++n_stores;
+            for (int j = 0; j < 32; ++j) v[j] += t[j];
+          }
+          if (sc) {
+            float t[32];
+            load32(t, sc, row_ok);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= t[j];
+          }
+          if (apo) {
+            float t[32];
+            load32(t, apo, row_ok);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] += t[j];
+          }
+          if (ep.round_tf32) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = round_tf32_f(v[j]);
+          }
+        }
+        // stage the block (thread = row, 16-byte chunks XOR-swizzled by the row), then store it four rows per
+        // instruction: 8 lanes x 16 bytes = one whole 128-byte line of C per row
+        __syncwarp();                                // the previous block's reads of the staging buffer are done
+        const uint32_t rowb = my_stage + (uint32_t)(lane * 128);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sts128(rowb + ((((uint32_t)j) ^ sw) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+        const int ch = lane & 7, n = nb + 4 * ch;
+        float* cbase = ep.C + (long long)(m0 + q * 32 + (lane >> 3)) * ep.ldc + n;
+        const int rows_left = ep.M - (m0 + q * 32 + (lane >> 3));      // this lane's rows: rows_left > 4 * it
+        if (full) {
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + (lane >> 3);
+            const float4 o = lds128(my_stage + (uint32_t)(rr * 128) + ((((uint32_t)ch) ^ (uint32_t)(rr & 7)) << 4));
+            if (rows_left > 4 * it) *reinterpret_cast<float4*>(cbase + (long long)(4 * it) * ep.ldc) = o;
+          }
+        } else {
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + (lane >> 3);
+            const float4 o = lds128(my_stage + (uint32_t)(rr * 128) + ((((uint32_t)ch) ^ (uint32_t)(rr & 7)) << 4));
+            if (rows_left > 4 * it && n < ep.N) {
+              float* dst = cbase + (long long)(4 * it) * ep.ldc;
+              if (n + 3 < ep.N) *reinterpret_cast<float4*>(dst) = o;
+              else { dst[0] = o.x; if (n + 1 < ep.N) dst[1] = o.y; if (n + 2 < ep.N) dst[2] = o.z; }
+            }
+          }
         }
       }
       // this warp is done reading the accumulator: hand it back to the MMA issuer
@@ -275,7 +336,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       __syncwarp();
       if (lane == 0) mbar_arrive(tmem_empty_bar + acc);
     }
-    if (lane == 0) tma_store_wait_all<0>();          // shared memory must outlive the stores
   }
   // ===== teardown =====
   tc_fence_before();
@@ -376,37 +436,39 @@ bool gemm_tc_supported(const GemmOp& op) {
   return op.M > 0 && op.N > 0 && op.K > 0;
 }
 
-template <int BN, int BK, int STAGES, bool SPLIT>
-static cudaError_t launch_tc(const GemmOp& op, cudaStream_t st) {
-  CUtensorMap ma, mb, mc;
+template <int BN, int BK, int STAGES, bool SPLIT, int EPI>
+static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
+  CUtensorMap ma, mb;
   const int sw_in = BK == 32 ? (int)CU_TENSOR_MAP_SWIZZLE_128B : (int)CU_TENSOR_MAP_SWIZZLE_64B;
   // A[M,K] rows of a_sm floats; B operand is stored [N][K] (element (k,n) at n*b_sn + k)
   if (!tc_make_map(&ma, op.A, op.K, op.M, op.a_sm, BK, TC_BM, sw_in) || !tc_make_map(&mb, op.B, op.K, op.N, op.b_sn, BK, BN, sw_in))
     return cudaErrorInvalidValue;
-  if (op.C) {
-    if (!tc_make_map(&mc, op.C, op.N, op.M, op.ldc, 32, 32, (int)CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
-  } else {
-    mc = ma;
-  }
   TcEpilogue ep;
-  ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.has_c = op.C ? 1 : 0; ep.sdim = op.sdim > 0 ? op.sdim : 1;
+  ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.C = op.C; ep.ldc = op.ldc; ep.sdim = op.sdim > 0 ? op.sdim : 1;
   ep.scale = op.scale; ep.ld_sc = op.ld_sc; ep.add_pre = op.add_pre; ep.ld_ap = op.ld_ap;
   ep.add_post = op.add_post; ep.ld_apo = op.ld_apo; ep.bias = op.bias; ep.act = op.act;
   ep.s_out = op.act ? op.s_out : nullptr; ep.ld_s = op.ld_s;
   ep.yref = op.rowsum ? op.yref : nullptr; ep.ld_y = op.ld_y; ep.rowsum = op.rowsum; ep.ld_rs = op.ld_rs;
   ep.round_tf32 = SPLIT ? 0 : op.round_tf32;
   constexpr int RAW = (TC_BM + BN) * BK * 4;
-  constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + 4 * 2 * 32 * 128 + 256 + 1024;
+  constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + (SPLIT ? 4 : 8) * 32 * 128 + 256 + 1024;
   static_assert(SMEM <= 232448, "shared memory budget of one CTA");
   static std::atomic<unsigned long long> attr_mask{0};
-  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(gemm_tc_kernel<BN, BK, STAGES, SPLIT>), SMEM, attr_mask);
+  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI>), SMEM, attr_mask);
   if (e != cudaSuccess) return e;
   // persistent CTAs, one per SM: each walks its share of the 128 x BN output tiles
   const int num_sms = tc_current_num_sms();
   const long long n_tiles = (long long)((op.N + BN - 1) / BN) * ((op.M + TC_BM - 1) / TC_BM);
   const int grid = (int)(n_tiles < num_sms ? n_tiles : num_sms);
-  gemm_tc_kernel<BN, BK, STAGES, SPLIT><<<grid, SPLIT ? 320 : 192, SMEM, st>>>(ma, mb, mc, ep);
+  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI><<<grid, 320, SMEM, st>>>(ma, mb, ep);
   return cudaGetLastError();
+}
+
+template <int BN, int BK, int STAGES, bool SPLIT>
+static cudaError_t launch_tc(const GemmOp& op, cudaStream_t st) {
+  if (op.bias || op.act) return launch_tc1<BN, BK, STAGES, SPLIT, 2>(op, st);
+  if (op.rowsum || op.scale || op.add_pre || op.add_post || (op.round_tf32 && !SPLIT)) return launch_tc1<BN, BK, STAGES, SPLIT, 1>(op, st);
+  return launch_tc1<BN, BK, STAGES, SPLIT, 0>(op, st);
 }
 
 cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st) {
@@ -422,8 +484,8 @@ cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st) {
     if (bn == 64) return launch_tc<64, 32, 4, true>(op, st);
     if (bn == 128) return launch_tc<128, 32, 3, true>(op, st);
     if (variant == 1) return launch_tc<256, 32, 2, true>(op, st);
-    if (variant == 2) return launch_tc<128, 32, 3, true>(op, st);
-    return launch_tc<256, 16, 4, true>(op, st);
+    if (variant == 2) return launch_tc<256, 16, 4, true>(op, st);
+    return launch_tc<128, 32, 3, true>(op, st);        // measured best of the three at [25600, 1024] x [1024, 1024] (profiles/r02b)
   }
   if (bn == 64) return launch_tc<64, 32, 4, false>(op, st);
   if (bn == 128) return launch_tc<128, 32, 4, false>(op, st);
