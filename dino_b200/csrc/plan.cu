@@ -458,6 +458,24 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
 
 static int push_wgrad(DinoPlan* p, GemmGroup& g, const GemmOp& op, cudaStream_t st);
 
+// dino_plan_profile: CUDA events around the Jacobian-chain stage of a step (the fused chain kernel, or the chain
+// contractions of the layer-by-layer path: forward chain, H1 loss, data-gradient chain)
+static int prof_begin(DinoPlan* p, cudaStream_t st) {
+  if (!p->profile) return 0;
+  if (p->ev_pending && cudaEventSynchronize(p->ev1) == cudaSuccess) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p->ev0, p->ev1) == cudaSuccess) { p->prof_ms += ms; p->prof_n += 1; }
+  }
+  DINO_CUDA(cudaEventRecord(p->ev0, st));
+  return 0;
+}
+static int prof_end(DinoPlan* p, cudaStream_t st) {
+  if (!p->profile) return 0;
+  DINO_CUDA(cudaEventRecord(p->ev1, st));
+  p->ev_pending = true;
+  return 0;
+}
+
 // Fused tcgen05 path: prep weights, then ONE kernel runs chain forward [+ H1 loss [+ chain backward]].
 // mlp_mode: 0 = the MLP forward (and the output loss) ran in their own launches; 1 = run the forward inside the chain
 // kernel; 2 = forward + output-loss statistics; 3 = forward + statistics + d loss / d q_hat (coef_q = 2 w_l2 / B_global)
@@ -471,17 +489,10 @@ static int run_chain_fused(DinoPlan* p, const float* params, const DinoBatch* b,
   else if (p->jac_mode == DINO_JAC_FULL) *top_out = {ws + p->off_ident, p->ld_ident, p->s};
   else *top_out = {b->seed, (long long)p->d_out, p->s};
   if (!weights_ready) DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
-  if (p->profile) {
-    if (p->ev_pending && cudaEventSynchronize(p->ev1) == cudaSuccess) {
-      float ms = 0.f;
-      if (cudaEventElapsedTime(&ms, p->ev0, p->ev1) == cudaSuccess) { p->prof_ms += ms; p->prof_n += 1; }
-    }
-    DINO_CUDA(cudaEventRecord(p->ev0, st));
-  }
+  if (prof_begin(p, st)) return 1;
   DINO_LAUNCH(launch_chain_fused(p->chain_maps, p->chain, p->chain_steps, ws, b->J, b->J_sqnorm, b->idx, seed, B, coef, do_loss,
                                  do_backward, stats, p->mlp, params, b->m, b->q, b->q_sqnorm, coef_q, mlp_mode, p->split, st));
-  if (p->profile) { DINO_CUDA(cudaEventRecord(p->ev1, st)); p->ev_pending = true; }
-  return 0;
+  return prof_end(p, st);
 }
 
 // weight gradients of the chain: dW_l += dR_l^T Q_l for every trainable layer (joins the grouped launch)
@@ -754,9 +765,11 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
     }
     if (push_chain_wgrads(p, B, grad, top, wg, st)) return 1;
   } else {
+    if (prof_begin(p, st)) return 1;
     if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
     if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st)) return 1;
     if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, wg, st)) return 1;
+    if (prof_end(p, st)) return 1;
   }
   if (run_mlp_backward(p, params, B, grad, wg, st)) return 1;
   return flush_wgrad(p, wg, st);

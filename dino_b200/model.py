@@ -297,6 +297,28 @@ class DeviceDataset:
                 _lib.check(lib.dino_sample_sqnorms(C.c_void_p(self.J.data_ptr()), self.n, self.J[0].numel(),
                                                    C.c_void_p(self.jn2.data_ptr()), _stream()), "dino_sample_sqnorms")
 
+    @classmethod
+    def from_device(cls, jac_mode: int, m, q=None, J=None, seed=None, U=None, V=None):
+        """A dataset over tensors that already live on the device (fp32, contiguous): nothing is copied."""
+        import torch
+        lib = _lib.load()
+        ds = cls.__new__(cls)
+        ds.m, ds.q, ds.J, ds.U, ds.V, ds.seed = m, q, J, U, V, seed
+        ds.n = int(m.shape[0])
+        ds.qn2 = ds.jn2 = None
+        for t in (m, q, J, U, V, seed):
+            if t is not None and (t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda):
+                raise ValueError("DeviceDataset.from_device needs contiguous fp32 CUDA tensors")
+        if q is not None:
+            ds.qn2 = torch.empty(ds.n, dtype=torch.float32, device=m.device)
+            _lib.check(lib.dino_sample_sqnorms(C.c_void_p(q.data_ptr()), ds.n, q[0].numel(), C.c_void_p(ds.qn2.data_ptr()),
+                                               _stream()), "dino_sample_sqnorms")
+        if J is not None and jac_mode != _lib.JAC_NONE:
+            ds.jn2 = torch.empty(ds.n, dtype=torch.float32, device=m.device)
+            _lib.check(lib.dino_sample_sqnorms(C.c_void_p(J.data_ptr()), ds.n, J[0].numel(), C.c_void_p(ds.jn2.data_ptr()),
+                                               _stream()), "dino_sample_sqnorms")
+        return ds
+
     def batch(self, idx_ptr: Optional[int], row_offset: int = 0) -> _lib.DinoBatch:
         """DinoBatch for rows addressed by a device int32 index array (idx_ptr) or, when idx_ptr is
         None, the contiguous rows starting at row_offset."""
@@ -660,9 +682,16 @@ class DinoModel:
         return stats.cpu().numpy()
 
     def predict(self, x, batch_size=32, **_ignored):
+        out = self.predict_device(x, batch_size)
+        if isinstance(out, list):
+            return [t.cpu().numpy() for t in out]
+        return out.cpu().numpy()
+
+    def predict_device(self, x, batch_size=32):
+        """``predict`` whose results stay on the device (torch tensors); ``x`` may be a DeviceDataset."""
         import torch
         lib = _lib.load()
-        ds = self._dataset(x, None)
+        ds = x if isinstance(x, DeviceDataset) else self._dataset(x, None)
         plan = self._plan(min(batch_size, ds.n))
         params = self.core.device_params()
         q = torch.empty(ds.n, self.core.d_out, dtype=torch.float32, device=params.device)
@@ -681,8 +710,8 @@ class DinoModel:
                                              C.c_void_p(q[lo].data_ptr()), C.c_void_p(J[lo].data_ptr()), st),
                            "dino_jacobian")
         if J is None:
-            return q.cpu().numpy()
-        return [q.cpu().numpy(), J.cpu().numpy()]
+            return q
+        return [q, J]
 
     # ---- one optimiser step ------------------------------------------------------------------------
     def _ensure_opt_state(self):

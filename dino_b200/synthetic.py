@@ -156,6 +156,33 @@ def make_dataset(arch: Arch, n: int, seed: int, noise=0.01):
     return dict(m=m.astype(np.float32), q=q.astype(np.float32), J=J.astype(np.float32)), tw
 
 
+def make_device_dataset(arch: Arch, n: int, seed: int, noise=0.01, chunk=512):
+    """The teacher data of ``make_dataset`` for large n / wide networks, produced ON the device: the teacher's outputs
+    and Jacobians come from this library's own forward + Jacobian-chain kernels (fp32x3 mode), the noise from torch's
+    device generator.  Data preparation, not the training path.  Returns (DeviceDataset, teacher weights, m on the host)."""
+    import torch
+    from .model import DeviceDataset
+    from . import _lib
+    rng = np.random.default_rng(seed)
+    tw = random_weights(arch, rng, teacher=True)
+    m_host = rng.standard_normal((n, arch.d_in), dtype=np.float32)
+    teacher = build_model(arch, tw, precision="fp32x3")
+    dev = teacher.core.device_params().device
+    m = torch.from_numpy(m_host).to(dev)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(seed + 7)
+    q = torch.empty(n, arch.d_out, dtype=torch.float32, device=dev)
+    J = torch.empty(n, arch.d_out, arch.d_in, dtype=torch.float32, device=dev)
+    for lo in range(0, n, chunk):
+        hi = min(n, lo + chunk)
+        part = DeviceDataset.from_device(_lib.JAC_FULL, m[lo:hi])
+        qc, Jc = teacher.predict_device(part, batch_size=min(chunk, 256))
+        q[lo:hi] = qc + noise * torch.randn(qc.shape, generator=gen, device=dev)
+        J[lo:hi] = Jc + (noise / math.sqrt(arch.d_in)) * torch.randn(Jc.shape, generator=gen, device=dev)
+    teacher.core.invalidate_plans()
+    return DeviceDataset.from_device(_lib.JAC_FULL, m, q, J), tw, m_host
+
+
 def build_model(arch: Arch, weights=None, name_prefix="", jac="full", precision=None):
     """A DinoModel of ``arch`` (through the reference-named builders) with ``weights`` injected."""
     from .construction.neuralNetworks import projected_dense, projected_resnet, generic_dense

@@ -192,9 +192,11 @@ int dino_gemm_nt_acc(int engine, const float* d_XT, int64_t ldx, const float* d_
 int dino_gemm_tn_acc(int engine, const float* d_X, int64_t ldx, const float* d_Y, int64_t ldy, float* d_C,
                      int32_t rows, int32_t n_in, int32_t n_out, dino_stream_t stream);
 
-/* Measurement aid: time the dominant kernel of the step (the fused Jacobian-chain kernel) with CUDA events on the
- * launching stream.  enable = 1 starts (totals reset), enable = 0 stops; the running totals are returned.  Use with
- * eager steps only (events are not recorded inside a replayed graph).  No counterpart in the reference. */
+/* Measurement aid: time the Jacobian-chain stage of dino_h1_fwd_bwd with CUDA events on the launching stream: the
+ * fused chain kernel, or - for networks wider than 128 - the chain contractions of the layer-by-layer path (forward
+ * chain, H1 loss kernel, data-gradient chain).  enable = 1 starts (totals reset), enable = 0 stops; the running totals
+ * are returned.  Use with eager steps only (events are not recorded inside a replayed graph).  No counterpart in the
+ * reference. */
 int dino_plan_profile(DinoPlan* plan, int enable, double* out_ms_sum, int64_t* out_count);
 
 /* Debug aid: %globaltimer stamps [step][phase] of CTA 0 of the fused chain kernel's last launch (all zero unless
