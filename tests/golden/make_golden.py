@@ -44,7 +44,7 @@ def load_reference():
         sys.modules[pkg] = m
     mods = {}
     for name in ("dataUtilities", "neuralNetworks", "neuralNetworkUtilities", "trainingUtilities",
-                 "jacobianConstruction", "jacobianTrainingDriver"):
+                 "jacobianConstruction", "jacobianTrainingDriver", "observableConstruction"):
         spec = importlib.util.spec_from_file_location("refdino.construction." + name, os.path.join(REF, name + ".py"))
         mod = importlib.util.module_from_spec(spec)
         sys.modules[spec.name] = mod
@@ -110,6 +110,11 @@ def main():
     g["settings_repr"] = np.array([repr(js[k]) for k in sorted(js.keys())])
     g["opt_keys"] = np.array(sorted(opt.keys()))
     g["opt_repr"] = np.array([repr(opt[k]) for k in sorted(opt.keys())])
+    osd = ref["observableConstruction"].observable_network_settings({})
+    osd.pop("opt_parameters")
+    osd.pop("problem_settings")
+    g["obs_settings_keys"] = np.array(sorted(osd.keys()))
+    g["obs_settings_repr"] = np.array([repr(osd[k]) for k in sorted(osd.keys())])
     np.savez_compressed(OUT, **g)
     print("wrote", OUT, len(g), "arrays", os.path.getsize(OUT), "bytes")
 

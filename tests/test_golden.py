@@ -133,3 +133,13 @@ def test_settings_dictionaries_match_reference_keys_and_defaults():
     assert [repr(js[k]) for k in sorted(js.keys())] == list(G["settings_repr"])
     assert sorted(opt.keys()) == list(G["opt_keys"])
     assert [repr(opt[k]) for k in sorted(opt.keys())] == list(G["opt_repr"])
+
+
+def test_observable_settings_dictionary_matches_reference_keys_and_defaults():
+    """observable_network_settings (observableConstruction.py:38-78): every key and default, pinned to the reference."""
+    osd = DC.observable_network_settings({})
+    opt = osd.pop("opt_parameters")
+    osd.pop("problem_settings")
+    assert sorted(osd.keys()) == list(G["obs_settings_keys"])
+    assert [repr(osd[k]) for k in sorted(osd.keys())] == list(G["obs_settings_repr"])
+    assert sorted(opt.keys()) == list(G["opt_keys"])

@@ -18,6 +18,7 @@ import pytest
 import torch
 
 import helpers as H
+from oracle import dino_oracle as O
 from dino_b200 import _lib, synthetic as S
 from dino_b200.model import DeviceDataset, _stream
 
@@ -54,21 +55,26 @@ def _both_ways(arch, B, seed):
     _lib.check(lib.dino_forward_noalloc(C.byref(spec), C.c_void_p(params.data_ptr()), C.c_void_p(m.data_ptr()), B,
                                         C.c_void_p(q_new.data_ptr()), _stream()), "dino_forward_noalloc")
     torch.cuda.synchronize()
-    return q_new.cpu().numpy(), q_ref.cpu().numpy()
+    # the oracle's forward pass (fp64) on the same inputs: the checker of both entry points
+    net = H.oracle_net(arch, w)
+    q_or, _ = O.batch_jacobian(net, torch.tensor(data["m"], dtype=torch.float64), False)
+    return q_new.cpu().numpy(), q_ref.cpu().numpy(), q_or.detach().numpy()
 
 
 def test_noalloc_forward_matches_forward_twice_in_a_row(cuda_device):
     # call 1: wide dense network, large batch -> fills much of the shared array
     a1 = S.Arch("rb_dense", 100, 50, hidden=[96, 64, 50], frozen_output=True, r_out=50)
-    got, want = _both_ways(a1, 200, 31)
+    got, want, oracle = _both_ways(a1, 200, 31)
     assert np.isfinite(got).all()
     assert H.rel_err(got, want) < 1e-5
+    assert H.rel_err(got, oracle) < 1e-5 and H.rel_err(want, oracle) < 1e-5
     # call 2, straight after: a smaller residual network and batch; stale activations of call 1 are
     # still in the array and must not leak into the result
     a2 = H.SMALL["resnet"]
-    got, want = _both_ways(a2, 7, 32)
+    got, want, oracle = _both_ways(a2, 7, 32)
     assert np.isfinite(got).all()
     assert H.rel_err(got, want) < 1e-5
+    assert H.rel_err(got, oracle) < 1e-5 and H.rel_err(want, oracle) < 1e-5
 
 
 def test_noalloc_rejects_sizes_beyond_the_fixed_array(cuda_device):
