@@ -51,6 +51,8 @@ SIGNATURES = {
     "dino_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(DinoBatch), C.c_int32, C.c_void_p, C.c_void_p]),
     "dino_jacobian": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(DinoBatch), C.c_int32, C.c_void_p, C.c_void_p,
                                 C.c_void_p]),
+    "dino_jvp": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(DinoBatch), C.c_int32, C.c_void_p, C.c_int32, C.c_void_p,
+                           C.c_void_p]),
     "dino_h1_fwd_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(DinoBatch), C.c_int32, C.c_float, C.c_float,
                                   C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "dino_h1_eval": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(DinoBatch), C.c_int32, C.c_void_p, C.c_void_p]),

@@ -722,6 +722,39 @@ extern "C" int dino_jacobian(DinoPlan* p, const float* params, const DinoBatch* 
   return 0;
 }
 
+// J(m) mhat by ONE forward-mode sweep: t_0 = mhat, t_{l+1} = (t_l W_l) * sg_l [+ t_skip]  (the tangent of the MLP forward).
+// The reference contracts the full batch Jacobian with mhat (inferenceOracle.py:96-98); a single column costs one
+// more pass of the network's own size.  mhat_rows = 1: one direction shared by all samples; = B: one per sample.
+extern "C" int dino_jvp(DinoPlan* p, const float* params, const DinoBatch* b, int32_t B, const float* d_mhat,
+                        int32_t mhat_rows, float* d_out, dino_stream_t stream) {
+  if (!p || !params || !b || !d_mhat || !d_out) return fail("dino_jvp: null argument");
+  if (!p->ws) return fail("dino_jvp: workspace not bound");
+  if (B < 1 || B > p->max_batch) return fail("dino_jvp: batch size outside [1, max_batch]");
+  if (!b->m) return fail("dino_jvp: batch.m is null");
+  if (mhat_rows != 1 && mhat_rows != B) return fail("dino_jvp: mhat must have 1 row or one row per sample");
+  cudaStream_t st = S(stream);
+  if (run_mlp_forward(p, params, b, B, st)) return 1;        // leaves sg_l = act'(a_l) of every layer in the workspace
+  float* ws = p->ws;
+  auto t_ptr = [&](int l) { return ws + p->off_dz[l % 3]; };
+  // t_0 = mhat, one row per sample (a shared direction is broadcast)
+  DINO_LAUNCH(launch_scale_seed(d_mhat, mhat_rows == 1 ? 0 : p->d_in, p->d_in, nullptr, 0, B, 1, p->d_in, t_ptr(0), p->ld_dz, st));
+  for (int l = 0; l < p->L; ++l) {
+    const LayerPlan& lp = p->layers[l];
+    GemmOp op = gemm_op_zero();
+    op.A = t_ptr(l); op.a_sm = p->ld_dz; op.a_sk = 1;
+    op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1;
+    op.M = B; op.N = lp.n_out; op.K = lp.n_in; op.sdim = 1;
+    if (lp.act == DINO_ACT_SOFTPLUS) { op.scale = ws + lp.sg_off; op.ld_sc = lp.ld_out; }
+    if (lp.skip_from >= 0) {
+      op.add_post = t_ptr(lp.skip_from); op.ld_apo = p->ld_dz;
+    }
+    if (l == p->L - 1) { op.C = d_out; op.ldc = p->d_out; }
+    else { op.C = t_ptr(l + 1); op.ldc = p->ld_dz; }
+    if (gemm_simt_only(p, op, st)) return 1;
+  }
+  return 0;
+}
+
 extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch* b, int32_t B, float w_l2,
                                float w_h1, float inv_gb, float* grad, float* stats, dino_stream_t stream) {
   if (!grad || !stats) return fail("dino_h1_fwd_bwd: null output");

@@ -1,7 +1,8 @@
 """InferenceOracle without the PDE model: ``J``, ``Jvp``, ``Jtvp`` of a trained network
 (inferenceOracle.py:105-139) served by the CUDA Jacobian chain.  The reference builds three extra
 TF graphs (Jt-product, full Jacobian, J-product by contraction with the full Jacobian, :79-98);
-here all three come from ``dino_jacobian``.  The PDE-backed methods (cost/misfit/gradient with
+here ``J`` is ``dino_jacobian``, ``Jtvp`` a reverse chain with the single seed row qhat (s = 1) and ``Jvp`` one
+forward-mode sweep (``dino_jvp``): neither product materialises the Jacobian.  The PDE-backed methods (cost/misfit/gradient with
 'PDE', hIPPYlib vectors) need FEniCS and are not provided."""
 import numpy as np
 
@@ -30,6 +31,7 @@ class InferenceOracle:
         self.dM = int(np.prod(self.parameter_shape))
         self._jac = neural_operator if len(neural_operator.outputs) == 2 else \
             equip_model_with_full_jacobian(neural_operator)
+        self._jt = None                             # the same network with a one-row output seed (Jtvp)
 
     @staticmethod
     def _rows(a):
@@ -43,14 +45,20 @@ class InferenceOracle:
         return J[0] if mi.shape[0] == 1 else J
 
     def Jvp(self, mi, mhat, sess=None):
-        """J(m) mhat (inferenceOracle.py:116-125)."""
+        """J(m) mhat (inferenceOracle.py:116-125).  The reference contracts the full batch Jacobian with mhat
+        (:96-98, "fwd mode was difficult to get to work in tf"); here it is one forward-mode sweep (dino_jvp)."""
         mi, mhat = self._rows(mi), self._rows(mhat)
-        return np.einsum('ikj,ij->ik', self._jac.predict(mi)[1], mhat)[0]
+        return self._jac.jvp(mi, mhat)[0]
 
     def Jtvp(self, mi, qhat):
-        """J(m)^T qhat (inferenceOracle.py:105-114)."""
+        """J(m)^T qhat (inferenceOracle.py:79-82,105-114): a reverse chain seeded with the single row qhat."""
         mi, qhat = self._rows(mi), self._rows(qhat)
-        return np.einsum('ikj,ik->ij', self._jac.predict(mi)[1], qhat)[0]
+        if self._jt is None:
+            from ..model import DinoModel
+            self._jt = DinoModel(self._jac.core, 'out_reduced', seed_dim=1, output_basis=np.zeros((self.dQ, 1), np.float32),
+                                 precision=self._jac.precision)
+        self._jt.output_basis = np.ascontiguousarray(qhat[0].astype(np.float32)[:, None])        # Phi = qhat as a column
+        return self._jt.predict(mi)[1][0, 0]
 
     def _pde_only(self, *a, **k):
         raise NotImplementedError('needs the hIPPYlib/FEniCS model wrapper, which this build does not include')

@@ -713,6 +713,29 @@ class DinoModel:
             return q
         return [q, J]
 
+    def jvp(self, x, mhat, batch_size=32):
+        """J_hat(m) mhat for every row of x: one forward-mode sweep (dino_jvp).  mhat: [d_in] or [1, d_in] (shared
+        direction) or [n, d_in] (one per sample).  Returns [n, d_out]."""
+        import torch
+        lib = _lib.load()
+        ds = x if isinstance(x, DeviceDataset) else self._dataset(x, None)
+        mh = np.ascontiguousarray(np.atleast_2d(np.asarray(mhat, dtype=np.float32)))
+        if mh.shape[1] != self.core.d_in or mh.shape[0] not in (1, ds.n):
+            raise ValueError(f"mhat has shape {mh.shape}; expected [1 or {ds.n}, {self.core.d_in}]")
+        plan = self._plan(min(batch_size, ds.n))
+        params = self.core.device_params()
+        mh_d = torch.from_numpy(mh).to(params.device)
+        out = torch.empty(ds.n, self.core.d_out, dtype=torch.float32, device=params.device)
+        st = _stream()
+        for lo in range(0, ds.n, batch_size):
+            B = min(batch_size, ds.n - lo)
+            batch = ds.batch(None, lo)
+            shared = mh.shape[0] == 1 and ds.n != 1
+            rows, src = (1, mh_d) if shared else (B, mh_d[lo])
+            _lib.check(lib.dino_jvp(plan.handle, C.c_void_p(params.data_ptr()), C.byref(batch), B, C.c_void_p(src.data_ptr()),
+                                    rows, C.c_void_p(out[lo].data_ptr()), st), "dino_jvp")
+        return out.cpu().numpy()
+
     # ---- one optimiser step ------------------------------------------------------------------------
     def _ensure_opt_state(self):
         import torch

@@ -107,6 +107,14 @@ int dino_forward(DinoPlan* plan, const float* d_params, const DinoBatch* batch, 
 int dino_jacobian(DinoPlan* plan, const float* d_params, const DinoBatch* batch, int32_t B,
                   float* d_q_out, float* d_J_out, dino_stream_t stream);
 
+/* Jacobian-vector product J_hat(m) mhat [B, d_out] by one forward-mode sweep through the network (the array form of
+ * InferenceOracle.Jvp, inferenceOracle.py:96-98,116-125, which contracts the full batch Jacobian with mhat).
+ * d_mhat is [mhat_rows, d_in] dense with mhat_rows = 1 (one direction for all samples) or B.  The transposed product
+ * J_hat^T qhat (InferenceOracle.Jtvp, :79-82,105-114) is dino_jacobian of a DINO_JAC_OUT_REDUCED plan with
+ * seed_dim = 1 and batch.seed = qhat: a reverse chain of a single row. */
+int dino_jvp(DinoPlan* plan, const float* d_params, const DinoBatch* batch, int32_t B, const float* d_mhat,
+             int32_t mhat_rows, float* d_out, dino_stream_t stream);
+
 /* One training step minus the optimiser: forward, Jacobian, w_l2*normalized_mse +
  * w_h1*normalized_mse_matrix, and d loss / d theta by the double backward.  Replaces what
  * session.run(train_op) computes inside network.fit (trainingUtilities.py:135-138).
