@@ -44,7 +44,12 @@ def get_the_data(settings, remapped_data=None, unflattened_data=None, verbose=Tr
             unflattened_train_dict = unflattened_data[0]
             unflattened_test_dict = None if len(unflattened_data) == 1 else unflattened_data[1]
         if settings['train_full_jacobian']:
-            shape_targets = remap_jacobian_data
+            # settings['device_data'] (extension, default False): form the dense targets with device contractions
+            # (float32) instead of the reference's host float64 loop
+            if settings.get('device_data', False):
+                from .deviceData import remap_jacobian_data_device as shape_targets
+            else:
+                shape_targets = remap_jacobian_data
         else:
             def shape_targets(d):
                 return flatten_data(d, target_rank=settings['target_rank'], batch_rank=settings['batch_rank'])
@@ -224,9 +229,13 @@ def jacobian_training_driver(settings, remapped_data=None, unflattened_data=None
             print('reduced_input_dim = ', settings['reduced_input_dim'])
         if settings['reduced_output_training']:
             settings['reduced_output_dim'] = projector_dict['output'].shape[1]
-        train_dict, test_dict = prune_the_data(projector_dict, train_dict, test_dict,
-                                               input_pruning=settings['reduced_input_training'],
-                                               output_pruning=settings['reduced_output_training'])
+        if settings.get('device_data', False):
+            from .deviceData import prune_the_data_device as prune
+        else:
+            prune = prune_the_data
+        train_dict, test_dict = prune(projector_dict, train_dict, test_dict,
+                                      input_pruning=settings['reduced_input_training'],
+                                      output_pruning=settings['reduced_output_training'])
     regressor = setup_the_dino(settings, train_dict, projector_dict,
                                reduced_input_training=settings['reduced_input_training'],
                                reduced_output_training=settings['reduced_output_training'])

@@ -71,7 +71,22 @@ def test_driver_end_to_end_and_weight_pickle(cuda_device, tmp_path):
     assert np.isfinite(out["l2_train"]) and np.isfinite(out["h1_train"])
 
 
-@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("tf32", 2e-2)])
+def test_driver_with_device_side_data_contractions(cuda_device, tmp_path):
+    """settings['device_data']: remap_jacobian_data / prune_the_data as device contractions (float32); the driver ends
+    at (almost) the same weights as with the reference's host float64 path."""
+    data_dir, _ = _make_data_dir(tmp_path)
+    ws = []
+    for dev_data in (False, True):
+        settings = _settings(data_dir, tmp_path)
+        settings["device_data"] = dev_data
+        np.random.seed(7)
+        reg = D.jacobian_training_driver(settings)
+        ws.append([w for l in reg.layers for w in l.get_weights()])
+    for a, b in zip(*ws):
+        assert H.rel_err(a, b) < 1e-3
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32x3", 5e-4), ("fp32", 1e-4), ("tf32", 2e-2)])
 def test_driver_stages_match_oracle(cuda_device, tmp_path, precision, tol, monkeypatch):
     """get_the_data -> setup_reduced_bases -> prune_the_data -> setup_the_dino -> train_dino, then the same reduced
     problem through the oracle's fit with identical initial weights and permutations."""

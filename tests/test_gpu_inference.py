@@ -33,3 +33,19 @@ def test_jvp_and_jtvp_without_the_jacobian(cuda_device, name, precision):
     Mh = rng.normal(size=(9, arch.d_in)).astype(np.float32)
     assert H.rel_err(model.jvp(data["m"], Mh, batch_size=4), np.einsum("bij,bj->bi", Jo, Mh)) < 1e-5
     assert H.rel_err(model.jvp(data["m"], Mh[2], batch_size=4), np.einsum("bij,j->bi", Jo, Mh[2])) < 1e-5
+
+
+@pytest.mark.parametrize("q,m,noise", [(10, 40, 0.3), (50, 100, 0.05), (7, 4225, 0.5), (20, 37, 1e-3)])
+def test_jacobian_error_metrics_on_the_device(cuda_device, q, m, noise):
+    """The seven metrics of compute_jacobian_errors (jacobianTests.py:104-126) from three d_Q x d_Q device Gram
+    contractions per sample vs the oracle's restatement of the reference's lines (float64 numpy, SVD of the truth)."""
+    from dino_b200.evaluation.jacobianTests import jacobian_error_metrics_device
+    rng = np.random.default_rng(q + m)
+    n = 5
+    J = rng.normal(size=(n, q, m))
+    P = J + noise * rng.normal(size=(n, q, m))
+    got = jacobian_error_metrics_device(torch.tensor(P, dtype=torch.float32).cuda(), torch.tensor(J, dtype=torch.float32).cuda())
+    for b in range(n):
+        want = O.jacobian_errors(P[b].astype(np.float32).astype(np.float64), J[b].astype(np.float32).astype(np.float64))
+        for k, v in want.items():
+            assert abs(got[k][b] - v) < 2e-4 * max(v, 1e-3), (k, got[k][b], v)
