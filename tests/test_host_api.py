@@ -32,13 +32,15 @@ def test_missing_library_is_a_loud_error(monkeypatch):
 
 
 def test_no_product_module_imports_the_oracle():
-    for base, _, files in os.walk(os.path.join(ROOT, "dino_b200")):
-        for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".h")):
-                assert "oracle" not in open(os.path.join(base, f)).read().replace("InferenceOracle", "").replace(
-                    "inferenceOracle", "").replace("oracle_dictionary", "").replace("``oracle.J``", "").replace(
-                    "for file, oracle in", "").replace("oracle.J(", "").replace("hasattr(oracle", "").replace(
-                    "oracle.predict", "").replace("{name: object", ""), (base, f)
+    """Nothing under dino_b200/ or dino/ imports, loads or executes anything under oracle/ (the word itself also names
+    the reference's InferenceOracle objects, so the check is on import statements and paths)."""
+    import re
+    pat = re.compile(r"^\s*(from|import)\s+oracle\b|dino_oracle|oracle/|[\"']oracle[\"']", re.M)
+    for top in ("dino_b200", "dino"):
+        for base, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h")):
+                    assert not pat.search(open(os.path.join(base, f)).read()), (base, f)
 
 
 def test_projected_dense_structure_and_names():
