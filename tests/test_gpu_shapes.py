@@ -163,3 +163,25 @@ def test_fit_with_validation_data(cuda_device):
     val = ([data["m"][32:]], [data["q"][32:], data["J"][32:]])
     hist = model.fit([data["m"][:32]], [data["q"][:32], data["J"][:32]], validation_data=val, epochs=3, batch_size=8)
     assert len(hist.history["val_loss"]) == 3 and np.isfinite(hist.history["val_loss"]).all()
+
+
+def test_two_plans_on_two_devices_in_one_process(cuda_device):
+    """Kernel attributes (dynamic shared memory) are per DEVICE and launch descriptors are not process-global: one
+    process drives a plan on cuda:0 and another on cuda:1, alternating, in both tensor-core modes."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs in one box")
+    results = {}
+    for precision in ("fp32x3", "tf32"):
+        for cfg, B in (("cfg2", 64), ("cfg3", 4)):
+            arch = S.CONFIGS[cfg]["arch"]
+            data, tw = S.make_dataset(arch, B, 3)
+            w = S.student_weights(arch, 4, tw, bias_noise=0.1)
+            for dev in (1, 0, 1):
+                torch.cuda.set_device(dev)
+                model = S.build_model(arch, w, precision=precision)
+                _compile(model, SGD(1.0))
+                hist = model.fit([data["m"]], [data["q"], data["J"]], epochs=1, batch_size=B, perms=[np.arange(B)])
+                results.setdefault((precision, cfg), []).append(hist.history["loss"][0])
+    torch.cuda.set_device(0)
+    for key, losses in results.items():
+        assert np.isfinite(losses).all() and max(losses) - min(losses) < 1e-5 * abs(losses[0]), (key, losses)
