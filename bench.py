@@ -407,7 +407,7 @@ def main():
     sampler.stop()
     stage_ms, stage_n = chain_stage_ms(model, ds, Bg, min(args.steps, 20), order)
     if dp.rank != 0:
-        return
+        return                                  # (what follows runs on rank 0 alone, without collectives)
 
     legs, extra, engine = {}, {}, None
     if not args.no_legs:

@@ -6,7 +6,7 @@
 //
 // Large networks keep the layer-by-layer GEMM path: there each weight must be reused across many
 // samples per load, which is what the tiled engines do.
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace dino {
 
@@ -298,12 +298,10 @@ bool mlp_fused_supported(const MlpNetDev& net) {
 cudaError_t launch_mlp_forward_fused(const MlpNetDev& net, const float* params, float* ws, const float* m,
                                      const int* idx, int B, cudaStream_t st) {
   const size_t smem = fwd_smem(net);
-  static size_t configured = 0;
-  if (smem > 40 * 1024 && smem > configured) {   // static (4 KB) + dynamic share the 48 KB default limit
-    cudaError_t e = cudaFuncSetAttribute(mlp_forward_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
+  // the attribute is per device: raise it once per device to the largest size mlp_fused_supported() admits
+  static std::atomic<unsigned long long> mask{0};
+  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(mlp_forward_fused_kernel), 160 * 1024, mask);
+  if (e != cudaSuccess) return e;
   mlp_forward_fused_kernel<<<cdiv_i(B, TS), MT, smem, st>>>(net, params, ws, m, idx, B, fwd_w_floats(net));
   return cudaGetLastError();
 }
@@ -311,12 +309,9 @@ cudaError_t launch_mlp_forward_fused(const MlpNetDev& net, const float* params, 
 cudaError_t launch_mlp_backward_fused(const MlpNetDev& net, const float* params, float* ws, float* grad, int B,
                                       int with_rowsum, cudaStream_t st) {
   const size_t smem = bwd_smem(net);
-  static size_t configured = 0;
-  if (smem > 40 * 1024 && smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_backward_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
+  static std::atomic<unsigned long long> mask{0};
+  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(mlp_backward_fused_kernel), 160 * 1024, mask);
+  if (e != cudaSuccess) return e;
   mlp_backward_fused_kernel<<<cdiv_i(B, TS), MT, smem, st>>>(net, params, ws, grad, B, with_rowsum, bwd_w_floats(net));
   return cudaGetLastError();
 }
