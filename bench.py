@@ -423,12 +423,10 @@ def main():
             del mtf
         del model, ds
         torch.cuda.empty_cache()
-        for leg, ln, lsteps in (("cfg2", 16384, 200), ("cfg4", 512, 10)):
+        for leg, ln, lsteps, lb in (("cfg2", 16384, 200, 256), ("cfg4", 512, 12, 128)):
             if leg == args.config:
                 continue
-            lc = S.CONFIGS[leg]
             la, lm, lds, ltw = build_problem(leg, ln, args.precision)
-            lb = lc["batch"]
             lorder = np.random.default_rng(0).permutation(ln).astype(np.int32)
             r = resident_steps(lm, lds, lb, lsteps, 10, dp, lorder)
             le = e2e_steps(lm, lds, lb, lb, lsteps, 10, dp, lorder)

@@ -156,7 +156,22 @@ __global__ void __launch_bounds__(256) loss_j_kernel(float* __restrict__ jhat, l
     const float nj = __ldg(jn2 + sb);
     const float g = coef / nj;
     float e = 0.f, nr = 0.f;
-    for (int c = lane; c < n; c += 32) {
+    int c = lane;
+    // four independent 128-byte requests per operand in flight per warp (rows of the full Jacobian are 17 KB long and
+    // not 16-byte aligned, so the loads stay scalar; what was missing is memory-level parallelism)
+    for (; c + 96 < n; c += 128) {
+      float tv[4], pv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { tv[u] = __ldg(t + c + 32 * u); pv[u] = p[c + 32 * u]; }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float d = pv[u] - tv[u];
+        e = fmaf(d, d, e);
+        nr = fmaf(tv[u], tv[u], nr);
+        if (write_grad) p[c + 32 * u] = g * d;
+      }
+    }
+    for (; c < n; c += 32) {
       const float tv = __ldg(t + c);
       const float d = p[c] - tv;
       e = fmaf(d, d, e);

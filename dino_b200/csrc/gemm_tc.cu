@@ -57,8 +57,10 @@ __device__ __forceinline__ float4 tc_ld4(const float* row, int n, int N) {
 
 // EPI: 0 plain store; 1 chain terms (rowsum / add_pre / scale / add_post / rounding); 2 network terms (bias / softplus +
 // sigmoid / add_pre / add_post)
-template <int BN, int BK, int STAGES, bool SPLIT, int EPI>
-__global__ void __launch_bounds__(320, 1)
+// NEPI: epilogue warps (4 or 8): 8 split the column blocks of a lane quarter over two warps, for contractions whose
+// main loop is short against their epilogue (tf32; fp32x3 with a short K)
+template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI>
+__global__ void __launch_bounds__((2 + NEPI + (SPLIT ? 4 : 0)) * 32, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep) {
   constexpr int A_BYTES = TC_BM * BK * 4, B_BYTES = BN * BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
@@ -71,7 +73,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   constexpr int NACC = 2 * SET_COLS <= 512 ? 2 : 1;          // two sets when they fit: the epilogue of tile i overlaps the MMAs of tile i+1
   constexpr uint32_t TMEM_COLS = NACC * SET_COLS;
   constexpr int EPI_BUF = 32 * 128;                          // one 32 x 32 fp32 block, 128-byte rows, chunks swizzled by the row
-  constexpr int NEPI = SPLIT ? 4 : 8;                        // epilogue warps (warps 2 .. 2 + NEPI - 1); fp32x3: warps 6-9 are the converters
+  constexpr int CONV0 = 2 + NEPI;                            // fp32x3: first of the four converter warps
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -157,10 +159,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         umma_commit(tmem_full_bar + acc);            // accumulator complete
       }
     }
-  } else if (SPLIT && warp >= 6) {
+  } else if (SPLIT && warp >= CONV0) {
     // ===== converters (fp32x3): lo tile of every landed stage =====
     {
-      const int t = threadIdx.x - 192;
+      const int t = threadIdx.x - CONV0 * 32;
       int it = 0;
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         for (int kb = 0; kb < nkb; ++kb, ++it) {
@@ -436,7 +438,7 @@ bool gemm_tc_supported(const GemmOp& op) {
   return op.M > 0 && op.N > 0 && op.K > 0;
 }
 
-template <int BN, int BK, int STAGES, bool SPLIT, int EPI>
+template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI>
 static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   CUtensorMap ma, mb;
   const int sw_in = BK == 32 ? (int)CU_TENSOR_MAP_SWIZZLE_128B : (int)CU_TENSOR_MAP_SWIZZLE_64B;
@@ -451,24 +453,29 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   ep.yref = op.rowsum ? op.yref : nullptr; ep.ld_y = op.ld_y; ep.rowsum = op.rowsum; ep.ld_rs = op.ld_rs;
   ep.round_tf32 = SPLIT ? 0 : op.round_tf32;
   constexpr int RAW = (TC_BM + BN) * BK * 4;
-  constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + (SPLIT ? 4 : 8) * 32 * 128 + 256 + 1024;
+  constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + NEPI * 32 * 128 + 256 + 1024;
   static_assert(SMEM <= 232448, "shared memory budget of one CTA");
   static std::atomic<unsigned long long> attr_mask{0};
-  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI>), SMEM, attr_mask);
+  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI>), SMEM, attr_mask);
   if (e != cudaSuccess) return e;
   // persistent CTAs, one per SM: each walks its share of the 128 x BN output tiles
   const int num_sms = tc_current_num_sms();
   const long long n_tiles = (long long)((op.N + BN - 1) / BN) * ((op.M + TC_BM - 1) / TC_BM);
   const int grid = (int)(n_tiles < num_sms ? n_tiles : num_sms);
-  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI><<<grid, 320, SMEM, st>>>(ma, mb, ep);
+  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI><<<grid, (2 + NEPI + (SPLIT ? 4 : 0)) * 32, SMEM, st>>>(ma, mb, ep);
   return cudaGetLastError();
 }
 
 template <int BN, int BK, int STAGES, bool SPLIT>
 static cudaError_t launch_tc(const GemmOp& op, cudaStream_t st) {
-  if (op.bias || op.act) return launch_tc1<BN, BK, STAGES, SPLIT, 2>(op, st);
-  if (op.rowsum || op.scale || op.add_pre || op.add_post || (op.round_tf32 && !SPLIT)) return launch_tc1<BN, BK, STAGES, SPLIT, 1>(op, st);
-  return launch_tc1<BN, BK, STAGES, SPLIT, 0>(op, st);
+  if (op.bias || op.act) return launch_tc1<BN, BK, STAGES, SPLIT, 2, SPLIT ? 4 : 8>(op, st);
+  if (op.rowsum || op.scale || op.add_pre || op.add_post || (op.round_tf32 && !SPLIT))
+    return launch_tc1<BN, BK, STAGES, SPLIT, 1, SPLIT ? 4 : 8>(op, st);
+  // plain store: in fp32x3 a short reduction leaves the epilogue as the pace-setter (the full-Jacobian output R_0 =
+  // Q_0 W_0^T has K = 100 and 17 KB rows): eight epilogue warps there as well
+  if (SPLIT && op.K <= 256 && (STAGES * 2 * (TC_BM + BN) * BK * 4 + 8 * 32 * 128 + 1280 <= 232448))
+    return launch_tc1<BN, BK, STAGES, SPLIT, 0, 8>(op, st);
+  return launch_tc1<BN, BK, STAGES, SPLIT, 0, SPLIT ? 4 : 8>(op, st);
 }
 
 cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st) {
