@@ -16,7 +16,7 @@
 //     128-byte lines of C (a thread owns a ROW of the accumulator; stored directly, a warp would touch 32 lines per
 //     instruction).  TMA stores were tried here first: with two 4 KB boxes in flight per warp their issue-to-read
 //     latency, not bandwidth, set the pace (0.9 TB/s of output at K = 200).
-// Warp roles: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 2-5 epilogue, warps 6-9 converters.
+// Warp roles: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, then 4 or 8 epilogue warps, then (fp32x3) 8 converter warps.
 // Persistent CTAs (one per SM) walk the 128 x BN output tiles.  Out-of-range rows/columns/K are zero-filled by TMA,
 // so M, N, K are arbitrary; leading dimensions must be multiples of 4 floats.
 #include <cuda.h>
@@ -31,6 +31,7 @@ namespace dino {
 using namespace tc;
 
 constexpr int TC_BM = 128;
+constexpr int TC_NCONV = 8;     // fp32x3: converter warps (a stage of 32-48 KB per 768 MMA cycles: four warps could not keep up)
 
 struct TcEpilogue {
   int M, N, K;
@@ -60,7 +61,7 @@ __device__ __forceinline__ float4 tc_ld4(const float* row, int n, int N) {
 // NEPI: epilogue warps (4 or 8): 8 split the column blocks of a lane quarter over two warps, for contractions whose
 // main loop is short against their epilogue (tf32; fp32x3 with a short K)
 template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI>
-__global__ void __launch_bounds__((2 + NEPI + (SPLIT ? 4 : 0)) * 32, 1)
+__global__ void __launch_bounds__((2 + NEPI + (SPLIT ? TC_NCONV : 0)) * 32, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep) {
   constexpr int A_BYTES = TC_BM * BK * 4, B_BYTES = BN * BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
@@ -96,7 +97,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   }
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); mbar_init(conv_bar + i, 4); }
+      for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); mbar_init(conv_bar + i, TC_NCONV); }
       mbar_init(tmem_full_bar, 1); mbar_init(tmem_full_bar + 1, 1);
       mbar_init(tmem_empty_bar, NEPI); mbar_init(tmem_empty_bar + 1, NEPI);
       fence_mbar_init();
@@ -169,7 +170,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           const int st = it % STAGES;
           mbar_wait(full_bar + st, (it / STAGES) & 1);
           const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
-          split_lo_tile(sa, sa + RAW_BYTES, RAW_BYTES, t, 128);
+          split_lo_tile(sa, sa + RAW_BYTES, RAW_BYTES, t, TC_NCONV * 32);
           fence_async_smem();                        // generic-proxy writes -> visible to the tensor core
           __syncwarp();
           if (lane == 0) mbar_arrive(conv_bar + st);
@@ -462,7 +463,7 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   const int num_sms = tc_current_num_sms();
   const long long n_tiles = (long long)((op.N + BN - 1) / BN) * ((op.M + TC_BM - 1) / TC_BM);
   const int grid = (int)(n_tiles < num_sms ? n_tiles : num_sms);
-  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI><<<grid, (2 + NEPI + (SPLIT ? 4 : 0)) * 32, SMEM, st>>>(ma, mb, ep);
+  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI><<<grid, (2 + NEPI + (SPLIT ? TC_NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep);
   return cudaGetLastError();
 }
 

@@ -21,6 +21,7 @@
 
 namespace dino {
 
+constexpr int WG_NCONV = 8;                    // fp32x3: converter warps
 constexpr int WG_X3_ROWS = 1024;                // fp32x3: longest reduction one TMEM accumulator takes
 
 struct WgOp {
@@ -39,7 +40,7 @@ struct WgGroup {
 };
 
 template <int TN, int BK, int STAGES, bool SPLIT>
-__global__ void __launch_bounds__(SPLIT ? 320 : 192, 1) wgrad_tc_kernel(const __grid_constant__ WgGroup g) {
+__global__ void __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1) wgrad_tc_kernel(const __grid_constant__ WgGroup g) {
   using namespace tc;
   constexpr int GROUP_BYTES = BK * 128;                    // one 32-column group: BK reduction rows of 128 bytes
   constexpr int A_BYTES = 4 * GROUP_BYTES, B_BYTES = (TN / 32) * GROUP_BYTES, RAW_BYTES = A_BYTES + B_BYTES;
@@ -67,7 +68,7 @@ __global__ void __launch_bounds__(SPLIT ? 320 : 192, 1) wgrad_tc_kernel(const __
 
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); mbar_init(conv_bar + i, 4); }
+      for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); mbar_init(conv_bar + i, WG_NCONV); }
       mbar_init(done_bar, 1);
       fence_mbar_init();
     }
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(SPLIT ? 320 : 192, 1) wgrad_tc_kernel(const __
         const int st = c % STAGES;
         mbar_wait(full_bar + st, (c / STAGES) & 1);
         const uint32_t sx = smem_u32(smem + st * STAGE_BYTES);
-        split_lo_tile(sx, sx + RAW_BYTES, RAW_BYTES, (int)threadIdx.x - 192, 128);
+        split_lo_tile(sx, sx + RAW_BYTES, RAW_BYTES, (int)threadIdx.x - 192, WG_NCONV * 32);
         fence_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(conv_bar + st);
@@ -242,7 +243,7 @@ static cudaError_t launch_wg(const GemmGroup& gg, int num_sms, cudaStream_t st) 
   static std::atomic<unsigned long long> mask{0};
   cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(wgrad_tc_kernel<TN, BK, STAGES, SPLIT>), SMEM, mask);
   if (e != cudaSuccess) return e;
-  wgrad_tc_kernel<TN, BK, STAGES, SPLIT><<<z, SPLIT ? 320 : 192, SMEM, st>>>(g);
+  wgrad_tc_kernel<TN, BK, STAGES, SPLIT><<<z, SPLIT ? 192 + WG_NCONV * 32 : 192, SMEM, st>>>(g);
   return cudaGetLastError();
 }
 
