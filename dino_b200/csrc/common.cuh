@@ -80,7 +80,10 @@ cudaError_t launch_mlp_backward_fused(const MlpNetDev& net, const float* params,
 // tcgen05 TF32 engine (gemm_tc.cu): both operands K-major (a_sk == b_sk == 1), 16-byte row pitches,
 // every epilogue term of GemmOp except atomic_c / split-K.  gemm_tc_supported() says whether an op qualifies.
 bool gemm_tc_supported(const GemmOp& op);
-cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st);   // split: fp32x3 (three MMAs on hi/lo operand splits)
+cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st);
+// the same contraction on CTA pairs (gemm_tc2.cu: tcgen05 cta_group::2, 256 x 256 tiles per pair)
+bool gemm_tc2_wanted(const GemmOp& op);
+cudaError_t launch_gemm_tc2(const GemmOp& op, int split, cudaStream_t st);   // split: fp32x3 (three MMAs on hi/lo operand splits)
 
 // weight staging for the TMA-fed engine: padded copy Wp[n_in][r4(n_out)] and transpose WTp[n_out][r4(n_in)]
 // mode 0 (tf32): both copies rounded to nearest TF32.  mode 1 (fp32x3): exact copies, plus (when wp_lo_off >= 0) the low

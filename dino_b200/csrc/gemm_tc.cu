@@ -24,7 +24,7 @@
 #include <cstdlib>
 #include <mutex>
 
-#include "tc_common.cuh"
+#include "tc_epilogue.cuh"
 
 namespace dino {
 
@@ -32,29 +32,6 @@ using namespace tc;
 
 constexpr int TC_BM = 128;
 constexpr int TC_NCONV = 8;     // fp32x3: converter warps (a stage of 32-48 KB per 768 MMA cycles: four warps could not keep up)
-
-struct TcEpilogue {
-  int M, N, K;
-  float* C; long long ldc;
-  int sdim;
-  const float* scale; long long ld_sc;
-  const float* add_pre; long long ld_ap;
-  const float* add_post; long long ld_apo;
-  const float* bias;
-  int act; float* s_out; long long ld_s;
-  const float* yref; long long ld_y; float* rowsum; long long ld_rs;
-  int round_tf32;
-};
-
-// 4 floats of a row at column n (n % 4 == 0): vector load when the four lie inside N, guarded scalars at the edge
-__device__ __forceinline__ float4 tc_ld4(const float* row, int n, int N) {
-  if (n + 3 < N) return *reinterpret_cast<const float4*>(row + n);
-  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (n < N) v.x = row[n];
-  if (n + 1 < N) v.y = row[n + 1];
-  if (n + 2 < N) v.z = row[n + 2];
-  return v;
-}
 
 // EPI: 0 plain store; 1 chain terms (rowsum / add_pre / scale / add_post / rounding); 2 network terms (bias / softplus +
 // sigmoid / add_pre / add_post)
@@ -187,7 +164,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     const int ew = warp - 2;                       // epilogue warp index
     const int half = ew >> 2;                      // NEPI == 8: even / odd column blocks
     const uint32_t my_stage = smem_u32(epi_stage + ew * EPI_BUF);
-    const uint32_t sw = (uint32_t)(lane & 7);
     int i = 0;
 #pragma unroll 1
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
@@ -195,145 +171,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       const int acc = i % NACC;
       mbar_wait(tmem_full_bar + acc, (i / NACC) & 1);
       tc_fence_after();
-      const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < ep.M;
-      const int b = row_ok ? row / ep.sdim : 0;
-      const float* sc = (EPI == 1 && ep.scale) ? ep.scale + (long long)b * ep.ld_sc : nullptr;
-      const float* ap = (EPI != 0 && ep.add_pre) ? ep.add_pre + (long long)row * ep.ld_ap : nullptr;
-      const float* apo = (EPI != 0 && ep.add_post) ? ep.add_post + (long long)row * ep.ld_apo : nullptr;
-      const float* yr = (EPI == 1 && ep.yref) ? ep.yref + (long long)row * ep.ld_y : nullptr;
-      float* so = (EPI == 2 && ep.s_out) ? ep.s_out + (long long)row * ep.ld_s : nullptr;
-      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * SET_COLS;
-#pragma unroll 1
-      for (int c0 = half * 32; c0 < BN; c0 += 32 * (NEPI / 4)) {
-        if (n0 + c0 >= ep.N) break;                  // warp-uniform
-        const int nb = n0 + c0;
-        const bool full = nb + 32 <= ep.N;           // warp-uniform: the block lies inside N
-        float v[32];
-        tmem_ld32(tacc + (uint32_t)c0, v);
-        if (SPLIT) {
-          float x[32];
-          tmem_ld32(tacc + ACC_COLS + (uint32_t)c0, x);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += x[j];
-        }
-        // 32 floats of a row-indexed operand at this block's columns (zeros outside the matrix)
-        auto load32 = [&](float (&d)[32], const float* rowp, bool ok) {
-          if (full) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 t = ok ? *reinterpret_cast<const float4*>(rowp + nb + j) : make_float4(0.f, 0.f, 0.f, 0.f);
-              d[j] = t.x; d[j + 1] = t.y; d[j + 2] = t.z; d[j + 3] = t.w;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 t = ok ? tc_ld4(rowp, nb + j, ep.N) : make_float4(0.f, 0.f, 0.f, 0.f);
-              d[j] = t.x; d[j + 1] = t.y; d[j + 2] = t.z; d[j + 3] = t.w;
-            }
-          }
-        };
-        if (EPI == 1 && yr) {
-          // d sigma term: rowsum[sample, n] += sum over the sample's chain rows of acc * yref  (segmented over the
-          // samples under this warp's 32 rows; lane j ends up with column j)
-          float p[32];
-          load32(p, yr, row_ok);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) p[j] *= v[j];
-          const int r_first = m0 + q * 32;
-          if (r_first < ep.M) {
-            const int b_lo = r_first / ep.sdim, b_hi = min(r_first + 31, ep.M - 1) / ep.sdim;
-            for (int bb = b_lo; bb <= b_hi; ++bb) {
-              float mm[32];
-#pragma unroll
-              for (int j = 0; j < 32; ++j) mm[j] = (row_ok && b == bb) ? p[j] : 0.f;
-              const float tot = colsum32(mm, lane);
-              if (nb + lane < ep.N) atomicAdd(ep.rowsum + (long long)bb * ep.ld_rs + nb + lane, tot);
-            }
-          }
-          if (!ep.C) continue;
-        }
-        if (EPI == 2) {
-          if (ep.bias) {
-            float t[32];
-            load32(t, ep.bias, true);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] += t[j];
-          }
-          if (ep.act) {
-            // sigmoid and softplus from one exponential: e = exp(-|x|)
-            float sg[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float e = expf(-fabsf(v[j])), r1 = 1.f / (1.f + e);
-              sg[j] = v[j] >= 0.f ? r1 : e * r1;
-              v[j] = fmaxf(v[j], 0.f) + log1pf(e);
-            }
-            if (so && row_ok) {
-              if (full) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(so + nb + j) = make_float4(sg[j], sg[j + 1], sg[j + 2], sg[j + 3]);
-              } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) if (nb + j < ep.N) so[nb + j] = sg[j];
-              }
-            }
-          }
-        }
-        if (EPI != 0) {
-          if (ap) {
-            float t[32];
-            load32(t, ap, row_ok);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] += t[j];
-          }
-          if (sc) {
-            float t[32];
-            load32(t, sc, row_ok);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= t[j];
-          }
-          if (apo) {
-            float t[32];
-            load32(t, apo, row_ok);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] += t[j];
-          }
-          if (ep.round_tf32) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = round_tf32_f(v[j]);
-          }
-        }
-        // stage the block (thread = row, 16-byte chunks XOR-swizzled by the row), then store it four rows per
-        // instruction: 8 lanes x 16 bytes = one whole 128-byte line of C per row
-        __syncwarp();                                // the previous block's reads of the staging buffer are done
-        const uint32_t rowb = my_stage + (uint32_t)(lane * 128);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) sts128(rowb + ((((uint32_t)j) ^ sw) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        __syncwarp();
-        const int ch = lane & 7, n = nb + 4 * ch;
-        float* cbase = ep.C + (long long)(m0 + q * 32 + (lane >> 3)) * ep.ldc + n;
-        const int rows_left = ep.M - (m0 + q * 32 + (lane >> 3));      // this lane's rows: rows_left > 4 * it
-        if (full) {
-#pragma unroll
-          for (int it = 0; it < 8; ++it) {
-            const int rr = it * 4 + (lane >> 3);
-            const float4 o = lds128(my_stage + (uint32_t)(rr * 128) + ((((uint32_t)ch) ^ (uint32_t)(rr & 7)) << 4));
-            if (rows_left > 4 * it) *reinterpret_cast<float4*>(cbase + (long long)(4 * it) * ep.ldc) = o;
-          }
-        } else {
-#pragma unroll
-          for (int it = 0; it < 8; ++it) {
-            const int rr = it * 4 + (lane >> 3);
-            const float4 o = lds128(my_stage + (uint32_t)(rr * 128) + ((((uint32_t)ch) ^ (uint32_t)(rr & 7)) << 4));
-            if (rows_left > 4 * it && n < ep.N) {
-              float* dst = cbase + (long long)(4 * it) * ep.ldc;
-              if (n + 3 < ep.N) *reinterpret_cast<float4*>(dst) = o;
-              else { dst[0] = o.x; if (n + 1 < ep.N) dst[1] = o.y; if (n + 2 < ep.N) dst[2] = o.z; }
-            }
-          }
-        }
-      }
+      tc_epilogue_tile<BN, SPLIT, EPI, NEPI, ACC_COLS>(ep, m0, n0, tmem_base + (uint32_t)acc * SET_COLS, my_stage, q, half, lane);
       // this warp is done reading the accumulator: hand it back to the MMA issuer
       tc_fence_before();
       __syncwarp();
@@ -482,6 +320,8 @@ static cudaError_t launch_tc(const GemmOp& op, cudaStream_t st) {
 cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st) {
   if (!gemm_tc_supported(op)) return cudaErrorNotSupported;
   static const int variant = getenv("DINO_TC_VARIANT") ? atoi(getenv("DINO_TC_VARIANT")) : 0;   // read once per process
+  static const int cg2 = getenv("DINO_TC_CG2") ? atoi(getenv("DINO_TC_CG2")) : 3;              // CTA-pair kernel for bit 0: tf32, bit 1: fp32x3
+  if (((split ? 2 : 1) & cg2) && gemm_tc2_wanted(op)) return launch_gemm_tc2(op, split, st);
   const int num_sms = tc_current_num_sms();
   const long long m_tiles = (op.M + TC_BM - 1) / TC_BM;
   // widest tile that still gives every SM work (small-M contractions: the network's own forward / backward)

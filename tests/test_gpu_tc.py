@@ -30,7 +30,7 @@ def _gemm(engine, A, Bt, M, N, K, lda, ldb, ldc):
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 64, 32), (100, 50, 50), (1600, 50, 100), (300, 100, 50), (257, 130, 70),
-                                   (512, 400, 200), (1000, 1024, 1024), (128, 8, 8), (5, 52, 300), (8192, 520, 100)])
+                                   (512, 400, 200), (1000, 1024, 1024), (128, 8, 8), (5, 52, 300), (8192, 520, 100), (19000, 1000, 260)])
 def test_tf32_gemm_matches_fp64(cuda_device, M, N, K):
     rng = np.random.default_rng(M * 7 + N * 3 + K)
     r4 = lambda n: (n + 3) & ~3
