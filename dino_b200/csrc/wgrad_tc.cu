@@ -179,6 +179,156 @@ __global__ void __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1) wgrad_tc
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
 }
 
+// ---- the same reduction on CTA pairs (tcgen05 cta_group::2): a pair owns a 256 x 256 tile of dW; each CTA stages its
+// 128 columns of X and its 128 columns of Y per reduction chunk, the leader issues the M = 256 MMAs, each CTA's tensor
+// memory holds its 128 rows of the tile.  Barrier scheme as in gemm_tc2.cu.  For layers with n_in, n_out > 128.
+template <int BK, int STAGES, bool SPLIT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1)
+wgrad_tc2_kernel(const __grid_constant__ WgGroup g) {
+  using namespace tc;
+  constexpr int GROUP_BYTES = BK * 128;
+  constexpr int A_BYTES = 4 * GROUP_BYTES, RAW_BYTES = 8 * GROUP_BYTES;
+  constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
+  constexpr uint32_t TMEM_COLS = SPLIT ? 512 : 256;
+  extern __shared__ uint8_t wg_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(wg_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* conv_bar = empty_bar + STAGES;
+  uint64_t* done_bar = conv_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+
+  const int pairx = blockIdx.x >> 1;
+  const uint32_t rank = cluster_ctarank();
+  int oi = 0;
+  while (oi + 1 < g.n && pairx >= g.op[oi + 1].z_start) ++oi;
+  const WgOp& op = g.op[oi];
+  const int total_chunks = (op.rows + BK - 1) / BK;
+  const int local = pairx - op.z_start;
+  const int split = local % op.splits, tile = local / op.splits;
+  const int m0 = (tile / op.n_tiles) * 256, n0 = (tile % op.n_tiles) * 256;
+  const int c_begin = split * op.chunks_per_cta;
+  const int nchunks = min(total_chunks - c_begin, op.chunks_per_cta);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ncols = min(256, op.n_out - n0);
+  // 32-column groups that hold data, per CTA of the pair: X columns [m0 + 128 r, +128), Y columns [n0 + 128 r, +128)
+  auto groups = [](int have) { return have <= 0 ? 0 : (min(128, have) + 31) >> 5; };
+  const int ga0 = groups(op.n_in - m0), ga1 = groups(op.n_in - m0 - 128), gb0 = groups(op.n_out - n0), gb1 = groups(op.n_out - n0 - 128);
+  const int ga = rank ? ga1 : ga0, gb = rank ? gb1 : gb0;
+
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); mbar_init(conv_bar + i, 2 * WG_NCONV); }
+      mbar_init(done_bar, 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (nchunks > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        const CUtensorMap* mx = &g.mx[oi];
+        const CUtensorMap* my = &g.my[oi];
+        const int mc = m0 + 128 * (int)rank, nc = n0 + 128 * (int)rank;
+        for (int c = 0; c < nchunks; ++c) {
+          const int st = c % STAGES;
+          mbar_wait(empty_bar + st, ((c / STAGES) & 1) ^ 1);
+          uint8_t* sx = smem + st * STAGE_BYTES;
+          const int k0 = (c_begin + c) * BK;
+          if (SPLIT) {
+            mbar_expect_tx(full_bar + st, (uint32_t)((ga + gb) * GROUP_BYTES));
+            for (int gI = 0; gI < ga; ++gI) tma_load_2d(sx + gI * GROUP_BYTES, mx, mc + 32 * gI, k0, full_bar + st);
+            for (int gI = 0; gI < gb; ++gI) tma_load_2d(sx + A_BYTES + gI * GROUP_BYTES, my, nc + 32 * gI, k0, full_bar + st);
+          } else {
+            if (rank == 0) mbar_expect_tx(full_bar + st, (uint32_t)((ga0 + ga1 + gb0 + gb1) * GROUP_BYTES));
+            for (int gI = 0; gI < ga; ++gI) tma_load_2d_2sm(sx + gI * GROUP_BYTES, mx, mc + 32 * gI, k0, full_bar + st);
+            for (int gI = 0; gI < gb; ++gI) tma_load_2d_2sm(sx + A_BYTES + gI * GROUP_BYTES, my, nc + 32 * gI, k0, full_bar + st);
+          }
+        }
+      }
+    } else if (warp == 1) {
+      if (rank == 0 && lane == 0) {
+        const uint32_t idesc = idesc_tf32_m(256, 256) | (1u << 15) | (1u << 16);     // both operands MN-major
+        for (int c = 0; c < nchunks; ++c) {
+          const int st = c % STAGES;
+          mbar_wait((SPLIT ? conv_bar : full_bar) + st, (c / STAGES) & 1);
+          tc_fence_after();
+          const uint32_t sx = smem_u32(smem + st * STAGE_BYTES), sy = sx + A_BYTES;
+          const uint64_t ad = desc_mn_sw128_32(sx, GROUP_BYTES), bd = desc_mn_sw128_32(sy, GROUP_BYTES);
+          constexpr uint64_t LO = RAW_BYTES >> 4;
+#pragma unroll
+          for (int k = 0; k < BK / 8; ++k) {
+            umma_tf32_2sm(tmem_base, ad + 64 * k, bd + 64 * k, idesc, (c > 0 || k > 0) ? 1u : 0u);
+            if (SPLIT) {
+              umma_tf32_2sm(tmem_base + 256u, ad + LO + 64 * k, bd + 64 * k, idesc, (c > 0 || k > 0) ? 1u : 0u);
+              umma_tf32_2sm(tmem_base + 256u, ad + 64 * k, bd + LO + 64 * k, idesc, 1u);
+            }
+          }
+          umma_commit_2sm(empty_bar + st);
+        }
+        umma_commit_2sm(done_bar);
+      }
+    } else if (SPLIT && warp >= 6) {
+      for (int c = 0; c < nchunks; ++c) {
+        const int st = c % STAGES;
+        // (a CTA whose halves are empty has nothing in flight: its full barrier never fires, it only reports in)
+        if (ga + gb > 0) {
+          mbar_wait(full_bar + st, (c / STAGES) & 1);
+          const uint32_t sx = smem_u32(smem + st * STAGE_BYTES);
+          split_lo_tile(sx, sx + RAW_BYTES, RAW_BYTES, (int)threadIdx.x - 192, WG_NCONV * 32);
+          fence_async_smem();
+        } else {
+          mbar_wait(empty_bar + st, ((c / STAGES) & 1) ^ 1);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(conv_bar + st, 0);
+      }
+    } else {
+      mbar_wait(done_bar, 0);
+      tc_fence_after();
+      const int q = warp & 3;
+      const int m = m0 + 128 * (int)rank + q * 32 + lane;
+      const bool vec = (op.n_out & 3) == 0 && (reinterpret_cast<uintptr_t>(op.C) & 15) == 0;
+      for (int c0 = 0; c0 < ncols; c0 += 32) {
+        float v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+        tmem_ld32(taddr, v);
+        if (SPLIT) {
+          float x[32];
+          tmem_ld32(taddr + 256u, x);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += x[j];
+        }
+        if (m < op.n_in) {
+          float* crow = op.C + (long long)m * op.n_out + n0 + c0;
+          if (vec && c0 + 32 <= ncols) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(crow + j), "f"(v[j]), "f"(v[j + 1]), "f"(v[j + 2]), "f"(v[j + 3]) : "memory");
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (c0 + j < ncols) atomicAdd(crow + j, v[j]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync();
+  if (warp == 1)
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+}
+
 // ---- host ---------------------------------------------------------------------------------------------
 // The ops passed here describe C[M,N] += A[M,K] * Bt[N,K]^T with BOTH operands K-major (a_sk == b_sk == 1):
 // A = XT (pitch a_sm), B = YT (pitch b_sn), or both MN-major (a_sm == b_sn == 1: the row-major chain states).
@@ -247,8 +397,73 @@ static cudaError_t launch_wg(const GemmGroup& gg, int num_sms, cudaStream_t st) 
   return cudaGetLastError();
 }
 
+static cudaError_t launch_wgrad_tc_rest(const GemmGroup& gg, int split, int num_sms, cudaStream_t st);
+
+template <int BK, int STAGES, bool SPLIT>
+static cudaError_t launch_wg2(const GemmGroup& gg, int num_sms, cudaStream_t st) {
+  WgGroup g;
+  g.n = gg.n;
+  double total_work = 0.0;
+  for (int i = 0; i < gg.n; ++i)
+    total_work += (double)gg.ops[i].K * ((gg.ops[i].M + 255) / 256) * ((gg.ops[i].N + 255) / 256);
+  const double target_pairs = num_sms / 2;
+  int z = 0;                               // in pairs
+  for (int i = 0; i < gg.n; ++i) {
+    const GemmOp& o = gg.ops[i];
+    WgOp& w = g.op[i];
+    w.C = o.C; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
+    const int chunks = (o.K + BK - 1) / BK;
+    w.n_tiles = (o.N + 255) / 256;
+    const int tiles = ((o.M + 255) / 256) * w.n_tiles;
+    long long splits = (long long)(target_pairs * ((double)o.K * tiles / total_work) / tiles);
+    if (splits < 1) splits = 1;
+    const int cap = WG_X3_ROWS / BK;
+    if (SPLIT && splits * cap < chunks) splits = (chunks + cap - 1) / cap;
+    if (splits > chunks) splits = chunks;
+    w.chunks_per_cta = (int)((chunks + splits - 1) / splits);
+    w.splits = (chunks + w.chunks_per_cta - 1) / w.chunks_per_cta;
+    w.z_start = z;
+    z += tiles * w.splits;
+    w.mn = 1;
+    if (!tc_make_map(&g.mx[i], o.A, (unsigned long long)o.M, (unsigned long long)o.K, o.a_sk, 32, BK, (int)CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) ||
+        !tc_make_map(&g.my[i], o.B, (unsigned long long)o.N, (unsigned long long)o.K, o.b_sk, 32, BK, (int)CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))
+      return cudaErrorInvalidValue;
+  }
+  constexpr int RAW = 8 * BK * 128;
+  constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + 128 + 1024;
+  static_assert(SMEM <= 232448, "shared memory budget of one CTA");
+  static std::atomic<unsigned long long> mask{0};
+  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(wgrad_tc2_kernel<BK, STAGES, SPLIT>), SMEM, mask);
+  if (e != cudaSuccess) return e;
+  wgrad_tc2_kernel<BK, STAGES, SPLIT><<<2 * z, SPLIT ? 192 + WG_NCONV * 32 : 192, SMEM, st>>>(g);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_wgrad_tc(const GemmGroup& gg, int split, int num_sms, cudaStream_t st) {
   if (gg.n <= 0) return cudaSuccess;
+  // layers wider than 128 both ways go to the CTA-pair kernel (row-major factors only); the rest stays here
+  static const int pairs_on = getenv("DINO_WG_CG2") ? atoi(getenv("DINO_WG_CG2")) : 1;     // read once per process
+  if (pairs_on) {
+    GemmGroup big, rest;
+    big.n = rest.n = 0;
+    for (int i = 0; i < gg.n; ++i) {
+      const GemmOp& o = gg.ops[i];
+      const bool mn = !(o.a_sk == 1 && o.b_sk == 1);
+      if (mn && o.M > 128 && o.N > 128 && o.K >= 2048) big.ops[big.n++] = o; else rest.ops[rest.n++] = o;
+    }
+    if (big.n > 0) {
+      cudaError_t e = split ? launch_wg2<32, 3, true>(big, num_sms, st) : launch_wg2<64, 3, false>(big, num_sms, st);
+      // (tf32 with 64 reduction rows per stage: the row-major operands arrive as 32-column boxes, eight per CTA and
+      //  stage, and the rate at which one thread can issue those boxes - not bandwidth - paced the 32-row version:
+      //  142 -> 86 us at 25600 rows, 1024 x 1024, cuBLAS TF32 90 us)
+      if (e != cudaSuccess || rest.n == 0) return e;
+      return launch_wgrad_tc_rest(rest, split, num_sms, st);
+    }
+  }
+  return launch_wgrad_tc_rest(gg, split, num_sms, st);
+}
+
+static cudaError_t launch_wgrad_tc_rest(const GemmGroup& gg, int split, int num_sms, cudaStream_t st) {
   // wide outputs take 128 x 256 tiles; transposed (K-major) factors only exist for the 128-wide kernels
   bool wide = false, kmajor = false;
   for (int i = 0; i < gg.n; ++i) {

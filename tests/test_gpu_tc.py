@@ -74,7 +74,8 @@ def test_tf32_weight_gradient_contraction(cuda_device, rows, n_in, n_out):
 
 
 @pytest.mark.parametrize("rows,n_in,n_out", [(64, 32, 32), (240, 13, 8), (1000, 50, 50), (12800, 100, 50), (300, 128, 128),
-                                             (77, 5, 100), (520, 300, 200), (1000, 130, 257)])
+                                             (77, 5, 100), (520, 300, 200), (1000, 130, 257), (4096, 300, 260),
+                                             (6000, 1024, 520), (2500, 129, 400)])
 def test_tf32_weight_gradient_contraction_row_major(cuda_device, rows, n_in, n_out):
     """C += X^T Y with the factors row-major (MN-major tensor-core operands) vs fp64, onto a non-zero C."""
     lib = _lib.load()
