@@ -22,7 +22,7 @@
 namespace dino {
 
 constexpr int WG_NCONV = 8;                    // fp32x3: converter warps
-constexpr int WG_X3_ROWS = 1024;                // fp32x3: longest reduction one TMEM accumulator takes
+constexpr int WG_X3_ROWS = 2048;                // fp32x3: longest reduction one TMEM accumulator takes (256 truncating additions, two chain contractions' worth; 1024 cost 20 % more time in per-CTA set-up and drain)
 
 struct WgOp {
   float* C;                 // gradient block [n_in, n_out], ldc = n_out
@@ -236,21 +236,20 @@ wgrad_tc2_kernel(const __grid_constant__ WgGroup g) {
     if (warp == 0) {
       if (lane == 0) {
         const CUtensorMap* mx = &g.mx[oi];
-        const CUtensorMap* my = &g.my[oi];
-        const int mc = m0 + 128 * (int)rank, nc = n0 + 128 * (int)rank;
+        const int mc = m0 + 128 * (int)rank;
         for (int c = 0; c < nchunks; ++c) {
           const int st = c % STAGES;
           mbar_wait(empty_bar + st, ((c / STAGES) & 1) ^ 1);
           uint8_t* sx = smem + st * STAGE_BYTES;
           const int k0 = (c_begin + c) * BK;
+          // (this thread brings the X boxes; the Y boxes are issued by a lane of warp 2, idle until the epilogue: the
+          //  issue rate of the 32-column boxes, not bandwidth, is what the feed runs out of)
           if (SPLIT) {
             mbar_expect_tx(full_bar + st, (uint32_t)((ga + gb) * GROUP_BYTES));
             for (int gI = 0; gI < ga; ++gI) tma_load_2d(sx + gI * GROUP_BYTES, mx, mc + 32 * gI, k0, full_bar + st);
-            for (int gI = 0; gI < gb; ++gI) tma_load_2d(sx + A_BYTES + gI * GROUP_BYTES, my, nc + 32 * gI, k0, full_bar + st);
           } else {
             if (rank == 0) mbar_expect_tx(full_bar + st, (uint32_t)((ga0 + ga1 + gb0 + gb1) * GROUP_BYTES));
             for (int gI = 0; gI < ga; ++gI) tma_load_2d_2sm(sx + gI * GROUP_BYTES, mx, mc + 32 * gI, k0, full_bar + st);
-            for (int gI = 0; gI < gb; ++gI) tma_load_2d_2sm(sx + A_BYTES + gI * GROUP_BYTES, my, nc + 32 * gI, k0, full_bar + st);
           }
         }
       }
@@ -292,6 +291,22 @@ wgrad_tc2_kernel(const __grid_constant__ WgGroup g) {
         if (lane == 0) mbar_arrive_cluster(conv_bar + st, 0);
       }
     } else {
+      if (warp == 2 && lane == 0) {
+        // second producer: the Y boxes of every stage
+        const CUtensorMap* my = &g.my[oi];
+        const int nc = n0 + 128 * (int)rank;
+        for (int c = 0; c < nchunks; ++c) {
+          const int st = c % STAGES;
+          mbar_wait(empty_bar + st, ((c / STAGES) & 1) ^ 1);
+          uint8_t* sx = smem + st * STAGE_BYTES;
+          const int k0 = (c_begin + c) * BK;
+          for (int gI = 0; gI < gb; ++gI) {
+            if (SPLIT) tma_load_2d(sx + A_BYTES + gI * GROUP_BYTES, my, nc + 32 * gI, k0, full_bar + st);
+            else tma_load_2d_2sm(sx + A_BYTES + gI * GROUP_BYTES, my, nc + 32 * gI, k0, full_bar + st);
+          }
+        }
+      }
+      __syncwarp();
       mbar_wait(done_bar, 0);
       tc_fence_after();
       const int q = warp & 3;
