@@ -37,8 +37,8 @@ constexpr int TC_NCONV = 8;     // fp32x3: converter warps (a stage of 32-48 KB 
 // sigmoid / add_pre / add_post)
 // NEPI: epilogue warps (4 or 8): 8 split the column blocks of a lane quarter over two warps, for contractions whose
 // main loop is short against their epilogue (tf32; fp32x3 with a short K)
-template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI>
-__global__ void __launch_bounds__((2 + NEPI + (SPLIT ? TC_NCONV : 0)) * 32, 1)
+template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI, int NCONV>
+__global__ void __launch_bounds__((2 + NEPI + (SPLIT ? NCONV : 0)) * 32, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep) {
   constexpr int A_BYTES = TC_BM * BK * 4, B_BYTES = BN * BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
@@ -74,7 +74,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   }
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); mbar_init(conv_bar + i, TC_NCONV); }
+      for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); mbar_init(conv_bar + i, NCONV > 0 ? NCONV : 1); }
       mbar_init(tmem_full_bar, 1); mbar_init(tmem_full_bar + 1, 1);
       mbar_init(tmem_empty_bar, NEPI); mbar_init(tmem_empty_bar + 1, NEPI);
       fence_mbar_init();
@@ -147,7 +147,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           const int st = it % STAGES;
           mbar_wait(full_bar + st, (it / STAGES) & 1);
           const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
-          split_lo_tile(sa, sa + RAW_BYTES, RAW_BYTES, t, TC_NCONV * 32);
+          split_lo_tile(sa, sa + RAW_BYTES, RAW_BYTES, t, NCONV * 32);
           fence_async_smem();                        // generic-proxy writes -> visible to the tensor core
           __syncwarp();
           if (lane == 0) mbar_arrive(conv_bar + st);
@@ -277,7 +277,7 @@ bool gemm_tc_supported(const GemmOp& op) {
   return op.M > 0 && op.N > 0 && op.K > 0;
 }
 
-template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI>
+template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI, int NCONV>
 static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   CUtensorMap ma, mb;
   const int sw_in = BK == 32 ? (int)CU_TENSOR_MAP_SWIZZLE_128B : (int)CU_TENSOR_MAP_SWIZZLE_64B;
@@ -295,26 +295,30 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + NEPI * 32 * 128 + 256 + 1024;
   static_assert(SMEM <= 232448, "shared memory budget of one CTA");
   static std::atomic<unsigned long long> attr_mask{0};
-  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI>), SMEM, attr_mask);
+  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI, NCONV>), SMEM, attr_mask);
   if (e != cudaSuccess) return e;
   // persistent CTAs, one per SM: each walks its share of the 128 x BN output tiles
   const int num_sms = tc_current_num_sms();
   const long long n_tiles = (long long)((op.N + BN - 1) / BN) * ((op.M + TC_BM - 1) / TC_BM);
   const int grid = (int)(n_tiles < num_sms ? n_tiles : num_sms);
-  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI><<<grid, (2 + NEPI + (SPLIT ? TC_NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep);
+  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI, NCONV><<<grid, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep);
   return cudaGetLastError();
 }
 
 template <int BN, int BK, int STAGES, bool SPLIT>
 static cudaError_t launch_tc(const GemmOp& op, cudaStream_t st) {
-  if (op.bias || op.act) return launch_tc1<BN, BK, STAGES, SPLIT, 2, SPLIT ? 4 : 8>(op, st);
-  if (op.rowsum || op.scale || op.add_pre || op.add_post || (op.round_tf32 && !SPLIT))
-    return launch_tc1<BN, BK, STAGES, SPLIT, 1, SPLIT ? 4 : 8>(op, st);
-  // plain store: in fp32x3 a short reduction leaves the epilogue as the pace-setter (the full-Jacobian output R_0 =
-  // Q_0 W_0^T has K = 100 and 17 KB rows): eight epilogue warps there as well
-  if (SPLIT && op.K <= 256 && (STAGES * 2 * (TC_BM + BN) * BK * 4 + 8 * 32 * 128 + 1280 <= 232448))
-    return launch_tc1<BN, BK, STAGES, SPLIT, 0, 8>(op, st);
-  return launch_tc1<BN, BK, STAGES, SPLIT, 0, SPLIT ? 4 : 8>(op, st);
+  constexpr int NC = SPLIT ? TC_NCONV : 0;
+  // fp32x3 with a short reduction (the width-100 layers of the full-Jacobian network: K = 100 against 17 KB rows): the
+  // epilogue, not the main loop, sets the pace: eight epilogue warps and four converter warps (448 threads)
+  constexpr bool FITS8 = STAGES * 2 * (TC_BM + BN) * BK * 4 + 8 * 32 * 128 + 1280 <= 232448;
+  const bool short_k = SPLIT && FITS8 && op.K <= 256;
+  if (op.bias || op.act) return launch_tc1<BN, BK, STAGES, SPLIT, 2, SPLIT ? 4 : 8, NC>(op, st);
+  if (op.rowsum || op.scale || op.add_pre || op.add_post || (op.round_tf32 && !SPLIT)) {
+    if (short_k) return launch_tc1<BN, BK, STAGES, SPLIT, 1, 8, SPLIT ? 4 : 0>(op, st);
+    return launch_tc1<BN, BK, STAGES, SPLIT, 1, SPLIT ? 4 : 8, NC>(op, st);
+  }
+  if (short_k) return launch_tc1<BN, BK, STAGES, SPLIT, 0, 8, SPLIT ? 4 : 0>(op, st);
+  return launch_tc1<BN, BK, STAGES, SPLIT, 0, SPLIT ? 4 : 8, NC>(op, st);
 }
 
 cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st) {
