@@ -54,6 +54,11 @@ void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
   } while (0)
 
 static inline long long r4(long long n) { return (n + 3) & ~3LL; }
+// Row pitch of a workspace array (floats).  A multiple of 8 floats = 32 bytes: a row then starts on a DRAM sector, so
+// the 16-byte pieces of a row never split a sector (a pitch of 100 or 4228 floats - multiples of 4 only - made every
+// other row start in the middle of one, and half-sector writes are read-modify-write).  Long rows (the full-Jacobian
+// output, 4225 wide) get whole 128-byte lines.
+static inline long long rpitch(long long n) { return n >= 1024 ? (n + 31) & ~31LL : (n + 7) & ~7LL; }
 
 struct LayerPlan {
   int n_in, n_out, act, has_bias, trainable, skip_from;
@@ -63,7 +68,7 @@ struct LayerPlan {
   long long wp_lo_off, wtp_lo_off;          // fp32x3 + fused chain kernel: their low parts
   long long dr_off;          // dR_{l+1} = gradient wrt the chain state above this layer [B*s, ld_out]; -1 for the top layer
   long long da_off;          // da_l [B, ld_out] (fused MLP backward keeps every layer's for the grouped weight gradient)
-  long long ld_out;          // r4(n_out)
+  long long ld_out;          // rpitch(n_out)
   int lands_skip;            // index l2 of the skip layer whose source is THIS layer's input, or -1
 };
 
@@ -150,7 +155,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     }
     lp.koff = poff; poff += r4((long long)lp.n_in * lp.n_out);
     if (lp.has_bias) { lp.boff = poff; poff += r4(lp.n_out); } else lp.boff = -1;
-    lp.ld_out = r4(lp.n_out);
+    lp.ld_out = rpitch(lp.n_out);
     p->layers.push_back(lp);
     n_in = ls.n_out;
   }
@@ -176,9 +181,9 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   // ---- workspace layout ------------------------------------------------------------------------
   const long long Bm = p->max_batch, Ms = Bm * (long long)p->s;
   long long off = 0;
-  auto take = [&](long long n) { long long o = off; off += r4(n); return o; };
-  p->ld_in = r4(p->d_in);
-  p->ld_ident = r4(p->d_out);
+  auto take = [&](long long n) { long long o = off; off += (n + 31) & ~31LL; return o; };     // arrays start on 128-byte lines
+  p->ld_in = rpitch(p->d_in);
+  p->ld_ident = rpitch(p->d_out);
   p->off_ident = (p->jac_mode == DINO_JAC_FULL) ? take((long long)p->d_out * p->ld_ident) : -1;
   p->off_z0 = take(Bm * p->ld_in);
   long long max_w = p->ld_in;
@@ -231,7 +236,7 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   p->prep.n = 0;
   p->max_in = p->max_out = 1;
   p->prep.mode = p->split;
-  for (auto& lp : p->layers) { lp.wp_off = lp.wtp_off = lp.wp_lo_off = lp.wtp_lo_off = -1; lp.ld_wp = r4(lp.n_out); lp.ld_wtp = r4(lp.n_in); }
+  for (auto& lp : p->layers) { lp.wp_off = lp.wtp_off = lp.wp_lo_off = lp.wtp_lo_off = -1; lp.ld_wp = rpitch(lp.n_out); lp.ld_wtp = rpitch(lp.n_in); }
   if (p->tc && p->jac_mode != DINO_JAC_NONE) {
     if (p->L > 32) { delete p; return fail("dino_plan_create: the tensor-core modes support at most 32 layers"); }
     for (auto& lp : p->layers) {
