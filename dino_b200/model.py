@@ -820,8 +820,8 @@ class DinoModel:
         norms = stage.get("norms")
         if norms is None or norms.shape[1] != Bl:
             norms = stage["norms"] = torch.empty(2, Bl, dtype=torch.float32, device=dev)
-            stage["stats"] = torch.zeros(_lib.STAT_SLOTS, dtype=torch.float32, device=dev)
-            stage["grad"] = torch.zeros(self.core.n_params, dtype=torch.float32, device=dev)
+            stage["grad"] = torch.zeros(self.core.n_params + _lib.STAT_SLOTS, dtype=torch.float32, device=dev)
+            stage["stats"] = stage["grad"][self.core.n_params:]          # statistics at the tail: one all-reduce carries both
         ds.qn2 = norms[0]
         _lib.check(lib.dino_sample_sqnorms(C.c_void_p(ds.q.data_ptr()), Bl, ds.q[0].numel(),
                                            C.c_void_p(ds.qn2.data_ptr()), st), "dino_sample_sqnorms")
@@ -834,9 +834,7 @@ class DinoModel:
         stats.zero_()
         plan = self._plan(Bl)
         self._ensure_opt_state()
-        self._train_step(plan, ds.batch(None), Bl, Bl * dp.world, stage["grad"], stats, dp, st)
-        if dp.world > 1:
-            dp.all_reduce_sum(stats)
+        self._train_step(plan, ds.batch(None), Bl, Bl * dp.world, stage["grad"], stats, dp, st)   # (its all-reduce covers the tail)
         host = stats.cpu().numpy()[None, :]          # device->host read of the step's result
         self.last_h2d_bytes = sum(int(t.numel()) * 4 for k, t in stage.items() if k in ("m", "q", "J", "U", "V"))
         self.last_d2h_bytes = int(stats.numel()) * 4
@@ -861,7 +859,9 @@ class DinoModel:
             pipe = self._pipe = {"copy": torch.cuda.Stream(), "sets": [{}, {}], "grad": None}
         copy_stream = pipe["copy"]
         if pipe["grad"] is None:
-            pipe["grad"] = torch.zeros(self.core.n_params, dtype=torch.float32, device=dev)
+            # the step's statistics ride at the tail of the gradient buffer: ONE all-reduce per step carries both
+            pipe["grad"] = torch.zeros(self.core.n_params + _lib.STAT_SLOTS, dtype=torch.float32, device=dev)
+        stats_tail = pipe["grad"][self.core.n_params:]
         self._ensure_opt_state()
         st = _stream()
         rows, pending, h2d = [], None, 0
@@ -902,7 +902,6 @@ class DinoModel:
             compute.wait_event(S["copied"])
             if "norms" not in S or S["norms"].shape[1] != Bl:
                 S["norms"] = torch.empty(2, Bl, dtype=torch.float32, device=dev)
-                S["stats"] = torch.zeros(_lib.STAT_SLOTS, dtype=torch.float32, device=dev)
                 S["host"] = torch.zeros(_lib.STAT_SLOTS, dtype=torch.float32).pin_memory()
                 S.pop("graph", None)
             opt = self.optimizer
@@ -919,11 +918,11 @@ class DinoModel:
                     ds.jn2 = S["norms"][1]
                     _lib.check(lib.dino_sample_sqnorms(C.c_void_p(ds.J.data_ptr()), Bl, ds.J[0].numel(),
                                                        C.c_void_p(ds.jn2.data_ptr()), _stream()), "dino_sample_sqnorms")
-                S["stats"].zero_()
+                stats_tail.zero_()
                 params = self.core.device_params()
                 _lib.check(lib.dino_h1_fwd_bwd(plan.handle, C.c_void_p(params.data_ptr()), C.byref(ds.batch(None)), Bl,
                                                self.loss_weights[0], self.loss_weights[1], 1.0 / (Bl * dp.world),
-                                               C.c_void_p(pipe["grad"].data_ptr()), C.c_void_p(S["stats"].data_ptr()),
+                                               C.c_void_p(pipe["grad"].data_ptr()), C.c_void_p(stats_tail.data_ptr()),
                                                _stream()), "dino_h1_fwd_bwd")
                 if dp.world > 1:
                     dp.all_reduce_sum(pipe["grad"])
@@ -936,9 +935,7 @@ class DinoModel:
                     _lib.check(lib.dino_sgd(C.c_void_p(params.data_ptr()), C.c_void_p(pipe["grad"].data_ptr()),
                                             self.core.n_params, opt.learning_rate, _stream()), "dino_sgd")
                 opt._t_dev += 1
-                if dp.world > 1:
-                    dp.all_reduce_sum(S["stats"])
-                S["host"].copy_(S["stats"], non_blocking=True)      # device->host read of the step's result
+                S["host"].copy_(stats_tail, non_blocking=True)      # device->host read of the step's result
 
             gkey = (Bl, opt.kind, float(opt.learning_rate), tuple(self.loss_weights), self.core.device_params().data_ptr(),
                     id(plan))

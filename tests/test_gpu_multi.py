@@ -30,9 +30,19 @@ model = S.build_model(arch, w, precision=os.environ.get("DINO_TEST_PRECISION", "
 model.compile(optimizer=Adam(1e-3), loss=[normalized_mse, normalized_mse_matrix], loss_weights=[1.0, 1.0],
               metrics=[l2_accuracy, f_accuracy_matrix])
 hist = model.fit([data["m"]], [data["q"], data["J"]], epochs=epochs, batch_size=B, perms=perms)
+w_fit = [x for l in model.layers for x in l.get_weights()]
+# the streaming path with HOST minibatches (fit_generator): every rank passes its shard of each global minibatch; the
+# gradient and the step's statistics travel in ONE all-reduce (statistics at the tail of the gradient buffer)
+def shards():
+    for k in range(12):
+        lo = (k * B) % (n - B)
+        sl = slice(lo + dp.rank * (B // dp.world), lo + (dp.rank + 1) * (B // dp.world))
+        yield [data["m"][sl]], [data["q"][sl], data["J"][sl]]
+rows = model.fit_generator(shards())
 if dp.rank == 0:
-    np.savez(os.environ["DINO_OUT"], loss=np.array(hist.history["loss"]),
-             **{f"w{i}": a for i, a in enumerate(x for l in model.layers for x in l.get_weights())})
+    np.savez(os.environ["DINO_OUT"], loss=np.array(hist.history["loss"]), fg_loss=np.array([r[0] for r in rows]),
+             **{f"w{i}": a for i, a in enumerate(w_fit)},
+             **{f"g{i}": a for i, a in enumerate(x for l in model.layers for x in l.get_weights())})
 '''
 
 
@@ -55,7 +65,8 @@ def test_two_ranks_match_one_rank_after_100_steps(cuda_device, tmp_path, precisi
     one = _run(1, str(tmp_path / "one.npz"), precision)
     two = _run(2, str(tmp_path / "two.npz"), precision)
     assert np.allclose(one["loss"], two["loss"], rtol=1e-6 if precision == "fp32" else 2e-6, atol=0)
+    assert np.allclose(one["fg_loss"], two["fg_loss"], rtol=1e-5, atol=0)
     for k in one.files:
-        if k.startswith("w"):
+        if k.startswith("w") or k.startswith("g"):
             a, b = one[k], two[k]
             assert np.abs(a - b).max() <= 1e-5 * max(np.abs(a).max(), 1e-30), k
