@@ -37,7 +37,7 @@ class DinoNetSpec(C.Structure):
 class DinoBatch(C.Structure):
     _fields_ = [("m", C.c_void_p), ("q", C.c_void_p), ("J", C.c_void_p), ("q_sqnorm", C.c_void_p),
                 ("J_sqnorm", C.c_void_p), ("idx", C.c_void_p), ("U", C.c_void_p), ("V", C.c_void_p),
-                ("seed", C.c_void_p)]
+                ("seed", C.c_void_p), ("ld_J", C.c_int64), ("J_row_sqnorm", C.c_void_p), ("n_samples", C.c_int64)]
 
 
 # name -> (restype, argtypes): every symbol include/dino_b200.h declares

@@ -33,6 +33,13 @@ struct GemmOp {
   const float* add_post; long long ld_apo;
   int round_tf32;                                    // round the stored result to nearest TF32 (it feeds a TF32 MMA,
                                                      // which would otherwise TRUNCATE it: a systematic bias per layer)
+  // A gathered per sample from a dataset (tensor-core engines only): A row m = sample m / a_rows, row m % a_rows of
+  // that sample, and the sample sits at a_idx[.] (null: its own number) in an array [a_nsamp, a_rows, *] with row pitch
+  // a_sm (a_sk for the MN-major operand of a weight gradient) and sample pitch a_ld2 floats.  a_rows == 0: plain A.
+  const int* a_idx; int a_rows; long long a_ld2; long long a_nsamp;
+  float* rowdot;                                     // rowdot[m] += sum_n v * yref[m,n]  (v as the row sums see it)
+  int pre_first;                                     // add_pre joins BEFORE the row sums / rowdot see the value
+  float alpha;                                       // weight gradients: C += alpha * X^T Y
 };
 
 inline GemmOp gemm_op_zero() {
@@ -45,6 +52,7 @@ inline GemmOp gemm_op_zero() {
   o.yref = nullptr; o.ld_y = 0; o.rowsum = nullptr; o.ld_rs = 0;
   o.add_pre = nullptr; o.ld_ap = 0; o.scale = nullptr; o.ld_sc = 0;
   o.add_post = nullptr; o.ld_apo = 0; o.round_tf32 = 0;
+  o.a_idx = nullptr; o.a_rows = 0; o.a_ld2 = 0; o.a_nsamp = 0; o.rowdot = nullptr; o.pre_first = 0; o.alpha = 1.f;
   return o;
 }
 
@@ -109,9 +117,13 @@ cudaError_t launch_transpose_batched(const float* src, int B, int rows, int cols
 cudaError_t launch_loss_q(const float* qhat, long long ld_qh, const float* q, const float* qn2,
                           const int* idx, int B, int n, float coef, float* dq, long long ld_dq,
                           float* stats, cudaStream_t st);
-cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, const float* jn2,
+cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, long long ld_jt, const float* jn2,
                           const int* idx, int B, int sdim, int n, float coef, int write_grad,
-                          float* stats, cudaStream_t st);
+                          float* stats, cudaStream_t st);     // ld_jt: row pitch of the target (0: n)
+cudaError_t launch_implicit_prep(const float* Q, long long ld, int n, const float* jn2, const int* idx, int B, int sdim, float coef,
+                                 float* Qc, float* negc, cudaStream_t st);
+cudaError_t launch_implicit_loss(const float* ddot, const float* tdot, const float* jn2, const float* jrn2, const int* idx, int B,
+                                 int sdim, float coef, float* stats, cudaStream_t st);
 cudaError_t launch_mlp_da(const float* dz, long long ld_dz, const float* s, long long ld_s,
                           const float* rowsum, long long ld_rs, int B, int n, float* da,
                           long long ld_da, float* dbias, cudaStream_t st);

@@ -142,7 +142,7 @@ cudaError_t launch_loss_q(const float* qhat, long long ld_qh, const float* q, co
 // d loss / d J_hat = coef * (J_hat - J) / ||J_b||_F^2 when write_grad.
 __global__ void __launch_bounds__(256) loss_j_kernel(float* __restrict__ jhat, long long ld_jh,
                                                      const float* __restrict__ jt, const float* __restrict__ jn2,
-                                                     const int* __restrict__ idx, int B, int sdim, int n,
+                                                     const int* __restrict__ idx, int B, int sdim, int n, long long ld_jt,
                                                      float coef, int write_grad, float* __restrict__ stats) {
   __shared__ float red[3][8];
   const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(256) loss_j_kernel(float* __restrict__ jhat, l
   for (long long row = (long long)blockIdx.x * 8 + wib; row < rows; row += (long long)gridDim.x * 8) {
     const int b = (int)(row / sdim), i = (int)(row % sdim);
     const long long sb = idx ? idx[b] : b;
-    const float* t = jt + (sb * sdim + i) * (long long)n;
+    const float* t = jt + (sb * sdim + i) * ld_jt;
     float* p = jhat + row * ld_jh;
     const float nj = __ldg(jn2 + sb);
     const float g = coef / nj;
@@ -193,12 +193,73 @@ __global__ void __launch_bounds__(256) loss_j_kernel(float* __restrict__ jhat, l
     atomicAdd(stats + slot, v);
   }
 }
-cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, const float* jn2, const int* idx, int B,
+cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, long long ld_jt, const float* jn2, const int* idx, int B,
                           int sdim, int n, float coef, int write_grad, float* stats, cudaStream_t st) {
   const long long rows = (long long)B * sdim;
   if (rows <= 0) return cudaSuccess;
-  loss_j_kernel<<<min(cdiv(rows, 8), 148 * 16), 256, 0, st>>>(jhat, ld_jh, jt, jn2, idx, B, sdim, n, coef, write_grad,
-                                                            stats);
+  loss_j_kernel<<<min(cdiv(rows, 8), 148 * 16), 256, 0, st>>>(jhat, ld_jh, jt, jn2, idx, B, sdim, n, ld_jt > 0 ? ld_jt : n, coef,
+                                                            write_grad, stats);
+  return cudaGetLastError();
+}
+
+// ---- the first layer of a full-Jacobian network without its Jacobian (plan.cu: run_implicit_layer0) -----------------
+// Qc[row, :] = c_b Q[row, :] and negc[b, :] = -c_b with c_b = coef / ||J_b||^2: the per-sample weight of the H1 term
+__global__ void __launch_bounds__(256) implicit_prep_kernel(const float* __restrict__ Q, long long ld, int n, const float* __restrict__ jn2,
+                                                            const int* __restrict__ idx, int B, int sdim, float coef,
+                                                            float* __restrict__ Qc, float* __restrict__ negc) {
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long rows = (long long)B * sdim;
+  for (long long row = (long long)blockIdx.x * 8 + wib; row < rows; row += (long long)gridDim.x * 8) {
+    const int b = (int)(row / sdim);
+    const long long sb = idx ? idx[b] : b;
+    const float c = coef / __ldg(jn2 + sb);
+    for (int j = lane; j < ld; j += 32) Qc[row * ld + j] = j < n ? c * Q[row * ld + j] : 0.f;
+    if (row % sdim == 0)
+      for (int j = lane; j < ld; j += 32) negc[(long long)b * ld + j] = -c;
+  }
+}
+cudaError_t launch_implicit_prep(const float* Q, long long ld, int n, const float* jn2, const int* idx, int B, int sdim, float coef,
+                                 float* Qc, float* negc, cudaStream_t st) {
+  const long long rows = (long long)B * sdim;
+  if (rows <= 0) return cudaSuccess;
+  implicit_prep_kernel<<<min(cdiv(rows, 8), 148 * 16), 256, 0, st>>>(Q, ld, n, jn2, idx, B, sdim, coef, Qc, negc);
+  return cudaGetLastError();
+}
+
+// ||Jhat_row - J_row||^2 = ddot / c_b - tdot + ||J_row||^2 with the two row dot products the contractions left behind
+// (ddot = c_b <Q M - T, Q>_row, tdot = <T, Q>_row, T = J W, M = W^T W); the statistics loss_j_kernel would have written
+__global__ void __launch_bounds__(256) implicit_loss_kernel(const float* __restrict__ ddot, const float* __restrict__ tdot,
+                                                            const float* __restrict__ jn2, const float* __restrict__ jrn2,
+                                                            const int* __restrict__ idx, int B, int sdim, float coef,
+                                                            float* __restrict__ stats) {
+  __shared__ float red[3][8];
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long rows = (long long)B * sdim;
+  float h1 = 0.f, rr = 0.f, cnt = 0.f;
+  for (long long row = (long long)blockIdx.x * 256 + threadIdx.x; row < rows; row += (long long)gridDim.x * 256) {
+    const int b = (int)(row / sdim), i = (int)(row % sdim);
+    const long long sb = idx ? idx[b] : b;
+    const float nj = __ldg(jn2 + sb), nr = __ldg(jrn2 + sb * sdim + i);
+    const float e = ddot[row] * (nj / coef) - tdot[row] + nr;
+    h1 += e / nj;
+    rr += e / nr;
+    cnt += 1.f;
+  }
+  h1 = warp_sum(h1); rr = warp_sum(rr); cnt = warp_sum(cnt);
+  if (lane == 0) { red[0][wib] = h1; red[1][wib] = rr; red[2][wib] = cnt; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    float v = 0.f;
+    for (int w = 0; w < 8; ++w) v += red[threadIdx.x][w];
+    const int slot = threadIdx.x == 0 ? ST_H1_SUM : (threadIdx.x == 1 ? ST_JROW_SUM : ST_JROWS);
+    atomicAdd(stats + slot, v);
+  }
+}
+cudaError_t launch_implicit_loss(const float* ddot, const float* tdot, const float* jn2, const float* jrn2, const int* idx, int B,
+                                 int sdim, float coef, float* stats, cudaStream_t st) {
+  const long long rows = (long long)B * sdim;
+  if (rows <= 0) return cudaSuccess;
+  implicit_loss_kernel<<<min(cdiv(rows, 256), 148 * 4), 256, 0, st>>>(ddot, tdot, jn2, jrn2, idx, B, sdim, coef, stats);
   return cudaGetLastError();
 }
 

@@ -66,7 +66,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nkb = (ep.K + BK - 1) / BK;
   // persistent: this CTA walks the output tiles blockIdx.x, blockIdx.x + gridDim.x, ... (column tile fastest)
-  const int tiles_n = (ep.N + BN - 1) / BN, n_tiles = tiles_n * ((ep.M + TC_BM - 1) / TC_BM);
+  // (A gathered per sample: row tiles do not cross samples, ep.a_tps of them per sample)
+  const int tiles_n = (ep.N + BN - 1) / BN;
+  const int n_tiles = tiles_n * (ep.a_rows > 0 ? (ep.M / ep.a_rows) * ep.a_tps : (ep.M + TC_BM - 1) / TC_BM);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
@@ -93,14 +95,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     if (lane == 0) {
       int it = 0;                                    // running stage counter: the ring does not restart per tile
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int m0 = (tile / tiles_n) * TC_BM, n0 = (tile % tiles_n) * BN;
+        const int mt = tile / tiles_n, n0 = (tile % tiles_n) * BN;
+        int m0 = mt * TC_BM, samp = 0;
+        if (ep.a_rows > 0) {
+          const int b = mt / ep.a_tps;
+          m0 = (mt % ep.a_tps) * TC_BM;              // row inside the sample
+          samp = ep.a_idx ? ep.a_idx[b] : b;
+        }
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int st = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(empty_bar + st, ph ^ 1);
           mbar_expect_tx(full_bar + st, RAW_BYTES);
           uint8_t* sa = smem + st * STAGE_BYTES;
-          tma_load_2d(sa, &tma_a, kb * BK, m0, full_bar + st);
+          if (ep.a_rows > 0) tma_load_3d(sa, &tma_a, kb * BK, m0, samp, full_bar + st);
+          else tma_load_2d(sa, &tma_a, kb * BK, m0, full_bar + st);
           tma_load_2d(sa + A_BYTES, &tma_b, kb * BK, n0, full_bar + st);
         }
       }
@@ -167,11 +176,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     int i = 0;
 #pragma unroll 1
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
-      const int m0 = (tile / tiles_n) * TC_BM, n0 = (tile % tiles_n) * BN;
+      const int mt = tile / tiles_n, n0 = (tile % tiles_n) * BN;
+      int m0 = mt * TC_BM, m_lim = ep.M;
+      if (ep.a_rows > 0) {
+        const int b = mt / ep.a_tps, r0 = (mt % ep.a_tps) * TC_BM;
+        m0 = b * ep.a_rows + r0;
+        m_lim = b * ep.a_rows + min(ep.a_rows, r0 + TC_BM);
+      }
       const int acc = i % NACC;
       mbar_wait(tmem_full_bar + acc, (i / NACC) & 1);
       tc_fence_after();
-      tc_epilogue_tile<BN, SPLIT, EPI, NEPI, ACC_COLS>(ep, m0, n0, tmem_base + (uint32_t)acc * SET_COLS, my_stage, q, half, lane);
+      tc_epilogue_tile<BN, SPLIT, EPI, NEPI, ACC_COLS>(ep, m0, n0, tmem_base + (uint32_t)acc * SET_COLS, my_stage, q, half, lane, m_lim);
       // this warp is done reading the accumulator: hand it back to the MMA issuer
       tc_fence_before();
       __syncwarp();
@@ -259,10 +274,25 @@ bool tc_make_map(CUtensorMap* out, const float* base, unsigned long long inner, 
   return true;
 }
 
+bool tc_make_map3(CUtensorMap* out, const float* base, unsigned long long inner, unsigned long long rows,
+                  unsigned long long samples, long long ld, long long ld2, unsigned box_inner, unsigned box_rows, int swizzle) {
+  PFN_tmapEncodeTiled enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t gdim[3] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)samples};
+  cuuint64_t gstride[2] = {(cuuint64_t)ld * sizeof(float), (cuuint64_t)ld2 * sizeof(float)};
+  cuuint32_t box[3] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  return enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), gdim, gstride, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 bool gemm_tc_supported(const GemmOp& op) {
   if (op.a_sk != 1 || op.b_sk != 1) return false;                  // both operands K-major
   if (op.a_mod > 0 || op.b_kmod > 0) return false;
   if (op.atomic_c || op.k_per_split) return false;
+  if (op.a_rows > 0 && (op.M % op.a_rows || (op.a_ld2 & 3) || op.a_nsamp < 1)) return false;
+  if (op.rowdot && !op.yref) return false;
   if (op.C == nullptr && op.rowsum == nullptr) return false;
   if (op.C && ((op.ldc & 3) || (reinterpret_cast<uintptr_t>(op.C) & 15))) return false;
   if ((op.a_sm & 3) || (op.b_sn & 3)) return false;                // TMA: 16-byte row pitch
@@ -272,7 +302,7 @@ bool gemm_tc_supported(const GemmOp& op) {
   if (op.add_post && ((op.ld_apo & 3) || (reinterpret_cast<uintptr_t>(op.add_post) & 15))) return false;
   if (op.bias && (reinterpret_cast<uintptr_t>(op.bias) & 15)) return false;
   if (op.s_out && ((op.ld_s & 3) || (reinterpret_cast<uintptr_t>(op.s_out) & 15))) return false;
-  if (op.rowsum && (!op.yref || (op.ld_y & 3) || (reinterpret_cast<uintptr_t>(op.yref) & 15))) return false;
+  if ((op.rowsum || op.rowdot) && (!op.yref || (op.ld_y & 3) || (reinterpret_cast<uintptr_t>(op.yref) & 15))) return false;
   if (op.act && !op.C) return false;
   return op.M > 0 && op.N > 0 && op.K > 0;
 }
@@ -282,14 +312,18 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   CUtensorMap ma, mb;
   const int sw_in = BK == 32 ? (int)CU_TENSOR_MAP_SWIZZLE_128B : (int)CU_TENSOR_MAP_SWIZZLE_64B;
   // A[M,K] rows of a_sm floats; B operand is stored [N][K] (element (k,n) at n*b_sn + k)
-  if (!tc_make_map(&ma, op.A, op.K, op.M, op.a_sm, BK, TC_BM, sw_in) || !tc_make_map(&mb, op.B, op.K, op.N, op.b_sn, BK, BN, sw_in))
-    return cudaErrorInvalidValue;
+  if (op.a_rows > 0) {
+    if (!tc_make_map3(&ma, op.A, op.K, op.a_rows, op.a_nsamp, op.a_sm, op.a_ld2, BK, TC_BM, sw_in)) return cudaErrorInvalidValue;
+  } else if (!tc_make_map(&ma, op.A, op.K, op.M, op.a_sm, BK, TC_BM, sw_in)) return cudaErrorInvalidValue;
+  if (!tc_make_map(&mb, op.B, op.K, op.N, op.b_sn, BK, BN, sw_in)) return cudaErrorInvalidValue;
   TcEpilogue ep;
+  ep.a_rows = op.a_rows; ep.a_tps = op.a_rows > 0 ? (op.a_rows + TC_BM - 1) / TC_BM : 0; ep.a_idx = op.a_idx;
+  ep.rowdot = op.rowdot; ep.pre_first = op.pre_first;
   ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.C = op.C; ep.ldc = op.ldc; ep.sdim = op.sdim > 0 ? op.sdim : 1;
   ep.scale = op.scale; ep.ld_sc = op.ld_sc; ep.add_pre = op.add_pre; ep.ld_ap = op.ld_ap;
   ep.add_post = op.add_post; ep.ld_apo = op.ld_apo; ep.bias = op.bias; ep.act = op.act;
   ep.s_out = op.act ? op.s_out : nullptr; ep.ld_s = op.ld_s;
-  ep.yref = op.rowsum ? op.yref : nullptr; ep.ld_y = op.ld_y; ep.rowsum = op.rowsum; ep.ld_rs = op.ld_rs;
+  ep.yref = (op.rowsum || op.rowdot) ? op.yref : nullptr; ep.ld_y = op.ld_y; ep.rowsum = op.rowsum; ep.ld_rs = op.ld_rs;
   ep.round_tf32 = SPLIT ? 0 : op.round_tf32;
   constexpr int RAW = (TC_BM + BN) * BK * 4;
   constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + NEPI * 32 * 128 + 256 + 1024;
@@ -299,7 +333,8 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   if (e != cudaSuccess) return e;
   // persistent CTAs, one per SM: each walks its share of the 128 x BN output tiles
   const int num_sms = tc_current_num_sms();
-  const long long n_tiles = (long long)((op.N + BN - 1) / BN) * ((op.M + TC_BM - 1) / TC_BM);
+  const long long m_tiles = op.a_rows > 0 ? (long long)(op.M / op.a_rows) * ((op.a_rows + TC_BM - 1) / TC_BM) : (op.M + TC_BM - 1) / TC_BM;
+  const long long n_tiles = (long long)((op.N + BN - 1) / BN) * m_tiles;
   const int grid = (int)(n_tiles < num_sms ? n_tiles : num_sms);
   gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI, NCONV><<<grid, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep);
   return cudaGetLastError();
@@ -313,7 +348,7 @@ static cudaError_t launch_tc(const GemmOp& op, cudaStream_t st) {
   constexpr bool FITS8 = STAGES * 2 * (TC_BM + BN) * BK * 4 + 8 * 32 * 128 + 1280 <= 232448;
   const bool short_k = SPLIT && FITS8 && op.K <= 256;
   if (op.bias || op.act) return launch_tc1<BN, BK, STAGES, SPLIT, 2, SPLIT ? 4 : 8, NC>(op, st);
-  if (op.rowsum || op.scale || op.add_pre || op.add_post || (op.round_tf32 && !SPLIT)) {
+  if (op.rowsum || op.rowdot || op.scale || op.add_pre || op.add_post || (op.round_tf32 && !SPLIT)) {
     if (short_k) return launch_tc1<BN, BK, STAGES, SPLIT, 1, 8, SPLIT ? 4 : 0>(op, st);
     return launch_tc1<BN, BK, STAGES, SPLIT, 1, SPLIT ? 4 : 8, NC>(op, st);
   }
@@ -325,7 +360,7 @@ cudaError_t launch_gemm_tc(const GemmOp& op, int split, cudaStream_t st) {
   if (!gemm_tc_supported(op)) return cudaErrorNotSupported;
   static const int variant = getenv("DINO_TC_VARIANT") ? atoi(getenv("DINO_TC_VARIANT")) : 0;   // read once per process
   static const int cg2 = getenv("DINO_TC_CG2") ? atoi(getenv("DINO_TC_CG2")) : 3;              // CTA-pair kernel for bit 0: tf32, bit 1: fp32x3
-  if (((split ? 2 : 1) & cg2) && gemm_tc2_wanted(op)) return launch_gemm_tc2(op, split, st);
+  if (((split ? 2 : 1) & cg2) && op.a_rows == 0 && !op.rowdot && !op.pre_first && gemm_tc2_wanted(op)) return launch_gemm_tc2(op, split, st);
   const int num_sms = tc_current_num_sms();
   const long long m_tiles = (op.M + TC_BM - 1) / TC_BM;
   // widest tile that still gives every SM work (small-M contractions: the network's own forward / backward)

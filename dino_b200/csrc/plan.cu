@@ -95,6 +95,10 @@ struct DinoPlan {
   ChainSteps chain_steps;
   bool mlp_in_chain;         // the fused chain kernel also runs the MLP forward and the output loss of its samples
   bool chain_fused;
+  // first layer without its Jacobian (run_implicit_layer0): workspace of the scaled chain state, J W, the two Gram
+  // matrices and the per-row dot products
+  bool implicit0;
+  long long off_qc, off_tb, off_negc, off_mw, off_sb, off_tdot, off_ddot, imp_zero_floats;
   // optional per-kernel timing (dino_plan_profile): CUDA events around the Jacobian-chain stage of each step
   // side stream: the chain's weight gradients run concurrently with the MLP backward (fork/join by events)
   cudaStream_t side;
@@ -280,6 +284,27 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
       }
     }
   }
+  // first layer without its Jacobian: FULL Jacobian of a wide (unreduced) input through a plain softplus layer
+  p->implicit0 = false;
+  p->off_qc = p->off_tb = p->off_negc = p->off_mw = p->off_sb = p->off_tdot = p->off_ddot = -1; p->imp_zero_floats = 0;
+  {
+    const LayerPlan& l0 = p->layers[0];
+    static const int min_din = getenv("DINO_B200_IMPLICIT_MIN") ? atoi(getenv("DINO_B200_IMPLICIT_MIN")) : 1024;   // read once per process
+    if (p->tc && !p->chain_fused && p->jac_mode == DINO_JAC_FULL && p->L >= 2 && l0.act == DINO_ACT_SOFTPLUS &&
+        l0.skip_from < 0 && l0.lands_skip < 0 && p->layers[1].skip_from < 0 && (l0.n_out & 3) == 0 && p->d_in >= min_din &&
+        getenv("DINO_B200_NO_IMPLICIT0") == nullptr) {
+      p->implicit0 = true;
+      const long long n1 = l0.n_out;
+      p->off_qc = take(Ms * l0.ld_out);
+      p->off_tb = take(Ms * l0.ld_out);
+      p->off_negc = take(Bm * l0.ld_out);
+      p->off_mw = take(n1 * n1);                 // the four below are cleared together at the start of a step
+      p->off_sb = take(n1 * n1);
+      p->off_tdot = take(Ms);
+      p->off_ddot = take(Ms);
+      p->imp_zero_floats = off - p->off_mw;
+    }
+  }
   p->ws_floats = off;
   if (p->chain_fused && getenv("DINO_B200_NO_SIDE_STREAM") == nullptr) {
     DINO_CUDA(cudaSetDevice(device));
@@ -349,6 +374,8 @@ static int check_call(const DinoPlan* p, const float* params, const DinoBatch* b
   if (need_targets) {
     if (!b->q || !b->q_sqnorm) return fail("batch.q / batch.q_sqnorm is null");
     if (p->jac_mode != DINO_JAC_NONE && (!b->J || !b->J_sqnorm)) return fail("batch.J / batch.J_sqnorm is null");
+    if (b->ld_J != 0 && (p->jac_mode == DINO_JAC_SKETCHED || p->chain_fused || b->ld_J < p->d_in))
+      return fail("batch.ld_J: a row pitch is only taken for the FULL / OUT_REDUCED Jacobian targets of the layer-by-layer path, and must be >= d_in");
   }
   return 0;
 }
@@ -406,7 +433,8 @@ static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b,
 // Top operand of the chain: Q_{L-1}.  Returns pointer / ld / row-modulus.
 struct TopQ { const float* ptr; long long ld; int mod; };
 
-static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* b, int B, cudaStream_t st, TopQ* top_out) {
+static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* b, int B, cudaStream_t st, TopQ* top_out,
+                             bool skip_first = false) {
   float* ws = p->ws;
   const int s = p->s, L = p->L;
   const int M = B * s;
@@ -434,7 +462,7 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
   const bool tc = p->tc;
   // (the staged weight copies were written ahead of the MLP forward; with the fused MLP kernels, here)
   if (tc && (p->mlp_fused || p->chain_fused)) DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
-  for (int l = L - 1; l >= 0; --l) {
+  for (int l = L - 1; l >= (skip_first ? 1 : 0); --l) {
     const LayerPlan& lp = p->layers[l];
     GemmOp op = gemm_op_zero();
     if (l == L - 1) { op.A = top.ptr; op.a_sm = top.ld; op.a_mod = top.mod; }
@@ -534,11 +562,11 @@ static int run_losses(DinoPlan* p, const DinoBatch* b, int B, float w_l2, float 
   if (p->jac_mode == DINO_JAC_SKETCHED) {
     const int k = p->s;
     DINO_LAUNCH(launch_sketch_close(ws + p->off_r0, p->ld_in, b->V, b->idx, B, k, p->d_in, ws + p->off_sk, st));
-    DINO_LAUNCH(launch_loss_j(ws + p->off_sk, k, b->J, b->J_sqnorm, b->idx, B, k, k, cj, grads ? 1 : 0, stats, st));
+    DINO_LAUNCH(launch_loss_j(ws + p->off_sk, k, b->J, 0, b->J_sqnorm, b->idx, B, k, k, cj, grads ? 1 : 0, stats, st));
     if (grads)
       DINO_LAUNCH(launch_sketch_open(ws + p->off_sk, b->V, b->idx, B, k, p->d_in, ws + p->off_r0, p->ld_in, st));
   } else {
-    DINO_LAUNCH(launch_loss_j(ws + p->off_r0, p->ld_in, b->J, b->J_sqnorm, b->idx, B, p->s, p->d_in, cj,
+    DINO_LAUNCH(launch_loss_j(ws + p->off_r0, p->ld_in, b->J, b->ld_J, b->J_sqnorm, b->idx, B, p->s, p->d_in, cj,
                               grads ? 1 : 0, stats, st));
   }
   return 0;
@@ -570,8 +598,116 @@ static int flush_wgrad(DinoPlan* p, GemmGroup& g, cudaStream_t st) {
   return 0;
 }
 
+// ---- first layer without its Jacobian ------------------------------------------------------------------------
+// FULL Jacobian of an unreduced input (d_in in the thousands, first layer W [d_in, n1], chain state Q [B*s, n1] above it):
+//   J_hat = Q W^T  [B*s, d_in]   is the only d_in-wide array of the step; the explicit path writes it, reads it with the
+// target, writes G = c_b (J_hat - J) over it and reads G twice more (data gradient G W, weight gradient G^T Q).  Both
+// products are linear in G, so with T = J W and M = W^T W (n1 x n1):
+//   G W   = c_b (Q M - T)                       -> contraction over d_in with the TARGET as operand, then an n1-wide one
+//   G^T Q = W (sum_b c_b Q_b^T Q_b) - J^T (c_b Q)
+//   ||J_hat - J||^2_row = <Q M, Q>_row - 2 <T, Q>_row + ||J_row||^2
+// and J_hat never exists: the target is read twice (by TMA, gathered per sample through a 3-D tensor map) instead of
+// the six passes over [B*s, d_in].  The arithmetic is the explicit path's to rounding: there J_hat carries the
+// contraction's error (1e-6 |J_hat| in fp32x3) into the difference, here T and Q M carry it.
+struct ImplicitCtx { const DinoBatch* b; float cj; float* stats; };
+
+static long long implicit_nsamp(const DinoBatch* b, int B) {
+  return b->idx ? (b->n_samples > 0 ? (long long)b->n_samples : (1LL << 22)) : (long long)B;
+}
+static GemmOp implicit_t1_op(const DinoPlan* p, const DinoBatch* b, int B) {
+  const LayerPlan& l0 = p->layers[0];
+  float* ws = p->ws;
+  GemmOp op = gemm_op_zero();
+  op.A = b->J; op.a_sm = b->ld_J; op.a_sk = 1;
+  op.a_rows = p->s; op.a_ld2 = (long long)p->s * b->ld_J; op.a_idx = b->idx; op.a_nsamp = implicit_nsamp(b, B);
+  op.B = ws + l0.wtp_off; op.b_sk = 1; op.b_sn = l0.ld_wtp;
+  op.M = B * p->s; op.N = l0.n_out; op.K = l0.n_in; op.sdim = p->s;
+  op.scale = ws + p->off_negc; op.ld_sc = l0.ld_out;
+  op.yref = ws + l0.q_off; op.ld_y = l0.ld_out; op.rowdot = ws + p->off_tdot;
+  op.C = ws + p->off_tb; op.ldc = l0.ld_out;
+  return op;
+}
+static GemmOp implicit_t2_op(const DinoPlan* p, const DinoBatch* b, int B, float* grad) {
+  const LayerPlan& l0 = p->layers[0];
+  float* ws = p->ws;
+  GemmOp op = gemm_op_zero();
+  op.A = b->J; op.a_sm = 1; op.a_sk = b->ld_J;
+  op.a_rows = p->s; op.a_ld2 = (long long)p->s * b->ld_J; op.a_idx = b->idx; op.a_nsamp = implicit_nsamp(b, B);
+  op.B = ws + p->off_qc; op.b_sk = l0.ld_out; op.b_sn = 1;
+  op.M = l0.n_in; op.N = l0.n_out; op.K = B * p->s;
+  op.C = grad + l0.koff; op.ldc = l0.n_out; op.atomic_c = 1; op.alpha = -1.f;
+  return op;
+}
+// this call can take the implicit first layer: plan, target layout and the engines' alignment rules
+static bool implicit_applicable(const DinoPlan* p, const DinoBatch* b, int B, float w_h1, float* grad) {
+  if (!p->implicit0 || w_h1 == 0.f || !b->J_row_sqnorm || b->ld_J < p->d_in || (b->ld_J & 3)) return false;
+  return gemm_tc_supported(implicit_t1_op(p, b, B)) && wgrad_tc_supported(implicit_t2_op(p, b, B, grad));
+}
+
+static int flush_wgrad(DinoPlan* p, GemmGroup& g, cudaStream_t st);
+static int push_wgrad(DinoPlan* p, GemmGroup& g, const GemmOp& op, cudaStream_t st);
+
+// layer 0 of the backward chain in that form: leaves dR_1 (the state gradient above layer 0), rs_0, the H1 statistics,
+// W S in the gradient of W (plain store: it runs before every accumulation into that block) and J^T (c Q) pending in wg
+static int run_implicit_layer0(DinoPlan* p, const float* params, int B, float* grad, GemmGroup& wg, const ImplicitCtx& cx,
+                               cudaStream_t st) {
+  float* ws = p->ws;
+  const DinoBatch* b = cx.b;
+  const LayerPlan& l0 = p->layers[0];
+  const int s = p->s, M = B * s, n1 = l0.n_out;
+  const float* Q = ws + l0.q_off;
+  const float* W = params + l0.koff;
+  DINO_CUDA(cudaMemsetAsync(ws + p->off_mw, 0, (size_t)p->imp_zero_floats * sizeof(float), st));
+  DINO_LAUNCH(launch_implicit_prep(Q, l0.ld_out, n1, b->J_sqnorm, b->idx, B, s, cx.cj, ws + p->off_qc, ws + p->off_negc, st));
+  {   // M = W^T W and S = (c Q)^T Q: two small Gram matrices in one grouped launch
+    GemmGroup g2;
+    g2.n = 0;
+    GemmOp op = gemm_op_zero();
+    op.A = W; op.a_sm = 1; op.a_sk = n1; op.B = W; op.b_sk = n1; op.b_sn = 1;
+    op.M = n1; op.N = n1; op.K = l0.n_in; op.C = ws + p->off_mw; op.ldc = n1; op.atomic_c = 1;
+    g2.ops[g2.n++] = op;
+    if (l0.trainable) {
+      op = gemm_op_zero();
+      op.A = ws + p->off_qc; op.a_sm = 1; op.a_sk = l0.ld_out; op.B = Q; op.b_sk = l0.ld_out; op.b_sn = 1;
+      op.M = n1; op.N = n1; op.K = M; op.C = ws + p->off_sb; op.ldc = n1; op.atomic_c = 1;
+      g2.ops[g2.n++] = op;
+    }
+    if (flush_wgrad(p, g2, st)) return 1;
+  }
+  // T = J W, stored as -c_b T; tdot[row] = <T, Q>_row
+  if (gemm(p, implicit_t1_op(p, b, B), st)) return 1;
+  {   // dQ_0 = c_b (Q M - T): row sums for d sigma, ddot[row] = <dQ_0, Q>_row, then * sg_0 -> dR_1
+    GemmOp op = gemm_op_zero();
+    op.A = ws + p->off_qc; op.a_sm = l0.ld_out; op.a_sk = 1;
+    op.B = ws + p->off_mw; op.b_sk = 1; op.b_sn = n1;              // symmetric
+    op.M = M; op.N = n1; op.K = n1; op.sdim = s;
+    op.add_pre = ws + p->off_tb; op.ld_ap = l0.ld_out; op.pre_first = 1;
+    op.yref = Q; op.ld_y = l0.ld_out;
+    op.rowsum = ws + l0.rs_off; op.ld_rs = l0.ld_out;
+    op.rowdot = ws + p->off_ddot;
+    op.scale = ws + l0.sg_off; op.ld_sc = l0.ld_out;
+    op.C = ws + l0.dr_off; op.ldc = l0.ld_out;
+    op.round_tf32 = p->split ? 0 : 1;
+    if (!gemm_tc_supported(op)) return fail("implicit first layer: contraction not supported by the tcgen05 engine");
+    if (gemm(p, op, st)) return 1;
+  }
+  DINO_LAUNCH(launch_implicit_loss(ws + p->off_ddot, ws + p->off_tdot, b->J_sqnorm, b->J_row_sqnorm, b->idx, B, s, cx.cj,
+                                   cx.stats, st));
+  if (l0.trainable) {
+    GemmOp op = gemm_op_zero();          // dW_0 = W S ...
+    op.A = W; op.a_sm = n1; op.a_sk = 1;
+    op.B = ws + p->off_sb; op.b_sk = 1; op.b_sn = n1;              // symmetric
+    op.M = l0.n_in; op.N = n1; op.K = n1;
+    op.C = grad + l0.koff; op.ldc = n1;
+    if (!gemm_tc_supported(op)) return fail("implicit first layer: contraction not supported by the tcgen05 engine");
+    if (gemm(p, op, st)) return 1;
+    if (push_wgrad(p, wg, implicit_t2_op(p, b, B, grad), st)) return 1;      // ... - J^T (c Q), with the step's other weight gradients
+  }
+  return 0;
+}
+
 static int run_chain_backward(DinoPlan* p, const float* params, int B, float* grad, const TopQ& top, GemmGroup& wg,
-                              cudaStream_t st) {
+                              cudaStream_t st, const ImplicitCtx* imp = nullptr) {
   float* ws = p->ws;
   const int s = p->s, L = p->L, M = B * s;
   // dR_l (gradient wrt the chain state entering layer l from below): l == 0 -> R0 buffer (holds G);
@@ -580,6 +716,10 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
   auto dr_ld = [&](int l) { return l == 0 ? p->ld_in : p->layers[l - 1].ld_out; };
   for (int l = 0; l < L; ++l) {
     const LayerPlan& lp = p->layers[l];
+    if (l == 0 && imp != nullptr) {
+      if (run_implicit_layer0(p, params, B, grad, wg, *imp, st)) return 1;
+      continue;
+    }
     const float* q; long long ldq; int qmod;
     if (l == L - 1) { q = top.ptr; ldq = top.ld; qmod = top.mod; }
     else { q = ws + lp.q_off; ldq = lp.ld_out; qmod = 0; }
@@ -803,10 +943,12 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
     }
     if (push_chain_wgrads(p, B, grad, top, wg, st)) return 1;
   } else {
+    const bool imp = implicit_applicable(p, b, B, w_h1, grad);
+    const ImplicitCtx cx = {b, 2.f * w_h1 * inv_gb, stats};
     if (prof_begin(p, st)) return 1;
-    if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top)) return 1;
-    if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st)) return 1;
-    if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, wg, st)) return 1;
+    if (p->jac_mode != DINO_JAC_NONE && run_chain_forward(p, params, b, B, st, &top, imp)) return 1;
+    if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st, imp)) return 1;
+    if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, wg, st, imp ? &cx : nullptr)) return 1;
     if (prof_end(p, st)) return 1;
   }
   if (run_mlp_backward(p, params, B, grad, wg, st)) return 1;

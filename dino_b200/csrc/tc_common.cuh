@@ -42,6 +42,11 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
@@ -223,5 +228,9 @@ int tc_current_num_sms();
 // swizzle is a CUtensorMapSwizzle value.
 bool tc_make_map(CUtensorMap* out, const float* base, unsigned long long inner, unsigned long long outer, long long ld,
                  unsigned box_inner, unsigned box_outer, int swizzle);
+// 3-D fp32 tensor map [samples, rows, inner] (row pitch ld, sample pitch ld2 floats), box {box_inner, box_rows, 1}: an
+// operand gathered per sample from a dataset; rows beyond a sample's own are zero-filled, never the next sample's.
+bool tc_make_map3(CUtensorMap* out, const float* base, unsigned long long inner, unsigned long long rows,
+                  unsigned long long samples, long long ld, long long ld2, unsigned box_inner, unsigned box_rows, int swizzle);
 
 }  // namespace dino

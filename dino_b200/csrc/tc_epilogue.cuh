@@ -16,6 +16,10 @@ struct TcEpilogue {
   int act; float* s_out; long long ld_s;
   const float* yref; long long ld_y; float* rowsum; long long ld_rs;
   int round_tf32;
+  // gemm_tc.cu only: A gathered per sample (a_rows rows each, a_tps row tiles per sample, sample numbers a_idx or 0..),
+  // per-row dot products with yref, add_pre ahead of the row sums
+  int a_rows, a_tps; const int* a_idx;
+  float* rowdot; int pre_first;
 };
 
 // 4 floats of a row at column n (n % 4 == 0): vector load when the four lie inside N, guarded scalars at the edge
@@ -34,12 +38,12 @@ __device__ __forceinline__ float4 tc_ld4(const float* row, int n, int N) {
 // sigmoid / add_pre / add_post).  SPLIT: the cross-term accumulator sits ACC_COLS columns above the main one.
 template <int BN, bool SPLIT, int EPI, int NEPI, uint32_t ACC_COLS>
 __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, int n0, uint32_t tacc_base, uint32_t my_stage,
-                                                 int q, int half, int lane) {
+                                                 int q, int half, int lane, int m_lim) {
   using namespace tc;
   const uint32_t sw = (uint32_t)(lane & 7);
   {
       const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < ep.M;
+      const bool row_ok = row < m_lim;     // m_lim: first row past this tile's share of C (M, or the end of the sample)
       const int b = row_ok ? row / ep.sdim : 0;
       const float* sc = (EPI == 1 && ep.scale) ? ep.scale + (long long)b * ep.ld_sc : nullptr;
       const float* ap = (EPI != 0 && ep.add_pre) ? ep.add_pre + (long long)row * ep.ld_ap : nullptr;
@@ -47,6 +51,8 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, i
       const float* yr = (EPI == 1 && ep.yref) ? ep.yref + (long long)row * ep.ld_y : nullptr;
       float* so = (EPI == 2 && ep.s_out) ? ep.s_out + (long long)row * ep.ld_s : nullptr;
       const uint32_t tacc = tacc_base + ((uint32_t)(q * 32) << 16);
+      const bool pre_first = EPI == 1 && ep.pre_first && ap;
+      float rdot = 0.f;
 #pragma unroll 1
       for (int c0 = half * 32; c0 < BN; c0 += 32 * (NEPI / 4)) {
         if (n0 + c0 >= ep.N) break;                  // warp-uniform
@@ -76,6 +82,12 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, i
             }
           }
         };
+        if (pre_first) {
+          float t[32];
+          load32(t, ap, row_ok);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += t[j];
+        }
         if (EPI == 1 && yr) {
           // d sigma term: rowsum[sample, n] += sum over the sample's chain rows of acc * yref  (segmented over the
           // samples under this warp's 32 rows; lane j ends up with column j)
@@ -83,9 +95,13 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, i
           load32(p, yr, row_ok);
 #pragma unroll
           for (int j = 0; j < 32; ++j) p[j] *= v[j];
+          if (ep.rowdot) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) rdot += p[j];
+          }
           const int r_first = m0 + q * 32;
-          if (r_first < ep.M) {
-            const int b_lo = r_first / ep.sdim, b_hi = min(r_first + 31, ep.M - 1) / ep.sdim;
+          if (ep.rowsum && r_first < m_lim) {
+            const int b_lo = r_first / ep.sdim, b_hi = min(r_first + 31, m_lim - 1) / ep.sdim;
             for (int bb = b_lo; bb <= b_hi; ++bb) {
               float mm[32];
 #pragma unroll
@@ -124,7 +140,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, i
           }
         }
         if (EPI != 0) {
-          if (ap) {
+          if (ap && !pre_first) {
             float t[32];
             load32(t, ap, row_ok);
 #pragma unroll
@@ -156,7 +172,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, i
         __syncwarp();
         const int ch = lane & 7, n = nb + 4 * ch;
         float* cbase = ep.C + (long long)(m0 + q * 32 + (lane >> 3)) * ep.ldc + n;
-        const int rows_left = ep.M - (m0 + q * 32 + (lane >> 3));      // this lane's rows: rows_left > 4 * it
+        const int rows_left = m_lim - (m0 + q * 32 + (lane >> 3));      // this lane's rows: rows_left > 4 * it
         if (full) {
 #pragma unroll
           for (int it = 0; it < 8; ++it) {
@@ -177,6 +193,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, i
           }
         }
       }
+      if (EPI == 1 && ep.rowdot && row_ok) atomicAdd(ep.rowdot + row, rdot);
   }
 }
 

@@ -31,6 +31,10 @@ struct WgOp {
   int chunks_per_cta;       // reduction chunks (of BK rows) per CTA
   int n_tiles, splits;      // CTAs of this op: m_tiles * n_tiles * splits, split fastest
   int mn;                   // 1: operands are the ROW-major chain states [rows, n] (MN-major UMMA operands), 0: transposed copies
+  // X gathered per sample from a dataset [samples, x_rows, n_in] (3-D tensor map): the reduction runs over chunks that
+  // do not cross samples, x_cps of them per sample (the last one zero-filled past the sample's rows)
+  const int* x_idx; int x_rows, x_cps;
+  float alpha;              // C += alpha * X^T Y
 };
 struct WgGroup {
   int n;
@@ -57,7 +61,7 @@ __global__ void __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1) wgrad_tc
   int oi = 0;
   while (oi + 1 < g.n && (int)blockIdx.x >= g.op[oi + 1].z_start) ++oi;
   const WgOp& op = g.op[oi];
-  const int total_chunks = (op.rows + BK - 1) / BK;
+  const int total_chunks = op.x_rows > 0 ? (op.rows / op.x_rows) * op.x_cps : (op.rows + BK - 1) / BK;
   const int local = blockIdx.x - op.z_start;
   const int split = local % op.splits, tile = local / op.splits;
   const int m0 = (tile / op.n_tiles) * 128, n0 = (tile % op.n_tiles) * TN;
@@ -93,7 +97,14 @@ __global__ void __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1) wgrad_tc
           mbar_wait(empty_bar + st, ((c / STAGES) & 1) ^ 1);
           uint8_t* sx = smem + st * STAGE_BYTES;
           const int k0 = (c_begin + c) * BK;
-          if (op.mn) {
+          if (op.x_rows > 0) {
+            const int b = (c_begin + c) / op.x_cps, r0 = ((c_begin + c) % op.x_cps) * BK;
+            const int samp = op.x_idx ? op.x_idx[b] : b;
+            mbar_expect_tx(full_bar + st, (uint32_t)((ga + gb) * GROUP_BYTES));
+            for (int gI = 0; gI < ga; ++gI) tma_load_3d(sx + gI * GROUP_BYTES, mx, m0 + 32 * gI, r0, samp, full_bar + st);
+            // (Y rows past the sample's last meet zero-filled X rows)
+            for (int gI = 0; gI < gb; ++gI) tma_load_2d(sx + A_BYTES + gI * GROUP_BYTES, my, n0 + 32 * gI, b * op.x_rows + r0, full_bar + st);
+          } else if (op.mn) {
             mbar_expect_tx(full_bar + st, (uint32_t)((ga + gb) * GROUP_BYTES));
             for (int gI = 0; gI < ga; ++gI) tma_load_2d(sx + gI * GROUP_BYTES, mx, m0 + 32 * gI, k0, full_bar + st);
             for (int gI = 0; gI < gb; ++gI) tma_load_2d(sx + A_BYTES + gI * GROUP_BYTES, my, n0 + 32 * gI, k0, full_bar + st);
@@ -157,6 +168,10 @@ __global__ void __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1) wgrad_tc
           tmem_ld32(taddr + TN, x);
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += x[j];
+        }
+        if (op.alpha != 1.f) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] *= op.alpha;
         }
         if (m < op.n_in) {
           float* crow = op.C + (long long)m * op.n_out + n0 + c0;
@@ -356,6 +371,7 @@ bool wgrad_tc_supported(const GemmOp& op) {
   if (kmaj && ((op.a_sm & 3) || (op.b_sn & 3))) return false;
   if (!kmaj && ((op.a_sk & 3) || (op.b_sk & 3))) return false;
   if ((reinterpret_cast<uintptr_t>(op.A) & 15) || (reinterpret_cast<uintptr_t>(op.B) & 15)) return false;
+  if (op.a_rows > 0 && (!mnmaj || op.K % op.a_rows || (op.a_ld2 & 3) || op.a_nsamp < 1)) return false;
   return op.ldc == op.N;
 }
 
@@ -374,7 +390,8 @@ static cudaError_t launch_wg(const GemmGroup& gg, int num_sms, cudaStream_t st) 
     const GemmOp& o = gg.ops[i];
     WgOp& w = g.op[i];
     w.C = o.C; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
-    const int chunks = (o.K + BK - 1) / BK;
+    w.x_idx = o.a_idx; w.x_rows = o.a_rows; w.x_cps = o.a_rows > 0 ? (o.a_rows + BK - 1) / BK : 0; w.alpha = o.alpha;
+    const int chunks = o.a_rows > 0 ? (o.K / o.a_rows) * w.x_cps : (o.K + BK - 1) / BK;
     const int m_tiles = (o.M + 127) / 128;
     w.n_tiles = (o.N + TN - 1) / TN;
     const int tiles = m_tiles * w.n_tiles;
@@ -389,7 +406,12 @@ static cudaError_t launch_wg(const GemmGroup& gg, int num_sms, cudaStream_t st) 
     w.z_start = z;
     z += tiles * w.splits;
     w.mn = (o.a_sk == 1 && o.b_sk == 1) ? 0 : 1;
-    if (w.mn) {
+    if (o.a_rows > 0) {
+      if (!w.mn) return cudaErrorNotSupported;
+      if (!tc_make_map3(&g.mx[i], o.A, (unsigned long long)o.M, (unsigned long long)o.a_rows, (unsigned long long)o.a_nsamp, o.a_sk, o.a_ld2, 32, BK, (int)CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) ||
+          !tc_make_map(&g.my[i], o.B, (unsigned long long)o.N, (unsigned long long)o.K, o.b_sk, 32, BK, (int)CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))
+        return cudaErrorInvalidValue;
+    } else if (w.mn) {
       // ROW-major [rows, n] with pitch a_sk / b_sk: box = 32 columns x BK reduction rows, 32-byte-atom swizzle
       if (!tc_make_map(&g.mx[i], o.A, (unsigned long long)o.M, (unsigned long long)o.K, o.a_sk, 32, BK, (int)CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) ||
           !tc_make_map(&g.my[i], o.B, (unsigned long long)o.N, (unsigned long long)o.K, o.b_sk, 32, BK, (int)CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))
@@ -427,6 +449,7 @@ static cudaError_t launch_wg2(const GemmGroup& gg, int num_sms, cudaStream_t st)
     const GemmOp& o = gg.ops[i];
     WgOp& w = g.op[i];
     w.C = o.C; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
+    w.x_idx = nullptr; w.x_rows = 0; w.x_cps = 0; w.alpha = 1.f;      // (gathered / scaled ops never come here)
     const int chunks = (o.K + BK - 1) / BK;
     w.n_tiles = (o.N + 255) / 256;
     const int tiles = ((o.M + 255) / 256) * w.n_tiles;
@@ -464,7 +487,7 @@ cudaError_t launch_wgrad_tc(const GemmGroup& gg, int split, int num_sms, cudaStr
     for (int i = 0; i < gg.n; ++i) {
       const GemmOp& o = gg.ops[i];
       const bool mn = !(o.a_sk == 1 && o.b_sk == 1);
-      if (mn && o.M > 128 && o.N > 128 && o.K >= 2048) big.ops[big.n++] = o; else rest.ops[rest.n++] = o;
+      if (mn && o.a_rows == 0 && o.alpha == 1.f && o.M > 128 && o.N > 128 && o.K >= 2048) big.ops[big.n++] = o; else rest.ops[rest.n++] = o;
     }
     if (big.n > 0) {
       cudaError_t e = split ? launch_wg2<32, 3, true>(big, num_sms, st) : launch_wg2<64, 3, false>(big, num_sms, st);
@@ -479,14 +502,23 @@ cudaError_t launch_wgrad_tc(const GemmGroup& gg, int split, int num_sms, cudaStr
 }
 
 static cudaError_t launch_wgrad_tc_rest(const GemmGroup& gg, int split, int num_sms, cudaStream_t st) {
-  // wide outputs take 128 x 256 tiles; transposed (K-major) factors only exist for the 128-wide kernels
-  bool wide = false, kmajor = false;
+  // outputs wider than 128 take 128 x 256 tiles (row-major factors only: transposed, K-major factors exist for the 128-wide
+  // kernels); everything else 128 x 128.  The group is split by width: a 100-wide layer in a 256-wide tile would spend
+  // 60 % of its tensor cycles on padding (the 4225 x 100 first layer of the full-Jacobian network shares its step with a
+  // 100 x 400 output layer)
+  GemmGroup wide, narrow;
+  wide.n = narrow.n = 0;
   for (int i = 0; i < gg.n; ++i) {
-    if (gg.ops[i].N > 128) wide = true;
-    if (gg.ops[i].a_sk == 1 && gg.ops[i].b_sk == 1) kmajor = true;
+    const GemmOp& o = gg.ops[i];
+    const bool kmajor = o.a_sk == 1 && o.b_sk == 1;
+    if (o.N > 128 && !kmajor) wide.ops[wide.n++] = o; else narrow.ops[narrow.n++] = o;
   }
-  if (wide && !kmajor) return split ? launch_wg<256, 16, 4, true>(gg, num_sms, st) : launch_wg<256, 32, 4, false>(gg, num_sms, st);
-  return split ? launch_wg<128, 32, 3, true>(gg, num_sms, st) : launch_wg<128, 32, 3, false>(gg, num_sms, st);
+  if (wide.n > 0) {
+    cudaError_t e = split ? launch_wg<256, 16, 4, true>(wide, num_sms, st) : launch_wg<256, 32, 4, false>(wide, num_sms, st);
+    if (e != cudaSuccess) return e;
+  }
+  if (narrow.n > 0) return split ? launch_wg<128, 32, 3, true>(narrow, num_sms, st) : launch_wg<128, 32, 3, false>(narrow, num_sms, st);
+  return cudaSuccess;
 }
 
 }  // namespace dino

@@ -265,6 +265,9 @@ class DeviceDataset:
     """(m, q, J[, U, V]) of one fit/evaluate call, resident in HBM as fp32 (numpy fp64 sources are
     cast on upload, exactly as Keras casts to floatx on feed)."""
 
+    ld_J = 0        # row pitch of J in floats (0: dense) and per-row squared norms: set by _prepare_wide_J
+    jrn2 = None
+
     def __init__(self, jac_mode: int, x: Sequence[np.ndarray], y: Optional[Sequence[np.ndarray]], seed=None):
         import torch
         lib = _lib.load()
@@ -279,6 +282,7 @@ class DeviceDataset:
         self.m = up(x[0])
         self.n = int(self.m.shape[0])
         self.U = self.V = self.q = self.J = self.qn2 = self.jn2 = None
+        self.ld_J, self.jrn2 = 0, None
         self.seed = None if seed is None else up(seed)
         if jac_mode == _lib.JAC_SKETCHED:
             if len(x) != 3:
@@ -296,6 +300,7 @@ class DeviceDataset:
                 self.jn2 = torch.empty(self.n, dtype=torch.float32, device=dev)
                 _lib.check(lib.dino_sample_sqnorms(C.c_void_p(self.J.data_ptr()), self.n, self.J[0].numel(),
                                                    C.c_void_p(self.jn2.data_ptr()), _stream()), "dino_sample_sqnorms")
+                self._prepare_wide_J(jac_mode)
 
     @classmethod
     def from_device(cls, jac_mode: int, m, q=None, J=None, seed=None, U=None, V=None):
@@ -306,6 +311,7 @@ class DeviceDataset:
         ds.m, ds.q, ds.J, ds.U, ds.V, ds.seed = m, q, J, U, V, seed
         ds.n = int(m.shape[0])
         ds.qn2 = ds.jn2 = None
+        ds.ld_J, ds.jrn2 = 0, None
         for t in (m, q, J, U, V, seed):
             if t is not None and (t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda):
                 raise ValueError("DeviceDataset.from_device needs contiguous fp32 CUDA tensors")
@@ -317,7 +323,30 @@ class DeviceDataset:
             ds.jn2 = torch.empty(ds.n, dtype=torch.float32, device=m.device)
             _lib.check(lib.dino_sample_sqnorms(C.c_void_p(J.data_ptr()), ds.n, J[0].numel(), C.c_void_p(ds.jn2.data_ptr()),
                                                _stream()), "dino_sample_sqnorms")
+            ds._prepare_wide_J(jac_mode)
         return ds
+
+    def _prepare_wide_J(self, jac_mode: int):
+        """Targets of a FULL Jacobian over an unreduced input (d_in in the thousands): rows on a 16-byte pitch (zero
+        padded) and the squared norm of every row, which is what lets dino_h1_fwd_bwd take the first layer without
+        forming J_hat (include/dino_b200.h: DinoBatch.ld_J, J_row_sqnorm).  The one case where a dataset
+        built by from_device is copied: a row length that is not a multiple of 4 floats (d_M = 4225)."""
+        import torch
+        if jac_mode != _lib.JAC_FULL or self.J is None or self.J.dim() != 3:
+            return
+        d_in = int(self.J.shape[2])
+        if d_in < int(os.environ.get("DINO_B200_IMPLICIT_MIN", "1024")) or os.environ.get("DINO_B200_NO_IMPLICIT0"):
+            return
+        ld = (d_in + 3) & ~3
+        if ld != d_in:
+            Jp = torch.zeros(self.J.shape[0], self.J.shape[1], ld, dtype=torch.float32, device=self.J.device)
+            Jp[:, :, :d_in].copy_(self.J)
+            self.J = Jp
+        self.ld_J = ld
+        rows = self.n * int(self.J.shape[1])
+        self.jrn2 = torch.empty(rows, dtype=torch.float32, device=self.J.device)
+        _lib.check(_lib.load().dino_sample_sqnorms(C.c_void_p(self.J.data_ptr()), rows, ld, C.c_void_p(self.jrn2.data_ptr()),
+                                                   _stream()), "dino_sample_sqnorms")
 
     def batch(self, idx_ptr: Optional[int], row_offset: int = 0) -> _lib.DinoBatch:
         """DinoBatch for rows addressed by a device int32 index array (idx_ptr) or, when idx_ptr is
@@ -328,8 +357,12 @@ class DeviceDataset:
             if idx_ptr is None and row_offset:
                 return t.data_ptr() + row_offset * t[0].numel() * 4 if t.dim() > 1 else t.data_ptr() + row_offset * 4
             return t.data_ptr()
+        jrn2 = None
+        if self.jrn2 is not None:
+            jrn2 = self.jrn2.data_ptr() + (row_offset * int(self.J.shape[1]) * 4 if idx_ptr is None and row_offset else 0)
         return _lib.DinoBatch(p(self.m), p(self.q), p(self.J), p(self.qn2), p(self.jn2), idx_ptr,
-                              p(self.U), p(self.V), None if self.seed is None else self.seed.data_ptr())
+                              p(self.U), p(self.V), None if self.seed is None else self.seed.data_ptr(),
+                              self.ld_J, jrn2, self.n)
 
 
 class TrainEngine:

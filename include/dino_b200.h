@@ -71,6 +71,12 @@ typedef struct {
   const float* U;    /* SKETCHED: [n, d_out, k] (jacobianConstruction.py:115) else NULL */
   const float* V;    /* SKETCHED: [n, d_in, k]  (jacobianConstruction.py:116) else NULL */
   const float* seed; /* OUT_REDUCED: Phi^T [seed_dim, d_out] (jacobianConstruction.py:181) else NULL */
+  /* optional (zero / NULL: dense rows, not given).  With all three of ld_J % 4 == 0, J_row_sqnorm and a plan whose first
+   * layer qualifies (FULL Jacobian of an unreduced input, d_in >= 1024, tensor-core precision), dino_h1_fwd_bwd never
+   * forms J_hat [B, d_out, d_in]: see DESIGN.md, "first layer without its Jacobian". */
+  int64_t ld_J;                /* row pitch of J in floats (>= d_in; padding columns must hold zeros) */
+  const float* J_row_sqnorm;   /* [n * seed_dim] squared norm of every row of J (dino_sample_sqnorms over the rows) */
+  int64_t n_samples;           /* rows n of the dataset arrays idx addresses (0: unknown) */
 } DinoBatch;
 
 /* statistics a step accumulates (+=) into the caller's float[DINO_STAT_SLOTS] device array;

@@ -185,3 +185,43 @@ def test_two_plans_on_two_devices_in_one_process(cuda_device):
     torch.cuda.set_device(0)
     for key, losses in results.items():
         assert np.isfinite(losses).all() and max(losses) - min(losses) < 1e-5 * abs(losses[0]), (key, losses)
+
+
+@pytest.mark.parametrize("precision", ["fp32x3", "tf32"])
+def test_first_layer_without_its_jacobian(cuda_device, precision, monkeypatch):
+    """Full Jacobian over an unreduced input (d_in >= 1024): the step that never forms J_hat (csrc/plan.cu,
+    run_implicit_layer0: the target gathered per sample by TMA, J W and J^T Q instead of G W and G^T Q) against the
+    oracle and against the explicit path of the same library, over shuffled minibatches with a ragged last one: loss,
+    every metric of the history (the per-row Jacobian accuracy comes from row dot products there) and the weights."""
+    tol_j, tol_g = BARS[precision]
+    arch = S.Arch("generic_dense", 1030, 72, hidden=[40, 36])        # 72 rows per sample: one partial 128-row tile; 1030 % 4 != 0
+    n, B = 13, 5
+    data, tw = S.make_dataset(arch, n, 77)
+    w = S.student_weights(arch, 78, tw, bias_noise=0.1)
+    rng = np.random.default_rng(3)
+    perms = [rng.permutation(n) for _ in range(2)]
+
+    def run(explicit):
+        if explicit:
+            monkeypatch.setenv("DINO_B200_NO_IMPLICIT0", "1")
+        else:
+            monkeypatch.delenv("DINO_B200_NO_IMPLICIT0", raising=False)
+        model = S.build_model(arch, w, precision=precision)
+        _compile(model, SGD(0.5))
+        hist = model.fit([data["m"]], [data["q"], data["J"]], epochs=2, batch_size=B, perms=perms,
+                         validation_data=([data["m"]], [data["q"], data["J"]]))
+        return hist.history, {l.name: l.get_weights() for l in model.layers}
+
+    h_imp, w_imp = run(False)
+    h_exp, w_exp = run(True)
+    net = H.oracle_net(arch, w)
+    O.fit(net, H.oracle_batch(data), epochs=2, batch_size=B, lr=0.5, opt="sgd", perms=perms, vectorised=True)
+    ow = net.get_weights()
+    for k in h_exp:
+        if k.startswith("val_"):
+            continue       # evaluation always forms J_hat
+        assert np.allclose(h_imp[k], h_exp[k], rtol=20 * tol_j, atol=2 * tol_j), (k, h_imp[k], h_exp[k])
+    for name, ws0 in w.items():
+        for i, c in enumerate(ws0):
+            assert H.rel_err(w_imp[name][i] - c, w_exp[name][i] - c) < 2 * tol_g, name
+            assert H.rel_err(w_imp[name][i] - c, ow[name][i] - c) < 2 * tol_g, name
