@@ -120,6 +120,8 @@ cudaError_t launch_loss_q(const float* qhat, long long ld_qh, const float* q, co
 cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, long long ld_jt, const float* jn2,
                           const int* idx, int B, int sdim, int n, float coef, int write_grad,
                           float* stats, cudaStream_t st);     // ld_jt: row pitch of the target (0: n)
+cudaError_t launch_bias_act(float* z, long long ld, const float* bias, int B, int n, int act, float* s_out, long long ld_s,
+                            const float* add_post, long long ld_apo, cudaStream_t st);
 cudaError_t launch_implicit_prep(const float* Q, long long ld, int n, const float* jn2, const int* idx, int B, int sdim, float coef,
                                  float* Qc, float* negc, cudaStream_t st);
 cudaError_t launch_implicit_loss(const float* ddot, const float* tdot, const float* jn2, const float* jrn2, const int* idx, int B,

@@ -202,6 +202,33 @@ cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, long lo
   return cudaGetLastError();
 }
 
+// z = act(acc + bias) [+ add_post], s_out = act'(pre-activation): the epilogue of a network GEMM whose reduction was split over
+// CTAs (plan.cu: small-batch layers with a long reduction), in place on the accumulated sums
+__global__ void __launch_bounds__(256) bias_act_kernel(float* __restrict__ z, long long ld, const float* __restrict__ bias, int B, int n,
+                                                       int act, float* __restrict__ s_out, long long ld_s,
+                                                       const float* __restrict__ add_post, long long ld_apo) {
+  const long long total = (long long)B * n;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int b = (int)(i / n), c = (int)(i % n);
+    float v = z[(long long)b * ld + c];
+    if (bias) v += __ldg(bias + c);
+    if (act) {
+      const float e = expf(-fabsf(v)), r1 = 1.f / (1.f + e);
+      if (s_out) s_out[(long long)b * ld_s + c] = v >= 0.f ? r1 : e * r1;
+      v = fmaxf(v, 0.f) + log1pf(e);
+    }
+    if (add_post) v += add_post[(long long)b * ld_apo + c];
+    z[(long long)b * ld + c] = v;
+  }
+}
+cudaError_t launch_bias_act(float* z, long long ld, const float* bias, int B, int n, int act, float* s_out, long long ld_s,
+                            const float* add_post, long long ld_apo, cudaStream_t st) {
+  const long long total = (long long)B * n;
+  if (total <= 0) return cudaSuccess;
+  bias_act_kernel<<<min(cdiv(total, 256), 148 * 8), 256, 0, st>>>(z, ld, bias, B, n, act, s_out, ld_s, add_post, ld_apo);
+  return cudaGetLastError();
+}
+
 // ---- the first layer of a full-Jacobian network without its Jacobian (plan.cu: run_implicit_layer0) -----------------
 // Qc[row, :] = c_b Q[row, :] and negc[b, :] = -c_b with c_b = coef / ||J_b||^2: the per-sample weight of the H1 term
 __global__ void __launch_bounds__(256) implicit_prep_kernel(const float* __restrict__ Q, long long ld, int n, const float* __restrict__ jn2,

@@ -102,9 +102,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           m0 = (mt % ep.a_tps) * TC_BM;              // row inside the sample
           samp = ep.a_idx ? ep.a_idx[b] : b;
         }
+        const int PF = ep.pf;                        // gathered A streams from HBM: L2 prefetch this many K blocks ahead
+        if (ep.a_rows > 0)
+          for (int kb = 0; kb < min(PF, nkb); ++kb) tma_prefetch_3d(&tma_a, kb * BK, m0, samp);
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int st = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
+          if (ep.a_rows > 0 && kb + PF < nkb) tma_prefetch_3d(&tma_a, (kb + PF) * BK, m0, samp);
           mbar_wait(empty_bar + st, ph ^ 1);
           mbar_expect_tx(full_bar + st, RAW_BYTES);
           uint8_t* sa = smem + st * STAGE_BYTES;
@@ -319,6 +323,8 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   TcEpilogue ep;
   ep.a_rows = op.a_rows; ep.a_tps = op.a_rows > 0 ? (op.a_rows + TC_BM - 1) / TC_BM : 0; ep.a_idx = op.a_idx;
   ep.rowdot = op.rowdot; ep.pre_first = op.pre_first;
+  static const int pf = getenv("DINO_TC_PF") ? atoi(getenv("DINO_TC_PF")) : 0;      // read once per process
+  ep.pf = pf;
   ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.C = op.C; ep.ldc = op.ldc; ep.sdim = op.sdim > 0 ? op.sdim : 1;
   ep.scale = op.scale; ep.ld_sc = op.ld_sc; ep.add_pre = op.add_pre; ep.ld_ap = op.ld_ap;
   ep.add_post = op.add_post; ep.ld_apo = op.ld_apo; ep.bias = op.bias; ep.act = op.act;

@@ -395,6 +395,34 @@ static int gemm_simt_only(const DinoPlan* p, const GemmOp& op, cudaStream_t st) 
   return 0;
 }
 
+// One GEMM of the network itself (M = minibatch rows) on the tensor-core plans.  Three regimes:
+//   tiny (a few MFLOP: the width-100 layers)            -> the FFMA engine: one short launch beats the tcgen05 pipeline's set-up
+//   few row tiles and a long reduction (M <= 256, K >= 512) -> the reduction is split over CTAs (the weight-gradient kernel
+//       with both factors K-major, fp32 atomics into a cleared block), bias / activation / residual in a second pass:
+//       a [256, 1024] x [1024, 1024] layer has 16 output tiles for 148 SMs, a [128, 4225] x [4225, 100] one has ONE
+//   otherwise                                           -> gemm_tc_kernel with its fused epilogue
+// op describes the fused form (K-major A and B, bias / act / s_out / add_post).
+static int mlp_gemm(DinoPlan* p, const GemmOp& op, const GemmOp& op_simt, cudaStream_t st) {
+  const double flops = 2.0 * op.M * op.N * op.K;
+  if (flops < 2.0e7) return gemm_simt_only(p, op_simt, st);
+  if (op.M <= 256 && op.K >= 512 && op.C && (op.ldc & 3) == 0 && !op.add_pre && !op.scale) {
+    GemmGroup g;
+    g.n = 1;
+    GemmOp& w = g.ops[0];
+    w = gemm_op_zero();
+    w.A = op.A; w.a_sm = op.a_sm; w.a_sk = 1; w.B = op.B; w.b_sn = op.b_sn; w.b_sk = 1;
+    w.M = op.M; w.N = op.N; w.K = op.K; w.C = op.C; w.ldc = op.ldc; w.atomic_c = 1;
+    if (wgrad_tc_supported(w)) {
+      DINO_CUDA(cudaMemsetAsync(op.C, 0, ((size_t)(op.M - 1) * op.ldc + op.N) * sizeof(float), st));
+      DINO_LAUNCH(launch_wgrad_tc(g, 1, p->num_sms, st));
+      if (op.bias || op.act || op.add_post)
+        DINO_LAUNCH(launch_bias_act(op.C, op.ldc, op.bias, op.M, op.N, op.act, op.s_out, op.ld_s, op.add_post, op.ld_apo, st));
+      return 0;
+    }
+  }
+  return gemm(p, op, st, true);
+}
+
 static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b, int B, cudaStream_t st) {
   float* ws = p->ws;
   if (p->mlp_fused) {
@@ -412,8 +440,7 @@ static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b,
     const LayerPlan& lp = p->layers[l];
     GemmOp op = gemm_op_zero();
     op.A = zin; op.a_sm = ld_zin; op.a_sk = 1;
-    if (tc_mlp) { op.B = ws + lp.wtp_off; op.b_sk = 1; op.b_sn = lp.ld_wtp; }   // K-major W^T for the tcgen05 engine
-    else { op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1; }
+    op.B = params + lp.koff; op.b_sk = lp.n_out; op.b_sn = 1;
     op.M = B; op.N = lp.n_out; op.K = lp.n_in;
     op.C = ws + lp.z_off; op.ldc = lp.ld_out;
     op.bias = lp.has_bias ? params + lp.boff : nullptr;
@@ -424,7 +451,11 @@ static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b,
       op.add_post = j == 0 ? ws + p->off_z0 : ws + p->layers[j - 1].z_off;
       op.ld_apo = j == 0 ? p->ld_in : p->layers[j - 1].ld_out;
     }
-    if (tc_mlp ? gemm(p, op, st, true) : gemm_simt_only(p, op, st)) return 1;
+    if (tc_mlp) {
+      GemmOp opt = op;
+      opt.B = ws + lp.wtp_off; opt.b_sk = 1; opt.b_sn = lp.ld_wtp;             // K-major W^T for the tcgen05 engine
+      if (mlp_gemm(p, opt, op, st)) return 1;
+    } else if (gemm_simt_only(p, op, st)) return 1;
     zin = ws + lp.z_off; ld_zin = lp.ld_out;
   }
   return 0;
@@ -823,12 +854,15 @@ static int run_mlp_backward(DinoPlan* p, const float* params, int B, float* grad
     if (l > lowest_trainable) {   // dz_l = da_l W_l^T [+ dz above the residual block that starts here]
       GemmOp op = gemm_op_zero();
       op.A = da; op.a_sm = p->ld_dz; op.a_sk = 1;
-      if (tc_mlp) { op.B = ws + lp.wp_off; op.b_sk = 1; op.b_sn = lp.ld_wp; }     // 16-byte-pitch copy of W_l
-      else { op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out; }
+      op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out;
       op.M = B; op.N = lp.n_in; op.K = lp.n_out;
       op.C = dz_ptr(l); op.ldc = p->ld_dz;
       if (lp.lands_skip >= 0) { op.add_post = dz_ptr(lp.lands_skip + 1); op.ld_apo = p->ld_dz; }
-      if (tc_mlp ? gemm(p, op, st, true) : gemm_simt_only(p, op, st)) return 1;
+      if (tc_mlp) {
+        GemmOp opt = op;
+        opt.B = ws + lp.wp_off; opt.b_sk = 1; opt.b_sn = lp.ld_wp;               // 16-byte-pitch copy of W_l
+        if (mlp_gemm(p, opt, op, st)) return 1;
+      } else if (gemm_simt_only(p, op, st)) return 1;
     }
   }
   return 0;

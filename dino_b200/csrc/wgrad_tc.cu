@@ -25,7 +25,8 @@ constexpr int WG_NCONV = 8;                    // fp32x3: converter warps
 constexpr int WG_X3_ROWS = 2048;                // fp32x3: longest reduction one TMEM accumulator takes (256 truncating additions, two chain contractions' worth; 1024 cost 20 % more time in per-CTA set-up and drain)
 
 struct WgOp {
-  float* C;                 // gradient block [n_in, n_out], ldc = n_out
+  float* C;                 // gradient block [n_in, n_out]
+  long long ldc;            // its row pitch (n_out for a block of the parameter arena)
   int n_in, n_out, rows;    // rows = reduction length
   int z_start;              // first blockIdx.x of this op
   int chunks_per_cta;       // reduction chunks (of BK rows) per CTA
@@ -35,6 +36,7 @@ struct WgOp {
   // do not cross samples, x_cps of them per sample (the last one zero-filled past the sample's rows)
   const int* x_idx; int x_rows, x_cps;
   float alpha;              // C += alpha * X^T Y
+  int pf;                   // L2 prefetch distance (chunks) of the gathered X
 };
 struct WgGroup {
   int n;
@@ -100,6 +102,12 @@ __global__ void __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1) wgrad_tc
           if (op.x_rows > 0) {
             const int b = (c_begin + c) / op.x_cps, r0 = ((c_begin + c) % op.x_cps) * BK;
             const int samp = op.x_idx ? op.x_idx[b] : b;
+            const int PF = op.pf;                    // X streams from HBM: L2 prefetch this many chunks ahead
+            for (int cp = (c == 0 ? 1 : PF); PF > 0 && cp <= PF && c + cp < nchunks; ++cp) {
+              const int bp = (c_begin + c + cp) / op.x_cps, rp = ((c_begin + c + cp) % op.x_cps) * BK;
+              const int sp = op.x_idx ? op.x_idx[bp] : bp;
+              for (int gI = 0; gI < ga; ++gI) tma_prefetch_3d(mx, m0 + 32 * gI, rp, sp);
+            }
             mbar_expect_tx(full_bar + st, (uint32_t)((ga + gb) * GROUP_BYTES));
             for (int gI = 0; gI < ga; ++gI) tma_load_3d(sx + gI * GROUP_BYTES, mx, m0 + 32 * gI, r0, samp, full_bar + st);
             // (Y rows past the sample's last meet zero-filled X rows)
@@ -158,7 +166,7 @@ __global__ void __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1) wgrad_tc
       tc_fence_after();
       const int q = warp & 3;
       const int m = m0 + q * 32 + lane;
-      const bool vec = (op.n_out & 3) == 0 && (reinterpret_cast<uintptr_t>(op.C) & 15) == 0;
+      const bool vec = (op.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(op.C) & 15) == 0;
       for (int c0 = 0; c0 < ncols; c0 += 32) {
         float v[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
@@ -174,7 +182,7 @@ __global__ void __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1) wgrad_tc
           for (int j = 0; j < 32; ++j) v[j] *= op.alpha;
         }
         if (m < op.n_in) {
-          float* crow = op.C + (long long)m * op.n_out + n0 + c0;
+          float* crow = op.C + (long long)m * op.ldc + n0 + c0;
           if (vec && c0 + 32 <= ncols) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4)
@@ -372,7 +380,7 @@ bool wgrad_tc_supported(const GemmOp& op) {
   if (!kmaj && ((op.a_sk & 3) || (op.b_sk & 3))) return false;
   if ((reinterpret_cast<uintptr_t>(op.A) & 15) || (reinterpret_cast<uintptr_t>(op.B) & 15)) return false;
   if (op.a_rows > 0 && (!mnmaj || op.K % op.a_rows || (op.a_ld2 & 3) || op.a_nsamp < 1)) return false;
-  return op.ldc == op.N;
+  return op.ldc >= op.N;
 }
 
 template <int TN, int BK, int STAGES, bool SPLIT>
@@ -389,8 +397,10 @@ static cudaError_t launch_wg(const GemmGroup& gg, int num_sms, cudaStream_t st) 
   for (int i = 0; i < gg.n; ++i) {
     const GemmOp& o = gg.ops[i];
     WgOp& w = g.op[i];
-    w.C = o.C; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
+    w.C = o.C; w.ldc = o.ldc; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
     w.x_idx = o.a_idx; w.x_rows = o.a_rows; w.x_cps = o.a_rows > 0 ? (o.a_rows + BK - 1) / BK : 0; w.alpha = o.alpha;
+    static const int wpf = getenv("DINO_WG_PF") ? atoi(getenv("DINO_WG_PF")) : 0;     // read once per process
+    w.pf = wpf;
     const int chunks = o.a_rows > 0 ? (o.K / o.a_rows) * w.x_cps : (o.K + BK - 1) / BK;
     const int m_tiles = (o.M + 127) / 128;
     w.n_tiles = (o.N + TN - 1) / TN;
@@ -448,8 +458,8 @@ static cudaError_t launch_wg2(const GemmGroup& gg, int num_sms, cudaStream_t st)
   for (int i = 0; i < gg.n; ++i) {
     const GemmOp& o = gg.ops[i];
     WgOp& w = g.op[i];
-    w.C = o.C; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
-    w.x_idx = nullptr; w.x_rows = 0; w.x_cps = 0; w.alpha = 1.f;      // (gathered / scaled ops never come here)
+    w.C = o.C; w.ldc = o.N; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
+    w.x_idx = nullptr; w.x_rows = 0; w.x_cps = 0; w.alpha = 1.f; w.pf = 0;      // (gathered / scaled ops never come here)
     const int chunks = (o.K + BK - 1) / BK;
     w.n_tiles = (o.N + 255) / 256;
     const int tiles = ((o.M + 255) / 256) * w.n_tiles;
@@ -487,7 +497,7 @@ cudaError_t launch_wgrad_tc(const GemmGroup& gg, int split, int num_sms, cudaStr
     for (int i = 0; i < gg.n; ++i) {
       const GemmOp& o = gg.ops[i];
       const bool mn = !(o.a_sk == 1 && o.b_sk == 1);
-      if (mn && o.a_rows == 0 && o.alpha == 1.f && o.M > 128 && o.N > 128 && o.K >= 2048) big.ops[big.n++] = o; else rest.ops[rest.n++] = o;
+      if (mn && o.a_rows == 0 && o.alpha == 1.f && o.ldc == o.N && o.M > 128 && o.N > 128 && o.K >= 2048) big.ops[big.n++] = o; else rest.ops[rest.n++] = o;
     }
     if (big.n > 0) {
       cudaError_t e = split ? launch_wg2<32, 3, true>(big, num_sms, st) : launch_wg2<64, 3, false>(big, num_sms, st);
