@@ -111,7 +111,8 @@ cudaError_t launch_gather_rows(const float* src, const int* idx, int rows, int c
 cudaError_t launch_fill_identity(float* dst, int n, long long ld, cudaStream_t st);
 cudaError_t launch_scale_seed(const float* seed, long long seed_sample_stride, long long ld_seed,
                               const float* s, long long ld_s, int B, int sdim, int n,
-                              float* out, long long ld_out, cudaStream_t st);
+                              float* out, long long ld_out, cudaStream_t st, int round_out = 0);
+cudaError_t launch_identity_seed_wgrad(const float* dR, long long ld, int B, int sdim, int n_in, float* dW, cudaStream_t st);
 cudaError_t launch_transpose_batched(const float* src, int B, int rows, int cols, float* dst,
                                      long long ld_dst, const int* idx, cudaStream_t st);
 cudaError_t launch_loss_q(const float* qhat, long long ld_qh, const float* q, const float* qn2,

@@ -53,7 +53,7 @@ cudaError_t launch_fill_identity(float* dst, int n, long long ld, cudaStream_t s
 // out[(b*sdim+i), n] = seed[b*sample_stride + i*ld_seed + n] * s[b, n]
 __global__ void scale_seed_kernel(const float* __restrict__ seed, long long sample_stride, long long ld_seed,
                                   const float* __restrict__ s, long long ld_s, int B, int sdim, int n,
-                                  float* __restrict__ out, long long ld_out) {
+                                  float* __restrict__ out, long long ld_out, int round_out) {
   const long long total = (long long)B * sdim * n;
   for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
        e += (long long)gridDim.x * blockDim.x) {
@@ -63,16 +63,16 @@ __global__ void scale_seed_kernel(const float* __restrict__ seed, long long samp
     const long long b = row / sdim;
     float v = __ldg(seed + b * sample_stride + i * ld_seed + c);
     if (s) v *= s[b * ld_s + c];
-    out[row * ld_out + c] = v;
+    out[row * ld_out + c] = round_out ? round_tf32_f(v) : v;
   }
 }
 cudaError_t launch_scale_seed(const float* seed, long long seed_sample_stride, long long ld_seed,
                               const float* s, long long ld_s, int B, int sdim, int n, float* out,
-                              long long ld_out, cudaStream_t st) {
+                              long long ld_out, cudaStream_t st, int round_out) {
   const long long total = (long long)B * sdim * n;
   if (total <= 0) return cudaSuccess;
   scale_seed_kernel<<<min(cdiv(total, 256), 148 * 8), 256, 0, st>>>(seed, seed_sample_stride, ld_seed, s, ld_s,
-                                                                  B, sdim, n, out, ld_out);
+                                                                  B, sdim, n, out, ld_out, round_out);
   return cudaGetLastError();
 }
 
@@ -199,6 +199,36 @@ cudaError_t launch_loss_j(float* jhat, long long ld_jh, const float* jt, long lo
   if (rows <= 0) return cudaSuccess;
   loss_j_kernel<<<min(cdiv(rows, 8), 148 * 16), 256, 0, st>>>(jhat, ld_jh, jt, jn2, idx, B, sdim, n, ld_jt > 0 ? ld_jt : n, coef,
                                                             write_grad, stats);
+  return cudaGetLastError();
+}
+
+// Weight gradient of a linear top layer under the identity seed (FULL Jacobian): the chain state above it is I for every
+// sample, so dW[k, i] += sum_b dR[b*s + i, k]: a sum over samples, no contraction
+__global__ void __launch_bounds__(256) identity_seed_wgrad_kernel(const float* __restrict__ dR, long long ld, int B, int sdim, int n_in,
+                                                                  float* __restrict__ dW) {
+  __shared__ float tile[32][33];
+  const int i0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;     // 8 rows of 32
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int b = blockIdx.z; b < B; b += gridDim.z)
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + ty + 8 * u, k = k0 + tx;
+      if (i < sdim && k < n_in) acc[u] += dR[((long long)b * sdim + i) * ld + k];
+    }
+#pragma unroll
+  for (int u = 0; u < 4; ++u) tile[ty + 8 * u][tx] = acc[u];
+  __syncthreads();
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int k = k0 + ty + 8 * u, i = i0 + tx;
+    if (i < sdim && k < n_in) atomicAdd(dW + (long long)k * sdim + i, tile[tx][ty + 8 * u]);
+  }
+}
+cudaError_t launch_identity_seed_wgrad(const float* dR, long long ld, int B, int sdim, int n_in, float* dW, cudaStream_t st) {
+  if (B <= 0) return cudaSuccess;
+  const int gz = B < 8 ? B : 8;
+  identity_seed_wgrad_kernel<<<dim3(cdiv(sdim, 32), cdiv(n_in, 32), gz), 256, 0, st>>>(dR, ld, B, sdim, n_in, dW);
   return cudaGetLastError();
 }
 

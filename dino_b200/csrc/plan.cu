@@ -81,6 +81,8 @@ struct DinoPlan {
   long long n_params;
   bool seed_shared;          // FULL / OUT_REDUCED
   bool top_materialised;     // Q_{L-1} stored in the workspace (else it is the shared seed itself)
+  bool top_identity;         // tensor-core plans, FULL Jacobian, linear top layer: identity seed, never stored: the first chain
+                             // step is W_L^T (* sigma') per sample, the top weight gradient a sum over samples
   // workspace offsets (floats)
   long long off_ident, off_z0, off_r0, off_sk, off_dz[3], off_da, off_rs_begin, rs_floats;
   long long ld_in, ld_dz, ld_ident;
@@ -178,7 +180,11 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
   if (p->jac_mode == DINO_JAC_SKETCHED && p->s > 128) { delete p; return fail("dino_plan_create: sketch rank > 128"); }
   p->seed_shared = (p->jac_mode == DINO_JAC_FULL || p->jac_mode == DINO_JAC_OUT_REDUCED);
   const LayerPlan& last = p->layers[p->L - 1];
-  p->top_materialised = p->jac_mode != DINO_JAC_NONE &&
+  bool wide = p->d_in > 128;          // (narrow networks go to the fused chain kernel, which has its own top-layer handling)
+  for (auto& lp : p->layers) wide = wide || lp.n_out > 128;
+  p->top_identity = p->tc && wide && p->jac_mode == DINO_JAC_FULL && last.act == DINO_ACT_LINEAR && last.skip_from < 0 &&
+                    last.lands_skip < 0 && getenv("DINO_B200_NO_TOP_IDENTITY") == nullptr;
+  p->top_materialised = p->jac_mode != DINO_JAC_NONE && !p->top_identity &&
                         (!p->seed_shared || last.act == DINO_ACT_SOFTPLUS || last.skip_from >= 0 ||
                          p->tc /* TMA-addressable operand for the tensor-core weight gradient */);
 
@@ -495,6 +501,15 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
   if (tc && (p->mlp_fused || p->chain_fused)) DINO_LAUNCH(launch_prep_weights(params, ws, p->prep, p->max_in, p->max_out, st));
   for (int l = L - 1; l >= (skip_first ? 1 : 0); --l) {
     const LayerPlan& lp = p->layers[l];
+    if (l == L - 1 && p->top_identity) {
+      // I * W_L^T: row i of every sample is row i of the staged W_L^T, times sigma' of the layer below
+      const LayerPlan* below = l > 0 ? &p->layers[l - 1] : nullptr;
+      const bool sc = below && below->act == DINO_ACT_SOFTPLUS;
+      DINO_LAUNCH(launch_scale_seed(ws + lp.wtp_off, 0, lp.ld_wtp, sc ? ws + below->sg_off : nullptr, sc ? below->ld_out : 0, B, s,
+                                    lp.n_in, below ? ws + below->q_off : ws + p->off_r0, below ? below->ld_out : p->ld_in, st,
+                                    (below && !p->split) ? 1 : 0));
+      continue;
+    }
     GemmOp op = gemm_op_zero();
     if (l == L - 1) { op.A = top.ptr; op.a_sm = top.ld; op.a_mod = top.mod; }
     else { op.A = ws + lp.q_off; op.a_sm = lp.ld_out; }
@@ -754,7 +769,9 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
     const float* q; long long ldq; int qmod;
     if (l == L - 1) { q = top.ptr; ldq = top.ld; qmod = top.mod; }
     else { q = ws + lp.q_off; ldq = lp.ld_out; qmod = 0; }
-    if (lp.trainable) {     // dW_l += dR_l^T Q_l   (reduction over all B*s chain rows, split-K)
+    if (lp.trainable && l == L - 1 && p->top_identity) {
+      DINO_LAUNCH(launch_identity_seed_wgrad(dr_ptr(l), dr_ld(l), B, s, lp.n_in, grad + lp.koff, st));
+    } else if (lp.trainable) {     // dW_l += dR_l^T Q_l   (reduction over all B*s chain rows, split-K)
       GemmOp op = gemm_op_zero();
       op.A = dr_ptr(l); op.a_sm = 1; op.a_sk = dr_ld(l);
       op.B = q; op.b_sk = ldq; op.b_sn = 1; op.b_kmod = qmod;
