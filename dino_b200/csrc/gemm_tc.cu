@@ -31,6 +31,10 @@ namespace dino {
 using namespace tc;
 
 constexpr int TC_BM = 128;
+// A gathered per sample, sample length a multiple of g = 16, 32, 64: a 128-row tile of consecutive minibatch rows is
+// loaded as up to 128 / g boxes, each inside one sample; m[j] has a box of (j + 1) * g rows.  (Otherwise row tiles stop at
+// sample ends and the last one of a sample is part empty: 4 tiles for 400 rows.)
+struct TcGatherMaps { CUtensorMap m[8]; };
 constexpr int TC_NCONV = 8;     // fp32x3: converter warps (a stage of 32-48 KB per 768 MMA cycles: four warps could not keep up)
 
 // EPI: 0 plain store; 1 chain terms (rowsum / add_pre / scale / add_post / rounding); 2 network terms (bias / softplus +
@@ -39,7 +43,8 @@ constexpr int TC_NCONV = 8;     // fp32x3: converter warps (a stage of 32-48 KB 
 // main loop is short against their epilogue (tf32; fp32x3 with a short K)
 template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI, int NCONV>
 __global__ void __launch_bounds__((2 + NEPI + (SPLIT ? NCONV : 0)) * 32, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep,
+               const __grid_constant__ TcGatherMaps gmaps) {
   constexpr int A_BYTES = TC_BM * BK * 4, B_BYTES = BN * BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
   constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;           // columns of one accumulator
@@ -68,7 +73,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   // persistent: this CTA walks the output tiles blockIdx.x, blockIdx.x + gridDim.x, ... (column tile fastest)
   // (A gathered per sample: row tiles do not cross samples, ep.a_tps of them per sample)
   const int tiles_n = (ep.N + BN - 1) / BN;
-  const int n_tiles = tiles_n * (ep.a_rows > 0 ? (ep.M / ep.a_rows) * ep.a_tps : (ep.M + TC_BM - 1) / TC_BM);
+  const bool per_sample = ep.a_rows > 0 && ep.a_gran == 0;
+  const int n_tiles = tiles_n * (per_sample ? (ep.M / ep.a_rows) * ep.a_tps : (ep.M + TC_BM - 1) / TC_BM);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
@@ -97,23 +103,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int mt = tile / tiles_n, n0 = (tile % tiles_n) * BN;
         int m0 = mt * TC_BM, samp = 0;
-        if (ep.a_rows > 0) {
+        // gathered A: the boxes of this tile (rows inside a sample, sample number, height index)
+        int nbox = 0, box_r[8], box_s[8], box_h[8], rows_loaded = TC_BM;
+        if (per_sample) {
           const int b = mt / ep.a_tps;
           m0 = (mt % ep.a_tps) * TC_BM;              // row inside the sample
           samp = ep.a_idx ? ep.a_idx[b] : b;
+        } else if (ep.a_rows > 0) {
+          rows_loaded = min(TC_BM, ep.M - m0);
+          for (int row = m0, left = rows_loaded; left > 0;) {
+            const int b = row / ep.a_rows, r = row % ep.a_rows, h = min(left, ep.a_rows - r);
+            box_r[nbox] = r; box_s[nbox] = ep.a_idx ? ep.a_idx[b] : b; box_h[nbox] = h; ++nbox;
+            row += h; left -= h;
+          }
         }
-        const int PF = ep.pf;                        // gathered A streams from HBM: L2 prefetch this many K blocks ahead
-        if (ep.a_rows > 0)
-          for (int kb = 0; kb < min(PF, nkb); ++kb) tma_prefetch_3d(&tma_a, kb * BK, m0, samp);
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int st = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
-          if (ep.a_rows > 0 && kb + PF < nkb) tma_prefetch_3d(&tma_a, (kb + PF) * BK, m0, samp);
           mbar_wait(empty_bar + st, ph ^ 1);
-          mbar_expect_tx(full_bar + st, RAW_BYTES);
           uint8_t* sa = smem + st * STAGE_BYTES;
-          if (ep.a_rows > 0) tma_load_3d(sa, &tma_a, kb * BK, m0, samp, full_bar + st);
-          else tma_load_2d(sa, &tma_a, kb * BK, m0, full_bar + st);
+          if (nbox > 0) {
+            mbar_expect_tx(full_bar + st, (uint32_t)(rows_loaded * BK * 4 + B_BYTES));
+            int off = 0;
+            for (int j = 0; j < nbox; ++j) {
+              tma_load_3d(sa + off, &gmaps.m[box_h[j] / ep.a_gran - 1], kb * BK, box_r[j], box_s[j], full_bar + st);
+              off += box_h[j] * BK * 4;
+            }
+          } else {
+            mbar_expect_tx(full_bar + st, RAW_BYTES);
+            if (per_sample) tma_load_3d(sa, &tma_a, kb * BK, m0, samp, full_bar + st);
+            else tma_load_2d(sa, &tma_a, kb * BK, m0, full_bar + st);
+          }
           tma_load_2d(sa + A_BYTES, &tma_b, kb * BK, n0, full_bar + st);
         }
       }
@@ -182,7 +202,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++i) {
       const int mt = tile / tiles_n, n0 = (tile % tiles_n) * BN;
       int m0 = mt * TC_BM, m_lim = ep.M;
-      if (ep.a_rows > 0) {
+      if (ep.a_rows > 0 && ep.a_gran == 0) {
         const int b = mt / ep.a_tps, r0 = (mt % ep.a_tps) * TC_BM;
         m0 = b * ep.a_rows + r0;
         m_lim = b * ep.a_rows + min(ep.a_rows, r0 + TC_BM);
@@ -316,15 +336,21 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   CUtensorMap ma, mb;
   const int sw_in = BK == 32 ? (int)CU_TENSOR_MAP_SWIZZLE_128B : (int)CU_TENSOR_MAP_SWIZZLE_64B;
   // A[M,K] rows of a_sm floats; B operand is stored [N][K] (element (k,n) at n*b_sn + k)
+  TcGatherMaps gm;
+  int gran = 0;
   if (op.a_rows > 0) {
     if (!tc_make_map3(&ma, op.A, op.K, op.a_rows, op.a_nsamp, op.a_sm, op.a_ld2, BK, TC_BM, sw_in)) return cudaErrorInvalidValue;
+    for (int g = 64; g >= 16 && gran == 0; g >>= 1)
+      if (op.a_rows % g == 0) gran = g;
+    if (op.a_rows % TC_BM == 0) gran = 0;            // tiles never cross a sample: one box each
+    for (int j = 0; gran > 0 && j < TC_BM / gran; ++j)
+      if (!tc_make_map3(&gm.m[j], op.A, op.K, op.a_rows, op.a_nsamp, op.a_sm, op.a_ld2, BK, (unsigned)((j + 1) * gran), sw_in)) return cudaErrorInvalidValue;
   } else if (!tc_make_map(&ma, op.A, op.K, op.M, op.a_sm, BK, TC_BM, sw_in)) return cudaErrorInvalidValue;
   if (!tc_make_map(&mb, op.B, op.K, op.N, op.b_sn, BK, BN, sw_in)) return cudaErrorInvalidValue;
   TcEpilogue ep;
   ep.a_rows = op.a_rows; ep.a_tps = op.a_rows > 0 ? (op.a_rows + TC_BM - 1) / TC_BM : 0; ep.a_idx = op.a_idx;
   ep.rowdot = op.rowdot; ep.pre_first = op.pre_first;
-  static const int pf = getenv("DINO_TC_PF") ? atoi(getenv("DINO_TC_PF")) : 0;      // read once per process
-  ep.pf = pf;
+  ep.a_gran = gran;
   ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.C = op.C; ep.ldc = op.ldc; ep.sdim = op.sdim > 0 ? op.sdim : 1;
   ep.scale = op.scale; ep.ld_sc = op.ld_sc; ep.add_pre = op.add_pre; ep.ld_ap = op.ld_ap;
   ep.add_post = op.add_post; ep.ld_apo = op.ld_apo; ep.bias = op.bias; ep.act = op.act;
@@ -339,10 +365,10 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   if (e != cudaSuccess) return e;
   // persistent CTAs, one per SM: each walks its share of the 128 x BN output tiles
   const int num_sms = tc_current_num_sms();
-  const long long m_tiles = op.a_rows > 0 ? (long long)(op.M / op.a_rows) * ((op.a_rows + TC_BM - 1) / TC_BM) : (op.M + TC_BM - 1) / TC_BM;
+  const long long m_tiles = (op.a_rows > 0 && gran == 0) ? (long long)(op.M / op.a_rows) * ((op.a_rows + TC_BM - 1) / TC_BM) : (op.M + TC_BM - 1) / TC_BM;
   const long long n_tiles = (long long)((op.N + BN - 1) / BN) * m_tiles;
   const int grid = (int)(n_tiles < num_sms ? n_tiles : num_sms);
-  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI, NCONV><<<grid, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep);
+  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI, NCONV><<<grid, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep, gm);
   return cudaGetLastError();
 }
 

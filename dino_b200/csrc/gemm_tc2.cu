@@ -185,7 +185,7 @@ static cudaError_t launch_tc2(const GemmOp& op, cudaStream_t st) {
   ep.s_out = op.act ? op.s_out : nullptr; ep.ld_s = op.ld_s;
   ep.yref = op.rowsum ? op.yref : nullptr; ep.ld_y = op.ld_y; ep.rowsum = op.rowsum; ep.ld_rs = op.ld_rs;
   ep.round_tf32 = SPLIT ? 0 : op.round_tf32;
-  ep.a_rows = 0; ep.a_tps = 0; ep.a_idx = nullptr; ep.rowdot = nullptr; ep.pre_first = 0; ep.pf = 0;
+  ep.a_rows = 0; ep.a_tps = 0; ep.a_idx = nullptr; ep.rowdot = nullptr; ep.pre_first = 0; ep.a_gran = 0;
   constexpr int RAW = 2 * 128 * T2_BK * 4;
   constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + NEPI * 32 * 128 + 256 + 1024;
   static_assert(SMEM <= 232448, "shared memory budget of one CTA");

@@ -20,7 +20,7 @@ struct TcEpilogue {
   // per-row dot products with yref, add_pre ahead of the row sums
   int a_rows, a_tps; const int* a_idx;
   float* rowdot; int pre_first;
-  int pf;                    // L2 prefetch distance (K blocks) for the gathered A
+  int a_gran;                // > 0: consecutive-row tiles loaded as boxes of multiples of a_gran rows (gemm_tc.cu: TcGatherMaps)
 };
 
 // 4 floats of a row at column n (n % 4 == 0): vector load when the four lie inside N, guarded scalars at the edge

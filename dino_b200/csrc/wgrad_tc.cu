@@ -36,7 +36,6 @@ struct WgOp {
   // do not cross samples, x_cps of them per sample (the last one zero-filled past the sample's rows)
   const int* x_idx; int x_rows, x_cps;
   float alpha;              // C += alpha * X^T Y
-  int pf;                   // L2 prefetch distance (chunks) of the gathered X
 };
 struct WgGroup {
   int n;
@@ -102,12 +101,6 @@ __global__ void __launch_bounds__(SPLIT ? 192 + WG_NCONV * 32 : 192, 1) wgrad_tc
           if (op.x_rows > 0) {
             const int b = (c_begin + c) / op.x_cps, r0 = ((c_begin + c) % op.x_cps) * BK;
             const int samp = op.x_idx ? op.x_idx[b] : b;
-            const int PF = op.pf;                    // X streams from HBM: L2 prefetch this many chunks ahead
-            for (int cp = (c == 0 ? 1 : PF); PF > 0 && cp <= PF && c + cp < nchunks; ++cp) {
-              const int bp = (c_begin + c + cp) / op.x_cps, rp = ((c_begin + c + cp) % op.x_cps) * BK;
-              const int sp = op.x_idx ? op.x_idx[bp] : bp;
-              for (int gI = 0; gI < ga; ++gI) tma_prefetch_3d(mx, m0 + 32 * gI, rp, sp);
-            }
             mbar_expect_tx(full_bar + st, (uint32_t)((ga + gb) * GROUP_BYTES));
             for (int gI = 0; gI < ga; ++gI) tma_load_3d(sx + gI * GROUP_BYTES, mx, m0 + 32 * gI, r0, samp, full_bar + st);
             // (Y rows past the sample's last meet zero-filled X rows)
@@ -399,8 +392,6 @@ static cudaError_t launch_wg(const GemmGroup& gg, int num_sms, cudaStream_t st) 
     WgOp& w = g.op[i];
     w.C = o.C; w.ldc = o.ldc; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
     w.x_idx = o.a_idx; w.x_rows = o.a_rows; w.x_cps = o.a_rows > 0 ? (o.a_rows + BK - 1) / BK : 0; w.alpha = o.alpha;
-    static const int wpf = getenv("DINO_WG_PF") ? atoi(getenv("DINO_WG_PF")) : 0;     // read once per process
-    w.pf = wpf;
     const int chunks = o.a_rows > 0 ? (o.K / o.a_rows) * w.x_cps : (o.K + BK - 1) / BK;
     const int m_tiles = (o.M + 127) / 128;
     w.n_tiles = (o.N + TN - 1) / TN;
@@ -459,7 +450,7 @@ static cudaError_t launch_wg2(const GemmGroup& gg, int num_sms, cudaStream_t st)
     const GemmOp& o = gg.ops[i];
     WgOp& w = g.op[i];
     w.C = o.C; w.ldc = o.N; w.n_in = o.M; w.n_out = o.N; w.rows = o.K;
-    w.x_idx = nullptr; w.x_rows = 0; w.x_cps = 0; w.alpha = 1.f; w.pf = 0;      // (gathered / scaled ops never come here)
+    w.x_idx = nullptr; w.x_rows = 0; w.x_cps = 0; w.alpha = 1.f;      // (gathered / scaled ops never come here)
     const int chunks = (o.K + BK - 1) / BK;
     w.n_tiles = (o.N + 255) / 256;
     const int tiles = ((o.M + 255) / 256) * w.n_tiles;
