@@ -242,6 +242,9 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
       }
       p->mlp_fused = mlp_fused_supported(n);
     }
+    if (!p->mlp_fused)       // layer-by-layer backward: every softplus layer keeps its da, so that dW_l += z_l^T da_l can join the
+      for (auto& lp : p->layers)   // grouped weight-gradient launch at the end of the step
+        lp.da_off = lp.act == DINO_ACT_SOFTPLUS ? take(Bm * lp.ld_out) : -1;
   }
   p->prep.n = 0;
   p->max_in = p->max_out = 1;
@@ -403,7 +406,7 @@ static int gemm_simt_only(const DinoPlan* p, const GemmOp& op, cudaStream_t st) 
 
 // One GEMM of the network itself (M = minibatch rows) on the tensor-core plans.  Three regimes:
 //   tiny (a few MFLOP: the width-100 layers)            -> the FFMA engine: one short launch beats the tcgen05 pipeline's set-up
-//   few row tiles and a long reduction (M <= 256, K >= 512) -> the reduction is split over CTAs (the weight-gradient kernel
+//   few row tiles (M <= 256, K >= 128)                       -> the reduction is split over CTAs (the weight-gradient kernel
 //       with both factors K-major, fp32 atomics into a cleared block), bias / activation / residual in a second pass:
 //       a [256, 1024] x [1024, 1024] layer has 16 output tiles for 148 SMs, a [128, 4225] x [4225, 100] one has ONE
 //   otherwise                                           -> gemm_tc_kernel with its fused epilogue
@@ -411,7 +414,8 @@ static int gemm_simt_only(const DinoPlan* p, const GemmOp& op, cudaStream_t st) 
 static int mlp_gemm(DinoPlan* p, const GemmOp& op, const GemmOp& op_simt, cudaStream_t st) {
   const double flops = 2.0 * op.M * op.N * op.K;
   if (flops < 2.0e7) return gemm_simt_only(p, op_simt, st);
-  if (op.M <= 256 && op.K >= 512 && op.C && (op.ldc & 3) == 0 && !op.add_pre && !op.scale) {
+  static const int min_k = getenv("DINO_MLP_SPLIT_K") ? atoi(getenv("DINO_MLP_SPLIT_K")) : 128;     // read once per process
+  if (op.M <= 256 && op.K >= min_k && op.C && (op.ldc & 3) == 0 && !op.add_pre && !op.scale) {
     GemmGroup g;
     g.n = 1;
     GemmOp& w = g.ops[0];
@@ -848,11 +852,15 @@ static int run_mlp_backward(DinoPlan* p, const float* params, int B, float* grad
     const LayerPlan& lp = p->layers[l];
     const float* g = dz_ptr(l + 1);
     const float* da = g;
+    long long ld_da = p->ld_dz;
+    bool da_kept = false;           // da_l has a buffer of its own: its weight gradient can wait for the grouped launch
     float* dbias = (lp.trainable && lp.has_bias) ? grad + lp.boff : nullptr;
     if (lp.act == DINO_ACT_SOFTPLUS) {
+      float* dab = lp.da_off >= 0 ? ws + lp.da_off : ws + p->off_da;
+      if (lp.da_off >= 0) { ld_da = lp.ld_out; da_kept = true; }
       DINO_LAUNCH(launch_mlp_da(g, p->ld_dz, ws + lp.sg_off, lp.ld_out, lp.rs_off >= 0 ? ws + lp.rs_off : nullptr,
-                                lp.ld_out, B, lp.n_out, ws + p->off_da, p->ld_dz, dbias, st));
-      da = ws + p->off_da;
+                                lp.ld_out, B, lp.n_out, dab, ld_da, dbias, st));
+      da = dab;
     } else if (dbias != nullptr) {
       DINO_LAUNCH(launch_mlp_da(g, p->ld_dz, nullptr, 0, nullptr, 0, B, lp.n_out, nullptr, 0, dbias, st));
     }
@@ -860,17 +868,21 @@ static int run_mlp_backward(DinoPlan* p, const float* params, int B, float* grad
       GemmOp op = gemm_op_zero();
       op.A = l == 0 ? ws + p->off_z0 : ws + p->layers[l - 1].z_off;
       op.a_sm = 1; op.a_sk = l == 0 ? p->ld_in : p->layers[l - 1].ld_out;
-      op.B = da; op.b_sk = p->ld_dz; op.b_sn = 1;
+      op.B = da; op.b_sk = ld_da; op.b_sn = 1;
       op.M = lp.n_in; op.N = lp.n_out; op.K = B;
       op.C = grad + lp.koff; op.ldc = lp.n_out; op.atomic_c = 1;
-      // (da / dz live in rotating buffers: this contraction cannot wait for the grouped launch at the end of the step)
-      GemmGroup one;
-      one.n = 1; one.ops[0] = op;
-      if (flush_wgrad(p, one, st)) return 1;
+      if (da_kept) {
+        if (push_wgrad(p, wg, op, st)) return 1;
+      } else {
+        // (dz of a linear layer lives in a rotating buffer: this contraction cannot wait for the grouped launch)
+        GemmGroup one;
+        one.n = 1; one.ops[0] = op;
+        if (flush_wgrad(p, one, st)) return 1;
+      }
     }
     if (l > lowest_trainable) {   // dz_l = da_l W_l^T [+ dz above the residual block that starts here]
       GemmOp op = gemm_op_zero();
-      op.A = da; op.a_sm = p->ld_dz; op.a_sk = 1;
+      op.A = da; op.a_sm = ld_da; op.a_sk = 1;
       op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out;
       op.M = B; op.N = lp.n_in; op.K = lp.n_out;
       op.C = dz_ptr(l); op.ldc = p->ld_dz;
