@@ -38,7 +38,7 @@ struct TcGatherMaps { CUtensorMap m[8]; };
 constexpr int TC_NCONV = 8;     // fp32x3: converter warps (a stage of 32-48 KB per 768 MMA cycles: four warps could not keep up)
 
 // EPI: 0 plain store; 1 chain terms (rowsum / add_pre / scale / add_post / rounding); 2 network terms (bias / softplus +
-// sigmoid / add_pre / add_post)
+// sigmoid / add_pre / add_post); 3 chain terms + row dot products (tc_epilogue.cuh)
 // NEPI: epilogue warps (4 or 8): 8 split the column blocks of a lane quarter over two warps, for contractions whose
 // main loop is short against their epilogue (tf32; fp32x3 with a short K)
 template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI, int NCONV>
@@ -380,7 +380,11 @@ static cudaError_t launch_tc(const GemmOp& op, cudaStream_t st) {
   constexpr bool FITS8 = STAGES * 2 * (TC_BM + BN) * BK * 4 + 8 * 32 * 128 + 1280 <= 232448;
   const bool short_k = SPLIT && FITS8 && op.K <= 256;
   if (op.bias || op.act) return launch_tc1<BN, BK, STAGES, SPLIT, 2, SPLIT ? 4 : 8, NC>(op, st);
-  if (op.rowsum || op.rowdot || op.scale || op.add_pre || op.add_post || (op.round_tf32 && !SPLIT)) {
+  if (op.rowdot || op.pre_first) {      // the first layer without its Jacobian (plan.cu): class 1 plus row dot products
+    if (short_k) return launch_tc1<BN, BK, STAGES, SPLIT, 3, 8, SPLIT ? 4 : 0>(op, st);
+    return launch_tc1<BN, BK, STAGES, SPLIT, 3, SPLIT ? 4 : 8, NC>(op, st);
+  }
+  if (op.rowsum || op.scale || op.add_pre || op.add_post || (op.round_tf32 && !SPLIT)) {
     if (short_k) return launch_tc1<BN, BK, STAGES, SPLIT, 1, 8, SPLIT ? 4 : 0>(op, st);
     return launch_tc1<BN, BK, STAGES, SPLIT, 1, SPLIT ? 4 : 8, NC>(op, st);
   }

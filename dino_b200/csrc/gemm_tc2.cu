@@ -213,6 +213,7 @@ cudaError_t launch_gemm_tc2(const GemmOp& op, int split, cudaStream_t st) {
     // (Tried: the two cross terms as ONE bf16 contraction over [a | a_lo] x [b_lo | b] - a third fewer tensor cycles, the
     //  same accuracy - which came out slower, 274 against 241 us: the conversion got heavier and the kernel is not
     //  bound by the tensor pipe but by the clocks it can hold under the power cap.)
+    // (eight converter warps instead of four: 576 threads leave 96 registers each, the chain epilogue spills, 3 % slower)
     if (net) return launch_tc2<true, 2, 8, 3, 4>(op, st);
     if (chain) return launch_tc2<true, 1, 8, 3, 4>(op, st);
     return launch_tc2<true, 0, 8, 3, 4>(op, st);

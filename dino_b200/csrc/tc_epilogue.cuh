@@ -36,11 +36,14 @@ __device__ __forceinline__ float4 tc_ld4(const float* row, int n, int N) {
 // One accumulator tile of 128 rows x BN columns at tensor-memory address `tacc` (lane field 0), rows m0.. of C, columns
 // n0..; executed by the epilogue warp (q = its TMEM lane quarter, half = which of the NEPI / 4 warps of that quarter).
 // EPI: 0 plain store; 1 chain terms (rowsum / add_pre / scale / add_post / rounding); 2 network terms (bias / softplus +
-// sigmoid / add_pre / add_post).  SPLIT: the cross-term accumulator sits ACC_COLS columns above the main one.
-template <int BN, bool SPLIT, int EPI, int NEPI, uint32_t ACC_COLS>
+// sigmoid / add_pre / add_post); 3 chain terms plus the per-row dot products and add_pre ahead of the row sums (gemm_tc.cu
+// only: the first layer without its Jacobian).  SPLIT: the cross-term accumulator sits ACC_COLS columns above the main one.
+template <int BN, bool SPLIT, int EPI_, int NEPI, uint32_t ACC_COLS>
 __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, int n0, uint32_t tacc_base, uint32_t my_stage,
                                                  int q, int half, int lane, int m_lim) {
   using namespace tc;
+  constexpr int EPI = EPI_ == 3 ? 1 : EPI_;          // class 3 = class 1 + the terms marked EXT
+  constexpr bool EXT = EPI_ == 3;
   const uint32_t sw = (uint32_t)(lane & 7);
   {
       const int row = m0 + q * 32 + lane;
@@ -52,7 +55,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, i
       const float* yr = (EPI == 1 && ep.yref) ? ep.yref + (long long)row * ep.ld_y : nullptr;
       float* so = (EPI == 2 && ep.s_out) ? ep.s_out + (long long)row * ep.ld_s : nullptr;
       const uint32_t tacc = tacc_base + ((uint32_t)(q * 32) << 16);
-      const bool pre_first = EPI == 1 && ep.pre_first && ap;
+      const bool pre_first = EXT && ep.pre_first && ap;
       float rdot = 0.f;
 #pragma unroll 1
       for (int c0 = half * 32; c0 < BN; c0 += 32 * (NEPI / 4)) {
@@ -96,12 +99,12 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, i
           load32(p, yr, row_ok);
 #pragma unroll
           for (int j = 0; j < 32; ++j) p[j] *= v[j];
-          if (ep.rowdot) {
+          if (EXT && ep.rowdot) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) rdot += p[j];
           }
           const int r_first = m0 + q * 32;
-          if (ep.rowsum && r_first < m_lim) {
+          if ((!EXT || ep.rowsum) && r_first < m_lim) {
             const int b_lo = r_first / ep.sdim, b_hi = min(r_first + 31, m_lim - 1) / ep.sdim;
             for (int bb = b_lo; bb <= b_hi; ++bb) {
               float mm[32];
@@ -194,7 +197,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcEpilogue& ep, int m0, i
           }
         }
       }
-      if (EPI == 1 && ep.rowdot && row_ok) atomicAdd(ep.rowdot + row, rdot);
+      if (EXT && ep.rowdot && row_ok) atomicAdd(ep.rowdot + row, rdot);
   }
 }
 
