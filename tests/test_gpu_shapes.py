@@ -188,8 +188,8 @@ def test_two_plans_on_two_devices_in_one_process(cuda_device):
 
 
 @pytest.mark.parametrize("precision", ["fp32x3", "tf32"])
-@pytest.mark.parametrize("d_out", [72, 96])
-def test_first_layer_without_its_jacobian(cuda_device, precision, d_out, monkeypatch):
+@pytest.mark.parametrize("d_out,hidden", [(72, [40, 36]), (96, [40, 36]), (48, [264, 40])])
+def test_first_layer_without_its_jacobian(cuda_device, precision, d_out, hidden, monkeypatch):
     """Full Jacobian over an unreduced input (d_in >= 1024): the step that never forms J_hat (csrc/plan.cu,
     run_implicit_layer0: the target gathered per sample by TMA, J W and J^T Q instead of G W and G^T Q) against the
     oracle and against the explicit path of the same library, over shuffled minibatches with a ragged last one: loss,
@@ -197,7 +197,8 @@ def test_first_layer_without_its_jacobian(cuda_device, precision, d_out, monkeyp
     tol_j, tol_g = BARS[precision]
     # 72 rows per sample: row tiles stop at sample ends (one part-empty tile each); 96: 128-row tiles of consecutive rows,
     # loaded as 32-row-granular boxes from up to three samples; 1030 % 4 != 0: the target is re-pitched on upload
-    arch = S.Arch("generic_dense", 1030, d_out, hidden=[40, 36])
+    # hidden[0] = 264: a first layer wider than two 128-column tiles (the Gram matrices take the wide weight-gradient tiles)
+    arch = S.Arch("generic_dense", 1030, d_out, hidden=hidden)
     n, B = 13, 5
     data, tw = S.make_dataset(arch, n, 77)
     w = S.student_weights(arch, 78, tw, bias_noise=0.1)
