@@ -191,3 +191,37 @@ def test_synthetic_flop_and_byte_model_matches_survey():
     assert abs(S.flops_per_sample(S.CONFIGS["cfg2"]["arch"]) / 8.67e6 - 1) < 0.01
     assert S.bytes_per_sample(S.CONFIGS["cfg2"]["arch"]) == 20600
     assert S.bytes_per_sample(S.CONFIGS["cfg3"]["arch"]) == 81200
+
+
+def test_ctypes_structs_match_the_c_header(tmp_path):
+    """The ctypes mirrors of the C-ABI structs (dino_b200/_lib.py) have the size and field offsets gcc gives the structs of
+    include/dino_b200.h (a field added on one side only would shift every pointer after it)."""
+    import ctypes as C
+    import shutil
+    import subprocess
+    from dino_b200 import _lib
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    structs = {"DinoBatch": _lib.DinoBatch, "DinoNetSpec": _lib.DinoNetSpec, "DinoLayerSpec": _lib.DinoLayerSpec}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "dino_b200.h"', 'int main(void) {']
+    for name, cls in structs.items():
+        lines.append(f'  printf("{name} size %zu\\n", sizeof({name}));')
+        for fld, _ in cls._fields_:
+            lines.append(f'  printf("{name} {fld} %zu\\n", offsetof({name}, {fld}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "abi.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "abi"
+    inc = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include")
+    subprocess.run(["gcc", "-I", inc, str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split("\n")
+    seen = 0
+    for ln in out:
+        if not ln.strip():
+            continue
+        name, fld, val = ln.split()
+        cls = structs[name]
+        want = C.sizeof(cls) if fld == "size" else getattr(cls, fld).offset
+        assert int(val) == want, ln
+        seen += 1
+    assert seen == sum(len(c._fields_) + 1 for c in structs.values())
