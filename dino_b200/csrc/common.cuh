@@ -40,6 +40,8 @@ struct GemmOp {
   float* rowdot;                                     // rowdot[m] += sum_n v * yref[m,n]  (v as the row sums see it)
   int pre_first;                                     // add_pre joins BEFORE the row sums / rowdot see the value
   float alpha;                                       // weight gradients: C += alpha * X^T Y
+  const float* B_lo;                                 // fp32x3 on the tcgen05 engines: B - trunc_tf32(B), same layout as B (staged
+                                                     // weights): the converter warps then split A only
 };
 
 inline GemmOp gemm_op_zero() {
@@ -52,7 +54,7 @@ inline GemmOp gemm_op_zero() {
   o.yref = nullptr; o.ld_y = 0; o.rowsum = nullptr; o.ld_rs = 0;
   o.add_pre = nullptr; o.ld_ap = 0; o.scale = nullptr; o.ld_sc = 0;
   o.add_post = nullptr; o.ld_apo = 0; o.round_tf32 = 0;
-  o.a_idx = nullptr; o.a_rows = 0; o.a_ld2 = 0; o.a_nsamp = 0; o.rowdot = nullptr; o.pre_first = 0; o.alpha = 1.f;
+  o.a_idx = nullptr; o.a_rows = 0; o.a_ld2 = 0; o.a_nsamp = 0; o.rowdot = nullptr; o.pre_first = 0; o.alpha = 1.f; o.B_lo = nullptr;
   return o;
 }
 

@@ -44,7 +44,7 @@ constexpr int TC_NCONV = 8;     // fp32x3: converter warps (a stage of 32-48 KB 
 template <int BN, int BK, int STAGES, bool SPLIT, int EPI, int NEPI, int NCONV>
 __global__ void __launch_bounds__((2 + NEPI + (SPLIT ? NCONV : 0)) * 32, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep,
-               const __grid_constant__ TcGatherMaps gmaps) {
+               const __grid_constant__ TcGatherMaps gmaps, const __grid_constant__ CUtensorMap tma_b_lo) {
   constexpr int A_BYTES = TC_BM * BK * 4, B_BYTES = BN * BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
   constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;           // columns of one accumulator
@@ -122,19 +122,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(empty_bar + st, ph ^ 1);
           uint8_t* sa = smem + st * STAGE_BYTES;
+          const uint32_t lo_bytes = (SPLIT && ep.b_lo) ? (uint32_t)B_BYTES : 0u;
           if (nbox > 0) {
-            mbar_expect_tx(full_bar + st, (uint32_t)(rows_loaded * BK * 4 + B_BYTES));
+            mbar_expect_tx(full_bar + st, (uint32_t)(rows_loaded * BK * 4 + B_BYTES) + lo_bytes);
             int off = 0;
             for (int j = 0; j < nbox; ++j) {
               tma_load_3d(sa + off, &gmaps.m[box_h[j] / ep.a_gran - 1], kb * BK, box_r[j], box_s[j], full_bar + st);
               off += box_h[j] * BK * 4;
             }
           } else {
-            mbar_expect_tx(full_bar + st, RAW_BYTES);
+            mbar_expect_tx(full_bar + st, RAW_BYTES + lo_bytes);
             if (per_sample) tma_load_3d(sa, &tma_a, kb * BK, m0, samp, full_bar + st);
             else tma_load_2d(sa, &tma_a, kb * BK, m0, full_bar + st);
           }
           tma_load_2d(sa + A_BYTES, &tma_b, kb * BK, n0, full_bar + st);
+          if (SPLIT && ep.b_lo) tma_load_2d(sa + RAW_BYTES + A_BYTES, &tma_b_lo, kb * BK, n0, full_bar + st);
         }
       }
     }
@@ -180,7 +182,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           const int st = it % STAGES;
           mbar_wait(full_bar + st, (it / STAGES) & 1);
           const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
-          split_lo_tile(sa, sa + RAW_BYTES, RAW_BYTES, t, NCONV * 32);
+          split_lo_tile(sa, sa + RAW_BYTES, ep.b_lo ? A_BYTES : RAW_BYTES, t, NCONV * 32);
           fence_async_smem();                        // generic-proxy writes -> visible to the tensor core
           __syncwarp();
           if (lane == 0) mbar_arrive(conv_bar + st);
@@ -347,10 +349,13 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
       if (!tc_make_map3(&gm.m[j], op.A, op.K, op.a_rows, op.a_nsamp, op.a_sm, op.a_ld2, BK, (unsigned)((j + 1) * gran), sw_in)) return cudaErrorInvalidValue;
   } else if (!tc_make_map(&ma, op.A, op.K, op.M, op.a_sm, BK, TC_BM, sw_in)) return cudaErrorInvalidValue;
   if (!tc_make_map(&mb, op.B, op.K, op.N, op.b_sn, BK, BN, sw_in)) return cudaErrorInvalidValue;
+  CUtensorMap mbl = mb;
+  const bool b_lo = SPLIT && op.B_lo != nullptr && (reinterpret_cast<uintptr_t>(op.B_lo) & 15) == 0;
+  if (b_lo && !tc_make_map(&mbl, op.B_lo, op.K, op.N, op.b_sn, BK, BN, sw_in)) return cudaErrorInvalidValue;
   TcEpilogue ep;
   ep.a_rows = op.a_rows; ep.a_tps = op.a_rows > 0 ? (op.a_rows + TC_BM - 1) / TC_BM : 0; ep.a_idx = op.a_idx;
   ep.rowdot = op.rowdot; ep.pre_first = op.pre_first;
-  ep.a_gran = gran;
+  ep.a_gran = gran; ep.b_lo = b_lo ? 1 : 0;
   ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.C = op.C; ep.ldc = op.ldc; ep.sdim = op.sdim > 0 ? op.sdim : 1;
   ep.scale = op.scale; ep.ld_sc = op.ld_sc; ep.add_pre = op.add_pre; ep.ld_ap = op.ld_ap;
   ep.add_post = op.add_post; ep.ld_apo = op.ld_apo; ep.bias = op.bias; ep.act = op.act;
@@ -368,7 +373,7 @@ static cudaError_t launch_tc1(const GemmOp& op, cudaStream_t st) {
   const long long m_tiles = (op.a_rows > 0 && gran == 0) ? (long long)(op.M / op.a_rows) * ((op.a_rows + TC_BM - 1) / TC_BM) : (op.M + TC_BM - 1) / TC_BM;
   const long long n_tiles = (long long)((op.N + BN - 1) / BN) * m_tiles;
   const int grid = (int)(n_tiles < num_sms ? n_tiles : num_sms);
-  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI, NCONV><<<grid, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep, gm);
+  gemm_tc_kernel<BN, BK, STAGES, SPLIT, EPI, NEPI, NCONV><<<grid, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep, gm, mbl);
   return cudaGetLastError();
 }
 

@@ -28,7 +28,8 @@ constexpr int T2_BK = 32;
 // NCONV: converter warps of the fp32x3 form (a stage of 32 KB per 1536 MMA clocks: four keep up)
 template <bool SPLIT, int EPI, int NEPI, int STAGES, int NCONV>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((2 + NEPI + (SPLIT ? NCONV : 0)) * 32, 1)
-gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep) {
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep,
+                const __grid_constant__ CUtensorMap tma_b_lo) {
   constexpr int A_BYTES = 128 * T2_BK * 4, B_BYTES = 128 * T2_BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
   constexpr uint32_t ACC_COLS = 256;
@@ -90,9 +91,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           mbar_wait(empty_bar + st, ph ^ 1);
           uint8_t* sa = smem + st * STAGE_BYTES;
           if (SPLIT) {
-            mbar_expect_tx(full_bar + st, RAW_BYTES);
+            mbar_expect_tx(full_bar + st, ep.b_lo ? RAW_BYTES + B_BYTES : RAW_BYTES);
             tma_load_2d(sa, &tma_a, kb * T2_BK, m0, full_bar + st);
             tma_load_2d(sa + A_BYTES, &tma_b, kb * T2_BK, n0, full_bar + st);
+            if (ep.b_lo) tma_load_2d(sa + RAW_BYTES + A_BYTES, &tma_b_lo, kb * T2_BK, n0, full_bar + st);
           } else {
             if (rank == 0) mbar_expect_tx(full_bar + st, 2 * RAW_BYTES);     // the bytes of both CTAs land on the leader's barrier
             tma_load_2d_2sm(sa, &tma_a, kb * T2_BK, m0, full_bar + st);
@@ -141,7 +143,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         const int st = it % STAGES;
         mbar_wait(full_bar + st, (it / STAGES) & 1);
         const uint32_t sa = smem_u32(smem + st * STAGE_BYTES);
-        split_lo_tile(sa, sa + RAW_BYTES, RAW_BYTES, t, NCONV * 32);
+        split_lo_tile(sa, sa + RAW_BYTES, ep.b_lo ? A_BYTES : RAW_BYTES, t, NCONV * 32);
         fence_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(conv_bar + st, 0);
@@ -174,10 +176,14 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
 
 template <bool SPLIT, int EPI, int NEPI, int STAGES, int NCONV>
 static cudaError_t launch_tc2(const GemmOp& op, cudaStream_t st) {
-  CUtensorMap ma, mb;
+  CUtensorMap ma, mb, mbl;
   if (!tc_make_map(&ma, op.A, op.K, op.M, op.a_sm, T2_BK, 128, (int)CU_TENSOR_MAP_SWIZZLE_128B) ||
       !tc_make_map(&mb, op.B, op.K, op.N, op.b_sn, T2_BK, 128, (int)CU_TENSOR_MAP_SWIZZLE_128B))
     return cudaErrorInvalidValue;
+  const bool b_lo = SPLIT && op.B_lo != nullptr && (reinterpret_cast<uintptr_t>(op.B_lo) & 15) == 0;
+  if (b_lo) {
+    if (!tc_make_map(&mbl, op.B_lo, op.K, op.N, op.b_sn, T2_BK, 128, (int)CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+  } else mbl = mb;
   TcEpilogue ep;
   ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.C = op.C; ep.ldc = op.ldc; ep.sdim = op.sdim > 0 ? op.sdim : 1;
   ep.scale = op.scale; ep.ld_sc = op.ld_sc; ep.add_pre = op.add_pre; ep.ld_ap = op.ld_ap;
@@ -185,7 +191,7 @@ static cudaError_t launch_tc2(const GemmOp& op, cudaStream_t st) {
   ep.s_out = op.act ? op.s_out : nullptr; ep.ld_s = op.ld_s;
   ep.yref = op.rowsum ? op.yref : nullptr; ep.ld_y = op.ld_y; ep.rowsum = op.rowsum; ep.ld_rs = op.ld_rs;
   ep.round_tf32 = SPLIT ? 0 : op.round_tf32;
-  ep.a_rows = 0; ep.a_tps = 0; ep.a_idx = nullptr; ep.rowdot = nullptr; ep.pre_first = 0; ep.a_gran = 0;
+  ep.a_rows = 0; ep.a_tps = 0; ep.a_idx = nullptr; ep.rowdot = nullptr; ep.pre_first = 0; ep.a_gran = 0; ep.b_lo = b_lo ? 1 : 0;
   constexpr int RAW = 2 * 128 * T2_BK * 4;
   constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + NEPI * 32 * 128 + 256 + 1024;
   static_assert(SMEM <= 232448, "shared memory budget of one CTA");
@@ -195,7 +201,7 @@ static cudaError_t launch_tc2(const GemmOp& op, cudaStream_t st) {
   const int num_sms = tc_current_num_sms();
   const long long n_tiles = (long long)((op.N + 255) / 256) * ((op.M + 255) / 256);
   const int pairs = (int)(n_tiles < num_sms / 2 ? n_tiles : num_sms / 2);
-  gemm_tc2_kernel<SPLIT, EPI, NEPI, STAGES, NCONV><<<2 * pairs, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep);
+  gemm_tc2_kernel<SPLIT, EPI, NEPI, STAGES, NCONV><<<2 * pairs, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep, mbl);
   return cudaGetLastError();
 }
 

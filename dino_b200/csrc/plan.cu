@@ -293,6 +293,16 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
       }
     }
   }
+  if (p->tc && p->split && !p->chain_fused && p->prep.n > 0 && getenv("DINO_B200_NO_WLO") == nullptr) {
+    // layer-by-layer fp32x3: the low parts of the staged weights are written once per step by prep_weights_kernel, and the
+    // contraction kernels fetch them by TMA instead of splitting the weight tile of every stage on chip
+    for (int l = 0; l < p->L; ++l) {
+      LayerPlan& lp = p->layers[l];
+      lp.wp_lo_off = take((long long)lp.n_in * lp.ld_wp);
+      lp.wtp_lo_off = take((long long)lp.n_out * lp.ld_wtp);
+      p->prep.e[l].wp_lo_off = lp.wp_lo_off; p->prep.e[l].wtp_lo_off = lp.wtp_lo_off;
+    }
+  }
   // first layer without its Jacobian: FULL Jacobian of a wide (unreduced) input through a plain softplus layer
   p->implicit0 = false;
   p->off_qc = p->off_tb = p->off_negc = p->off_mw = p->off_sb = p->off_tdot = p->off_ddot = -1; p->imp_zero_floats = 0;
@@ -464,6 +474,7 @@ static int run_mlp_forward(DinoPlan* p, const float* params, const DinoBatch* b,
     if (tc_mlp) {
       GemmOp opt = op;
       opt.B = ws + lp.wtp_off; opt.b_sk = 1; opt.b_sn = lp.ld_wtp;             // K-major W^T for the tcgen05 engine
+      if (p->split && lp.wtp_lo_off >= 0) opt.B_lo = ws + lp.wtp_lo_off;
       if (mlp_gemm(p, opt, op, st)) return 1;
     } else if (gemm_simt_only(p, op, st)) return 1;
     zin = ws + lp.z_off; ld_zin = lp.ld_out;
@@ -519,7 +530,7 @@ static int run_chain_forward(DinoPlan* p, const float* params, const DinoBatch* 
     else { op.A = ws + lp.q_off; op.a_sm = lp.ld_out; }
     op.a_sk = 1;
     // W_l^T: element (k = out index, n = in index) = W_l[n][k]; the TF32 engine reads the 16-byte-pitch copy
-    if (tc) { op.B = ws + lp.wp_off; op.b_sk = 1; op.b_sn = lp.ld_wp; }
+    if (tc) { op.B = ws + lp.wp_off; op.b_sk = 1; op.b_sn = lp.ld_wp; if (p->split && lp.wp_lo_off >= 0) op.B_lo = ws + lp.wp_lo_off; }
     else { op.B = params + lp.koff; op.b_sk = 1; op.b_sn = lp.n_out; }
     op.M = M; op.N = lp.n_in; op.K = lp.n_out; op.sdim = s;
     if (lp.lands_skip >= 0) {
@@ -671,6 +682,7 @@ static GemmOp implicit_t1_op(const DinoPlan* p, const DinoBatch* b, int B) {
   op.A = b->J; op.a_sm = b->ld_J; op.a_sk = 1;
   op.a_rows = p->s; op.a_ld2 = (long long)p->s * b->ld_J; op.a_idx = b->idx; op.a_nsamp = implicit_nsamp(b, B);
   op.B = ws + l0.wtp_off; op.b_sk = 1; op.b_sn = l0.ld_wtp;
+  if (p->split && l0.wtp_lo_off >= 0) op.B_lo = ws + l0.wtp_lo_off;
   op.M = B * p->s; op.N = l0.n_out; op.K = l0.n_in; op.sdim = p->s;
   op.scale = ws + p->off_negc; op.ld_sc = l0.ld_out;
   op.yref = ws + l0.q_off; op.ld_y = l0.ld_out; op.rowdot = ws + p->off_tdot;
@@ -795,6 +807,7 @@ static int run_chain_backward(DinoPlan* p, const float* params, int B, float* gr
       // tensor-core path: dQ_l = dR_l W_l with the K-major copy W_l^T; the cross-row d sigma sum, the per-sample
       // scaling and the residual all happen in the epilogue of the same launch
       op.B = ws + lp.wtp_off; op.b_sk = 1; op.b_sn = lp.ld_wtp;
+      if (p->split && lp.wtp_lo_off >= 0) op.B_lo = ws + lp.wtp_lo_off;
       if (need_rs) {
         op.yref = q; op.ld_y = ldq;
         op.rowsum = ws + lp.rs_off; op.ld_rs = lp.ld_out;
@@ -890,6 +903,7 @@ static int run_mlp_backward(DinoPlan* p, const float* params, int B, float* grad
       if (tc_mlp) {
         GemmOp opt = op;
         opt.B = ws + lp.wp_off; opt.b_sk = 1; opt.b_sn = lp.ld_wp;               // 16-byte-pitch copy of W_l
+        if (p->split && lp.wp_lo_off >= 0) opt.B_lo = ws + lp.wp_lo_off;
         if (mlp_gemm(p, opt, op, st)) return 1;
       } else if (gemm_simt_only(p, op, st)) return 1;
     }

@@ -20,6 +20,7 @@ struct TcEpilogue {
   // per-row dot products with yref, add_pre ahead of the row sums
   int a_rows, a_tps; const int* a_idx;
   float* rowdot; int pre_first;
+  int b_lo;                  // fp32x3: the lo tile of B arrives by TMA (precomputed), the converters split A only
   int a_gran;                // > 0: consecutive-row tiles loaded as boxes of multiples of a_gran rows (gemm_tc.cu: TcGatherMaps)
 };
 
