@@ -108,3 +108,41 @@ def prune_the_data_device(projector_dict, train_dict, test_dict, input_pruning=T
                 Jd = torch.stack([gemm_tn(Phi, Jd[i].contiguous()) for i in range(Jd.shape[0])])
         d['J_data'] = back(Jd)
     return train_dict, test_dict
+
+
+def upload_factors(data_dict):
+    """m, q and the singular factors U, sigma, V of a dataset as device tensors (float32): uploaded ONCE, so that the
+    per-epoch re-flattening of the sketched training (jacobianTrainingDriver.py:234-241) never goes back to the host."""
+    return {k: _dev(data_dict[k]) for k in ('m_data', 'q_data', 'U_data', 'sigma_data', 'V_data')}
+
+
+def flatten_data_device(data_dict, target_rank=80, batch_rank=8, order_random=True, diagonalize_sigma=True, seed=0,
+                        burn_in=0):
+    """flatten_data (dataUtilities.py:348-445) on device tensors: truncate the factors to target_rank, draw the same column
+    permutation as the host function (numpy RandomState(seed) after burn_in draws), cut the columns into
+    target_rank / batch_rank groups and make every group a training row [m, U_g, V_g] -> [q, diag(sigma_g)].  Pure data
+    movement: the result equals the host function's cast to float32, element for element.  Inputs may be numpy arrays or
+    the tensors of upload_factors; the returned dict holds device tensors, which DinoModel.fit / evaluate take as they
+    are."""
+    import torch
+    assert target_rank % batch_rank == 0
+    groups = target_rank // batch_rank
+    m, q = _dev(data_dict['m_data']), _dev(data_dict['q_data'])
+    U = _dev(data_dict['U_data'])[:, :, :target_rank]
+    sg = _dev(data_dict['sigma_data'])[:, :target_rank]
+    V = _dev(data_dict['V_data'])[:, :, :target_rank]
+    if order_random:
+        random_state = np.random.RandomState(seed=seed)
+        for _ in range(burn_in):
+            random_state.permutation(target_rank)
+        cols = torch.from_numpy(random_state.permutation(target_rank).astype(np.int64)).to(U.device)
+        U, sg, V = U.index_select(2, cols), sg.index_select(1, cols), V.index_select(2, cols)
+    n, dQ, dM = m.shape[0], U.shape[1], V.shape[1]
+    rows = n * groups
+    Unew = U.reshape(n, dQ, groups, batch_rank).permute(0, 2, 1, 3).contiguous().reshape(rows, dQ, batch_rank)
+    Vnew = V.reshape(n, dM, groups, batch_rank).permute(0, 2, 1, 3).contiguous().reshape(rows, dM, batch_rank)
+    snew = sg.contiguous().reshape(rows, batch_rank)
+    if diagonalize_sigma:
+        snew = torch.diag_embed(snew)
+    return {'m_data': m.repeat_interleave(groups, dim=0), 'q_data': q.repeat_interleave(groups, dim=0),
+            'U_data': Unew, 'sigma_data': snew, 'V_data': Vnew}

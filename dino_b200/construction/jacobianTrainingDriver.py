@@ -146,8 +146,16 @@ def train_dino(settings, regressor, train_dict, test_dict, unflattened_train_dic
         for epoch in range(settings['outer_epochs']):
             if verbose:
                 print(('Running inner iteration ' + str(epoch)).center(80))
-            train_dict = flatten_data(unflattened_train_dict, target_rank=settings['target_rank'],
-                                      batch_rank=settings['batch_rank'], order_random=True, burn_in=epoch)
+            if settings.get('device_data', False):
+                # the factors go to the device once; every outer epoch re-draws and regroups the sketch columns there
+                if epoch == 0:
+                    from .deviceData import upload_factors, flatten_data_device
+                    device_factors = upload_factors(unflattened_train_dict)
+                train_dict = flatten_data_device(device_factors, target_rank=settings['target_rank'],
+                                                 batch_rank=settings['batch_rank'], order_random=True, burn_in=epoch)
+            else:
+                train_dict = flatten_data(unflattened_train_dict, target_rank=settings['target_rank'],
+                                          batch_rank=settings['batch_rank'], order_random=True, burn_in=epoch)
             regressor = train_h1_network(regressor, train_dict, test_dict, opt_parameters=settings['opt_parameters'],
                                          verbose=True)
     else:

@@ -274,6 +274,8 @@ class DeviceDataset:
         dev = _device()
 
         def up(a):
+            if isinstance(a, torch.Tensor):          # already on a device (construction/deviceData.py): no host round trip
+                return a.to(device=dev, dtype=torch.float32).contiguous()
             a = np.asarray(a)
             if a.dtype != np.float32:
                 a = a.astype(np.float32)

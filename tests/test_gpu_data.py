@@ -45,3 +45,21 @@ def test_large_remap_matches_numpy(cuda_device):
     out = remap_jacobian_data_device(d)
     want = np.einsum("nqk,nk,nmk->nqm", d["U_data"], d["sigma_data"], d["V_data"])
     assert H.rel_err(out["J_data"], want) < 1e-5
+
+
+@pytest.mark.parametrize("burn_in", [0, 3])
+def test_flatten_data_on_the_device_is_the_host_function(cuda_device, burn_in):
+    """flatten_data (dataUtilities.py:348-445) as device data movement: the same column permutation, grouping and sample
+    replication as the host function, element for element (float32 casts of the same values)."""
+    from dino_b200.construction import flatten_data
+    from dino_b200.construction.deviceData import flatten_data_device, upload_factors
+    d = _svd_data()
+    rank = d["sigma_data"].shape[1]
+    br = 2 if rank % 2 == 0 else 1
+    tr = (rank // br) * br
+    host = flatten_data(d, target_rank=tr, batch_rank=br, order_random=True, burn_in=burn_in)
+    dev = flatten_data_device(upload_factors(d), target_rank=tr, batch_rank=br, order_random=True, burn_in=burn_in)
+    assert set(dev) == set(host)
+    for k in host:
+        assert dev[k].is_cuda
+        assert np.array_equal(dev[k].cpu().numpy(), np.asarray(host[k], dtype=np.float32)), k

@@ -230,3 +230,25 @@ def test_fit_generator_matches_train_on_batch(cuda_device):
     for la, lb in zip(a.layers, b.layers):
         for wa, wb in zip(la.get_weights(), lb.get_weights()):
             np.testing.assert_allclose(wb, wa, rtol=1e-5, atol=1e-7)
+
+
+def test_sketched_driver_reshuffles_on_the_device(cuda_device, tmp_path):
+    """settings['device_data'] with shuffle_every_epoch: the factors are uploaded once and every outer epoch re-flattens them
+    on the device (deviceData.flatten_data_device); DinoModel.fit takes the device tensors as they are.  Same seeds ->
+    the training data are the host path's element for element, so the trained weights agree to summation order."""
+    data_dir, _ = _make_data_dir(tmp_path)
+    out = []
+    for dev_data in (False, True):
+        settings = _settings(data_dir, tmp_path, architecture="generic_dense", train_full_jacobian=0, target_rank=10,
+                             batch_rank=5, truncation_dimension=12, depth=2, reduced_input_training=False,
+                             shuffle_every_epoch=True, outer_epochs=2, inner_epochs=1)
+        settings["opt_parameters"].update(train_full_jacobian=0, keras_epochs=1, keras_batch_size=16)
+        settings["device_data"] = dev_data
+        np.random.seed(3)                      # the minibatch order of fit
+        from dino_b200.construction.neuralNetworks import set_seed
+        set_seed(11)                           # the weight initialiser
+        regressor = D.jacobian_training_driver(settings)
+        out.append([x for l in regressor.layers for x in l.get_weights()])
+    for a, b in zip(*out):
+        assert np.isfinite(b).all()
+        assert H.rel_err(b, a) < 1e-4
