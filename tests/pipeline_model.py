@@ -56,9 +56,11 @@ def reverse_chain(layers, s, seed):
     return Q, R_next
 
 
-def step(layers, m, q, Jt, w=(1.0, 1.0), seed=None, V=None, inv_B=None):
+def step(layers, m, q, Jt, w=(1.0, 1.0), seed=None, V=None, inv_B=None, implicit_first_layer=False):
     """Returns dict(loss3, grads[(dW, db)], qhat, Jhat).  seed: None -> identity (full Jacobian);
-    [S,d_out] shared (Phi^T); or [B,S,d_out] per sample (U^T, then V [B,d_M,k] closes the sketch)."""
+    [S,d_out] shared (Phi^T); or [B,S,d_out] per sample (U^T, then V [B,d_M,k] closes the sketch).
+    implicit_first_layer: layer 0 of the backward chain and the H1 loss as csrc/plan.cu's run_implicit_layer0 computes
+    them - from T = J W_1, M = W_1^T W_1 and the chain state Q above layer 0, never from J_hat (full Jacobian only)."""
     B = m.shape[0]
     inv_B = 1.0 / B if inv_B is None else inv_B
     nL = len(layers)
@@ -74,6 +76,14 @@ def step(layers, m, q, Jt, w=(1.0, 1.0), seed=None, V=None, inv_B=None):
     # losses (trainingUtilities.py:25-37)
     eq, nq = ((q - qh) ** 2).sum(1), (q ** 2).sum(1)
     eJ, nJ = ((Jt - Jh) ** 2).sum((1, 2)), (Jt ** 2).sum((1, 2))
+    if implicit_first_layer:
+        assert V is None and layers[0].skip_from < 0
+        W1, Q0 = layers[0].W, Q[0]
+        cb = 2.0 * w[1] * inv_B / nJ                       # [B]
+        T = Jt @ W1                                        # [B,S,n1]: the target is the operand of the d_in-wide contraction
+        Mw = W1.T @ W1
+        QM = Q0 @ Mw
+        eJ = ((QM * Q0).sum(2) - 2.0 * (T * Q0).sum(2) + (Jt ** 2).sum(2)).sum(1)       # per-row identity, summed
     l2, h1 = (eq / nq).sum() * inv_B, (eJ / nJ).sum() * inv_B
     dq = 2.0 * w[0] * (qh - q) / nq[:, None] * inv_B
     dJ = 2.0 * w[1] * (Jh - Jt) / nJ[:, None, None] * inv_B
@@ -84,10 +94,16 @@ def step(layers, m, q, Jt, w=(1.0, 1.0), seed=None, V=None, inv_B=None):
     rowsum = [None] * nL
     dR_in = {0: dR}
     for l in range(nL):
-        dRl = dR_in[l]
-        dQ = dRl @ layers[l].W
-        if layers[l].trainable:
-            dW[l] += np.einsum("bsi,bso->io", dRl, Q[l])
+        if l == 0 and implicit_first_layer:
+            Qc = cb[:, None, None] * Q0
+            dQ = Qc @ Mw - cb[:, None, None] * T                                        # = G W_1
+            if layers[0].trainable:
+                dW[0] += W1 @ np.einsum("bsi,bso->io", Qc, Q0) - np.einsum("bsi,bso->io", Jt, Qc)   # = G^T Q
+        else:
+            dRl = dR_in[l]
+            dQ = dRl @ layers[l].W
+            if layers[l].trainable:
+                dW[l] += np.einsum("bsi,bso->io", dRl, Q[l])
         rowsum[l] = (dQ * Q[l]).sum(1)
         nxt = dQ * s[l][:, None, :]
         if layers[l].skip_from >= 0:

@@ -57,3 +57,24 @@ def test_pipeline_matches_autograd(kind, mode):
         if L.bias is not None:
             ref = grads[gi].numpy(); gi += 1
             assert np.abs(ref - out["db"][l]).max() < 1e-12 * (np.abs(ref).max() + 1e-30)
+
+
+def test_first_layer_without_its_jacobian_is_the_same_step():
+    """The identities behind csrc/plan.cu: run_implicit_layer0 (G W = c (Q M - T), G^T Q = W S - J^T (c Q), the per-row
+    error from row dot products), fp64: the same loss and gradients as the explicit stages, and as autograd."""
+    net = dict(nets())["generic"]
+    B = 4
+    m, q = rng.normal(size=(B, net.d_in)), rng.normal(size=(B, net.d_out))
+    J = rng.normal(size=(B, net.d_out, net.d_in))
+    layers = to_layers(net)
+    a = P.step(layers, m, q, J, w=(0.7, 1.3))
+    b = P.step(layers, m, q, J, w=(0.7, 1.3), implicit_first_layer=True)
+    assert np.allclose(a["loss3"], b["loss3"], rtol=1e-12, atol=0)
+    for x, y in zip(a["dW"] + [v for v in a["db"] if v is not None], b["dW"] + [v for v in b["db"] if v is not None]):
+        assert np.abs(x - y).max() <= 1e-12 * max(np.abs(x).max(), 1e-30)
+    batch = O.Batch(torch.tensor(m), torch.tensor(q), torch.tensor(J))
+    (lt, _, _), grads = O.h1_step_grads(net, batch, (0.7, 1.3))
+    assert abs(b["loss3"][0] - lt) < 1e-12 * abs(lt)
+    mine = [g for l, L in enumerate(layers) for g in ([b["dW"][l]] + ([b["db"][l]] if L.b is not None else [])) if L.trainable]
+    for x, y in zip(mine, grads):
+        assert np.abs(x - y.numpy()).max() <= 1e-10 * max(np.abs(x).max(), 1e-30)
