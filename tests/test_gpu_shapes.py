@@ -229,3 +229,31 @@ def test_first_layer_without_its_jacobian(cuda_device, precision, d_out, hidden,
         for i, c in enumerate(ws0):
             assert H.rel_err(w_imp[name][i] - c, w_exp[name][i] - c) < 2 * tol_g, name
             assert H.rel_err(w_imp[name][i] - c, ow[name][i] - c) < 2 * tol_g, name
+
+
+def test_first_layer_without_its_jacobian_over_100_adam_steps(cuda_device, monkeypatch):
+    """100 Adam steps (25 epochs of 4 shuffled minibatches) of a full-Jacobian network over a 1030-wide input: the
+    Jacobian-free first layer and the explicit path end at the same loss and the same parameters (fp32x3; Adam's
+    division by sqrt(v) amplifies per-step differences of 1e-6, hence 2e-3 on the parameter change)."""
+    arch = S.Arch("generic_dense", 1030, 96, hidden=[40, 36])
+    n, B = 64, 16
+    data, tw = S.make_dataset(arch, n, 5)
+    w = S.student_weights(arch, 6, tw, bias_noise=0.1)
+    rng = np.random.default_rng(9)
+    perms = [rng.permutation(n) for _ in range(25)]
+    res = []
+    for explicit in (False, True):
+        if explicit:
+            monkeypatch.setenv("DINO_B200_NO_IMPLICIT0", "1")
+        else:
+            monkeypatch.delenv("DINO_B200_NO_IMPLICIT0", raising=False)
+        model = S.build_model(arch, w, precision="fp32x3")
+        _compile(model, Adam(1e-3))
+        hist = model.fit([data["m"]], [data["q"], data["J"]], epochs=25, batch_size=B, perms=perms)
+        res.append((hist.history["loss"], {l.name: l.get_weights() for l in model.layers}))
+    (la, wa), (lb, wb) = res
+    assert lb[-1] < 0.9 * lb[0]                                   # it trains
+    assert np.allclose(la, lb, rtol=1e-3, atol=0)
+    for name, ws0 in w.items():
+        for i, c in enumerate(ws0):
+            assert H.rel_err(wa[name][i] - c, wb[name][i] - c) < 2e-3, name
