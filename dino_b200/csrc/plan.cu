@@ -331,6 +331,17 @@ extern "C" int dino_plan_create(const DinoNetSpec* spec, int device, DinoPlan** 
     DINO_CUDA(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
     DINO_CUDA(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
     DINO_CUDA(cudaEventCreateWithFlags(&p->ev_prep, cudaEventDisableTiming));
+  } else if (p->tc && p->jac_mode != DINO_JAC_NONE && getenv("DINO_B200_NO_SIDE_STREAM") == nullptr) {
+    // layer-by-layer tensor-core plans: the network's backward pass (some twenty short launches on a few SMs each) runs
+    // on a HIGH-PRIORITY side stream next to the grouped weight gradients of the chain, which fill the GPU for a
+    // millisecond: its CTAs take the SMs the big launch frees first
+    int least = 0, greatest = 0;
+    DINO_CUDA(cudaSetDevice(device));
+    DINO_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    DINO_CUDA(cudaStreamCreateWithPriority(&p->side, cudaStreamNonBlocking, greatest));
+    DINO_CUDA(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+    DINO_CUDA(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+    DINO_CUDA(cudaEventCreateWithFlags(&p->ev_prep, cudaEventDisableTiming));
   }
   *out = p;
   return 0;
@@ -1027,6 +1038,21 @@ extern "C" int dino_h1_fwd_bwd(DinoPlan* p, const float* params, const DinoBatch
     if (run_losses(p, b, B, w_l2, w_h1, inv_gb, true, stats, st, imp)) return 1;
     if (p->jac_mode != DINO_JAC_NONE && run_chain_backward(p, params, B, grad, top, wg, st, imp ? &cx : nullptr)) return 1;
     if (prof_end(p, st)) return 1;
+  }
+  if (!p->chain_fused && p->side != nullptr && p->jac_mode != DINO_JAC_NONE && wg.n > 0) {
+    // fork: network backward (and its weight gradients) on the high-priority side stream, the chain's grouped weight
+    // gradients on the main stream; both only ADD into the gradient (the one plain store into it, W_1 S of the
+    // Jacobian-free first layer, was enqueued before the fork)
+    GemmGroup wg2;
+    wg2.n = 0;
+    DINO_CUDA(cudaEventRecord(p->ev_fork, st));
+    DINO_CUDA(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+    if (run_mlp_backward(p, params, B, grad, wg2, p->side)) return 1;
+    if (flush_wgrad(p, wg2, p->side)) return 1;
+    DINO_CUDA(cudaEventRecord(p->ev_join, p->side));
+    if (flush_wgrad(p, wg, st)) return 1;
+    DINO_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
+    return 0;
   }
   if (run_mlp_backward(p, params, B, grad, wg, st)) return 1;
   return flush_wgrad(p, wg, st);
