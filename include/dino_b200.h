@@ -9,8 +9,11 @@
  *   - plain C: pointers, sizes, no torch / C++ types.  Every pointer named d_* / listed as
  *     "device" is a CUDA device pointer owned by the caller.  The library never allocates or
  *     frees device memory: the caller supplies one workspace (dino_plan_workspace_bytes).
- *   - all tensors fp32, row-major, dense.  Kernels are launched on `stream` (a cudaStream_t
- *     passed as void*), asynchronously; no entry point synchronises the host.
+ *   - all tensors fp32, row-major, dense (the one exception: DinoBatch.ld_J).  Kernels are launched on
+ *     `stream` (a cudaStream_t passed as void*), asynchronously; no entry point synchronises the host.
+ *     dino_h1_fwd_bwd of a tensor-core plan also uses one plan-owned side stream, forked from and joined
+ *     back into `stream` by events inside the call (capturable in a CUDA graph; DINO_B200_NO_SIDE_STREAM=1
+ *     keeps everything on `stream`): work enqueued on `stream` after the call sees all of its results.
  *   - return 0 on success, non-zero on error; dino_last_error() gives a thread-local message.
  *   - a plan is not thread-safe; use one plan per (device, network, host thread).
  *   - built for sm_100a only; there is no CPU or other-architecture fallback.
