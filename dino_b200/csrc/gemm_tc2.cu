@@ -26,19 +26,21 @@ using namespace tc;
 constexpr int T2_BK = 32;
 
 // NCONV: converter warps of the fp32x3 form (a stage of 32 KB per 1536 MMA clocks: four keep up)
-template <bool SPLIT, int EPI, int NEPI, int STAGES, int NCONV>
+template <bool SPLIT, int EPI, int NEPI, int STAGES, int NCONV, int BN2>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((2 + NEPI + (SPLIT ? NCONV : 0)) * 32, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const TcEpilogue ep,
                 const __grid_constant__ CUtensorMap tma_b_lo) {
-  constexpr int A_BYTES = 128 * T2_BK * 4, B_BYTES = 128 * T2_BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
+  // BN2: columns of the pair's tile (256, or 128: half the operand reuse, but main + cross accumulators of fp32x3 then
+  // fit tensor memory twice and the epilogue of a tile overlaps the next tile's main loop)
+  constexpr int A_BYTES = 128 * T2_BK * 4, B_BYTES = (BN2 / 2) * T2_BK * 4, RAW_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGE_BYTES = SPLIT ? 2 * RAW_BYTES : RAW_BYTES;
-  constexpr uint32_t ACC_COLS = 256;
+  constexpr uint32_t ACC_COLS = BN2;
   // fp32x3: main sum + cross-term accumulator (as in gemm_tc.cu) fill tensor memory: one set, the epilogue does not
   // overlap the next tile.  (Tried: one accumulator and two passes over K - cross terms first, then the main products -
   // which frees the second set; the extra operand pass cost more than the overlap gave: 384 us against 240 us at
   // [25600,1024] x [1024,1024].  The feed - TMA, conversion, hand-over - not the tensor pipe, paces this kernel.)
-  constexpr uint32_t SET_COLS = SPLIT ? 512 : 256;
-  constexpr int NACC = SPLIT ? 1 : 2;
+  constexpr uint32_t SET_COLS = SPLIT ? 2 * ACC_COLS : ACC_COLS;
+  constexpr int NACC = 2 * SET_COLS <= 512 ? 2 : 1;
   constexpr int EPI_BUF = 32 * 128;
   constexpr int CONV0 = 2 + NEPI;
 
@@ -56,7 +58,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   const uint32_t rank = cluster_ctarank();                   // 0 = leader
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const int nkb = (ep.K + T2_BK - 1) / T2_BK;
-  const int tiles_n = (ep.N + 255) / 256, n_tiles = tiles_n * ((ep.M + 255) / 256);
+  const int tiles_n = (ep.N + BN2 - 1) / BN2, n_tiles = tiles_n * ((ep.M + 255) / 256);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
@@ -84,7 +86,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     if (lane == 0) {
       int it = 0;
       for (int tile = pair; tile < n_tiles; tile += n_pairs) {
-        const int m0 = (tile / tiles_n) * 256 + (int)rank * 128, n0 = (tile % tiles_n) * 256 + (int)rank * 128;
+        const int m0 = (tile / tiles_n) * 256 + (int)rank * 128, n0 = (tile % tiles_n) * BN2 + (int)rank * (BN2 / 2);
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int st = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
@@ -106,7 +108,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   } else if (warp == 1) {
     // ===== MMA issuer: the leader CTA's elected thread, for the pair =====
     if (rank == 0 && lane == 0) {
-      const uint32_t idesc = idesc_tf32_m(256, 256);
+      const uint32_t idesc = idesc_tf32_m(256, BN2);
       int it = 0, i = 0;
       for (int tile = pair; tile < n_tiles; tile += n_pairs, ++i) {
         const int acc = i % NACC;
@@ -156,11 +158,11 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     int i = 0;
 #pragma unroll 1
     for (int tile = pair; tile < n_tiles; tile += n_pairs, ++i) {
-      const int m0 = (tile / tiles_n) * 256 + (int)rank * 128, n0 = (tile % tiles_n) * 256;
+      const int m0 = (tile / tiles_n) * 256 + (int)rank * 128, n0 = (tile % tiles_n) * BN2;
       const int acc = i % NACC;
       mbar_wait(tmem_full_bar + acc, (i / NACC) & 1);
       tc_fence_after();
-      tc_epilogue_tile<256, SPLIT, EPI, NEPI, ACC_COLS>(ep, m0, n0, tmem_base + (uint32_t)acc * SET_COLS, my_stage, q, half, lane, ep.M);
+      tc_epilogue_tile<BN2, SPLIT, EPI, NEPI, ACC_COLS>(ep, m0, n0, tmem_base + (uint32_t)acc * SET_COLS, my_stage, q, half, lane, ep.M);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(tmem_empty_bar + acc, 0);
@@ -174,15 +176,15 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
 }
 
-template <bool SPLIT, int EPI, int NEPI, int STAGES, int NCONV>
+template <bool SPLIT, int EPI, int NEPI, int STAGES, int NCONV, int BN2 = 256>
 static cudaError_t launch_tc2(const GemmOp& op, cudaStream_t st) {
   CUtensorMap ma, mb, mbl;
   if (!tc_make_map(&ma, op.A, op.K, op.M, op.a_sm, T2_BK, 128, (int)CU_TENSOR_MAP_SWIZZLE_128B) ||
-      !tc_make_map(&mb, op.B, op.K, op.N, op.b_sn, T2_BK, 128, (int)CU_TENSOR_MAP_SWIZZLE_128B))
+      !tc_make_map(&mb, op.B, op.K, op.N, op.b_sn, T2_BK, BN2 / 2, (int)CU_TENSOR_MAP_SWIZZLE_128B))
     return cudaErrorInvalidValue;
   const bool b_lo = SPLIT && op.B_lo != nullptr && (reinterpret_cast<uintptr_t>(op.B_lo) & 15) == 0;
   if (b_lo) {
-    if (!tc_make_map(&mbl, op.B_lo, op.K, op.N, op.b_sn, T2_BK, 128, (int)CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    if (!tc_make_map(&mbl, op.B_lo, op.K, op.N, op.b_sn, T2_BK, BN2 / 2, (int)CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
   } else mbl = mb;
   TcEpilogue ep;
   ep.M = op.M; ep.N = op.N; ep.K = op.K; ep.C = op.C; ep.ldc = op.ldc; ep.sdim = op.sdim > 0 ? op.sdim : 1;
@@ -192,16 +194,16 @@ static cudaError_t launch_tc2(const GemmOp& op, cudaStream_t st) {
   ep.yref = op.rowsum ? op.yref : nullptr; ep.ld_y = op.ld_y; ep.rowsum = op.rowsum; ep.ld_rs = op.ld_rs;
   ep.round_tf32 = SPLIT ? 0 : op.round_tf32;
   ep.a_rows = 0; ep.a_tps = 0; ep.a_idx = nullptr; ep.rowdot = nullptr; ep.pre_first = 0; ep.a_gran = 0; ep.b_lo = b_lo ? 1 : 0;
-  constexpr int RAW = 2 * 128 * T2_BK * 4;
+  constexpr int RAW = (128 + BN2 / 2) * T2_BK * 4;
   constexpr int SMEM = STAGES * (SPLIT ? 2 * RAW : RAW) + NEPI * 32 * 128 + 256 + 1024;
   static_assert(SMEM <= 232448, "shared memory budget of one CTA");
   static std::atomic<unsigned long long> attr_mask{0};
-  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(gemm_tc2_kernel<SPLIT, EPI, NEPI, STAGES, NCONV>), SMEM, attr_mask);
+  cudaError_t e = tc_set_smem_once(reinterpret_cast<const void*>(gemm_tc2_kernel<SPLIT, EPI, NEPI, STAGES, NCONV, BN2>), SMEM, attr_mask);
   if (e != cudaSuccess) return e;
   const int num_sms = tc_current_num_sms();
-  const long long n_tiles = (long long)((op.N + 255) / 256) * ((op.M + 255) / 256);
+  const long long n_tiles = (long long)((op.N + BN2 - 1) / BN2) * ((op.M + 255) / 256);
   const int pairs = (int)(n_tiles < num_sms / 2 ? n_tiles : num_sms / 2);
-  gemm_tc2_kernel<SPLIT, EPI, NEPI, STAGES, NCONV><<<2 * pairs, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep, mbl);
+  gemm_tc2_kernel<SPLIT, EPI, NEPI, STAGES, NCONV, BN2><<<2 * pairs, (2 + NEPI + (SPLIT ? NCONV : 0)) * 32, SMEM, st>>>(ma, mb, ep, mbl);
   return cudaGetLastError();
 }
 
@@ -220,6 +222,9 @@ cudaError_t launch_gemm_tc2(const GemmOp& op, int split, cudaStream_t st) {
     //  same accuracy - which came out slower, 274 against 241 us: the conversion got heavier and the kernel is not
     //  bound by the tensor pipe but by the clocks it can hold under the power cap.)
     // (eight converter warps instead of four: 576 threads leave 96 registers each, the chain epilogue spills, 3 % slower)
+    // (Measured: launch_tc2<true, 1, 8, 4, 4, 128> - 256 x 128 tiles, whose two accumulator sets let the epilogue overlap the
+    //  next tile, four 48 KB stages - runs the cfg5 chain stage in 3.6 ms against 2.9 ms: at half the operand reuse the
+    //  main loop loses more than the exposed epilogue costs.  Not instantiated.)
     if (net) return launch_tc2<true, 2, 8, 3, 4>(op, st);
     if (chain) return launch_tc2<true, 1, 8, 3, 4>(op, st);
     return launch_tc2<true, 0, 8, 3, 4>(op, st);
